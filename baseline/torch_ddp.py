@@ -1,0 +1,95 @@
+"""Stand-in baseline: the SAME model/config as bench.py run through PyTorch
+eager + cuDNN/cuBLAS + DistributedDataParallel/NCCL -- "a path that only calls NCCL for the gradient
+all-reduce" (BASELINE.json). It exists because the TensorFlow reference cannot be installed on this
+image; it is NOT the reference arm (``--impl reference`` reports unavailable) and none of the product's
+kernels are used here. Built fairly: channels-last, cudnn.benchmark on, no host syncs inside a step.
+
+Timing protocol is identical to the product arm: per-step CUDA events with an L2 flush between steps,
+max over ranks; e2e region with pinned H2D input copy and a D2H loss read every step.
+"""
+from __future__ import annotations
+
+import json
+import os
+import time
+
+
+def build_model_a(torch):
+    nn = torch.nn
+    return nn.Sequential(nn.Conv2d(1, 32, 3), nn.ReLU(), nn.MaxPool2d(2), nn.Flatten(),
+                         nn.Linear(5408, 64), nn.ReLU(), nn.Linear(64, 10))
+
+
+def run(args, METRIC, ClockSampler, max_over_ranks, barrier, dist_env, make_batches):
+    import torch
+    import torch.distributed as dist
+    rank, world, local = dist_env()
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=dev)
+    torch.backends.cudnn.benchmark = True
+    torch.manual_seed(1234)
+    model = build_model_a(torch).to(dev).to(memory_format=torch.channels_last)
+    net = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local]) if world > 1 else model
+    opt = torch.optim.SGD(net.parameters(), lr=0.001)
+    lossf = torch.nn.CrossEntropyLoss()
+    B = args.batch_per_gpu
+    gb = B * world
+    xs, ys = make_batches(8, B, seed=100 + rank)
+    xs = [x.permute(0, 3, 1, 2).contiguous().pin_memory() for x in xs]
+    in_x = torch.empty((B, 1, 28, 28), dtype=torch.uint8, device=dev)
+    in_y = torch.empty((B,), dtype=torch.int64, device=dev)
+
+    def step(x_u8, y):
+        x = x_u8.float().div_(255.0).contiguous(memory_format=torch.channels_last)
+        opt.zero_grad(set_to_none=True)
+        loss = lossf(net(x), y)
+        loss.backward()
+        opt.step()
+        return loss
+
+    W = max(args.warmup, 3)
+    for i in range(W):
+        in_x.copy_(xs[i % 8], non_blocking=True); in_y.copy_(ys[i % 8], non_blocking=True)
+        step(in_x, in_y)
+    torch.cuda.synchronize()
+    K = args.steps
+    flush = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    sampler = ClockSampler(local)
+    barrier(world); torch.cuda.synchronize(); sampler.start()
+    for i in range(K):
+        if flush is not None:
+            flush.fill_(i & 0xFF)
+        starts[i].record()
+        step(in_x, in_y)
+        ends[i].record()
+    torch.cuda.synchronize(); barrier(world)
+    clocks = sampler.stop()
+    dev_ms = max_over_ranks(sum(s.elapsed_time(e) for s, e in zip(starts, ends)), world)
+    del flush
+    barrier(world); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    lv = 0.0
+    for i in range(K):
+        in_x.copy_(xs[i % 8], non_blocking=True); in_y.copy_(ys[i % 8], non_blocking=True)
+        lv = step(in_x, in_y).item()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0, world)
+    h2d = xs[0].numel() + ys[0].numel() * 8
+    out = {"metric": METRIC, "value": gb * K / (dev_ms / 1e3), "unit": "images/sec", "n_gpus": world, "steps": K,
+           "warmup": W, "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": "torch_eager_ddp_nccl_standin",
+           "config": {"model": "keras_mnist_cnn_conv32_pool_dense64_dense10", "global_batch": gb,
+                      "per_gpu_batch": B, "parallelism": f"dp{world}", "optimizer": "sgd",
+                      "l2": "flushed between timed steps" if not args.no_flush else "not flushed"},
+           "clocks": clocks,
+           "e2e": {"value": gb * K / e2e_s, "unit": "images/sec", "ms_per_step": 1e3 * e2e_s / K,
+                   "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "last_loss": lv},
+           "gpu_launches": 0}
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()

@@ -1,0 +1,330 @@
+// G12: gradient all-reduce over NVLink 5 / NVSwitch peer memory, FUSED with the 1/N scale, the optional
+// bf16 wire cast and the SGD / momentum / Adam update -- the per-step collective that TensorFlow runs
+// through NCCL cross_device_ops under MultiWorkerMirroredStrategy / MirroredStrategy
+// (distributed_with_keras.py:16,63; mnist_keras_distributed.py:243). No NCCL call and no separate
+// optimizer kernel on this path (G11 is folded in). Also serves G13 (initial broadcast) and G14 (metric
+// aggregation: the 4-float tail of the gradient arena is reduced with the gradients).
+//
+// Design (B200-first): every GPU reaches every peer at full bandwidth through NVSwitch, so there is
+// no ring. All NVLink traffic is *posted writes* (stores into the peer's receive slots); every load
+// is local. Two algorithms:
+//
+//   one-shot  (small arenas / few ranks): each rank pushes its whole gradient into slot[rank] of every
+//             peer, one flag barrier, every rank sums the N slots in rank order (bit-identical
+//             replicas) and applies the optimizer to its full local weights.  bytes out: (N-1)*S.
+//   two-shot  (large arenas): rank r owns slice r. push slice j to rank j (reduce-scatter), barrier,
+//             owner reduces + applies the optimizer on its slice only (optimizer state sharded by
+//             owner = ZeRO-1 for free), pushes the updated weights to every peer (all-gather),
+//             barrier.  bytes out: 2*(N-1)/N*S.
+//
+// Synchronisation: block b of every rank handles the same sub-range, so a per-(rank, block) flag is
+// enough -- no grid-wide sync, no cooperative launch. Flags carry a monotonically increasing epoch
+// kept in device memory, which makes the kernel replayable inside a CUDA graph. Receive slots are
+// double-buffered by epoch parity, which removes the exit barrier of the one-shot path: a slot
+// written at epoch e is rewritten at e+2, and a rank can only reach e+2 after every peer passed the
+// barrier of e+1, i.e. after it finished reading e. Waits are bounded: on timeout the kernel records
+// (code, epoch, peer, block) in a status word and stops spinning instead of hanging the GPU.
+//
+// All blocks of one launch must be co-resident (grid <= 148 * occupancy); the host wrapper enforces it.
+#include "common.cuh"
+#include <cuda_bf16.h>
+#include <cstring>
+
+namespace {
+
+constexpr int MAX_RANKS = 8;
+constexpr int MAX_BLOCKS = 256;
+constexpr int AR_THREADS = 512;
+
+struct ARParams {
+  int rank, world;
+  int mode;            // 0 one-shot, 1 two-shot
+  int opt;             // -1 reduce only, 0 SGD, 1 momentum, 2 nesterov, 3 Adam
+  int wire_bf16;       // push gradients as bf16
+  long n;              // trainable floats
+  long n_total;        // n + extras (reduced, not updated), multiple of 4
+  long slot_floats;    // floats per receive slot (one-shot: n_total, two-shot: slice size)
+  const float* g;      // local gradient arena [n_total]
+  float* w;            // local parameter arena [n_total] (tail receives the reduced extras)
+  float* s1; float* s2;            // optimizer slots (two-shot: slice-sized, one-shot: full)
+  __nv_bfloat16* w_bf16;           // optional local bf16 shadow of the weights [n_total]
+  float* recv[MAX_RANKS];          // peer-mapped receive buffers: [2 parity][world][slot_floats]
+  float* wpeer[MAX_RANKS];         // peer-mapped parameter arenas (two-shot all-gather targets)
+  __nv_bfloat16* wbf_peer[MAX_RANKS];
+  uint32_t* flags[MAX_RANKS];      // peer-mapped signal pads: [2 phase][world][MAX_BLOCKS]
+  uint32_t* epoch;                 // local [MAX_BLOCKS]
+  float* metrics;                  // local running sums of the extras, or nullptr
+  int n_extra;
+  TfdeHParams* hp;
+  unsigned* done_counter;          // local ticket for the hparams advance
+  int* status;                     // local [4]: code, epoch, peer, block
+  unsigned long long timeout_ns;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Signal "my block `b` finished its pushes of phase `phase`" to every peer, then wait for theirs.
+__device__ __forceinline__ void flag_barrier(const ARParams& p, int phase, int b, uint32_t e) {
+  __syncthreads();  // all pushes of this block issued
+  const int t = threadIdx.x;
+  if (t < p.world && t != p.rank) {
+    __threadfence_system();
+    st_release_sys(p.flags[t] + ((size_t)phase * p.world + p.rank) * MAX_BLOCKS + b, e);
+    const uint32_t* mine = p.flags[p.rank] + ((size_t)phase * p.world + t) * MAX_BLOCKS + b;
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned spins = 0;
+    while ((int)(ld_acquire_sys(mine) - e) < 0) {
+      if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > p.timeout_ns) {
+        if (atomicCAS(p.status, 0, 1) == 0) { p.status[1] = (int)e; p.status[2] = t; p.status[3] = b; }
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float bf16_round(float v) { return __bfloat162float(__float2bfloat16(v)); }
+
+struct Hyper { float lr, mu, b1, b2, eps, gs, lr_t; };
+
+__device__ __forceinline__ float update_one(int opt, float w, float g, float* s1, float* s2, long si,
+                                            const Hyper& h) {
+  if (opt < 0) return g;
+  g *= h.gs;
+  if (opt == 0) return w - h.lr * g;
+  if (opt == 1 || opt == 2) {
+    const float v = h.mu * s1[si] - h.lr * g;
+    s1[si] = v;
+    return w + (opt == 2 ? (h.mu * v - h.lr * g) : v);
+  }
+  const float m = h.b1 * s1[si] + (1.f - h.b1) * g;
+  const float v = h.b2 * s2[si] + (1.f - h.b2) * g * g;
+  s1[si] = m; s2[si] = v;
+  return w - h.lr_t * m / (sqrtf(v) + h.eps);
+}
+
+// Push `cnt` floats (multiple of 4, 16-byte aligned) from local src to a peer slot.
+__device__ __forceinline__ void push_f32(float* dst, const float* src, long cnt) {
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+  float4* d4 = reinterpret_cast<float4*>(dst);
+  for (long i = threadIdx.x; i < cnt / 4; i += blockDim.x) __stcg(d4 + i, __ldg(s4 + i));
+}
+// bf16 wire format: slot holds cnt bf16 values (packed), cnt multiple of 4.
+__device__ __forceinline__ void push_bf16(float* dst, const float* src, long cnt) {
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+  uint2* d2 = reinterpret_cast<uint2*>(dst);
+  for (long i = threadIdx.x; i < cnt / 4; i += blockDim.x) {
+    const float4 v = __ldg(s4 + i);
+    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+    uint2 o; o.x = *reinterpret_cast<uint32_t*>(&a); o.y = *reinterpret_cast<uint32_t*>(&b);
+    __stcg(d2 + i, o);
+  }
+}
+__device__ __forceinline__ float slot_load(const float* slot, long i, int wire_bf16) {
+  if (!wire_bf16) return __ldcg(slot + i);
+  const unsigned short raw = __ldcg(reinterpret_cast<const unsigned short*>(slot) + i);
+  return __uint_as_float(((uint32_t)raw) << 16);
+}
+
+__global__ void __launch_bounds__(AR_THREADS)
+allreduce_fused_kernel(const ARParams p) {
+  const int b = blockIdx.x, nb = gridDim.x, t = threadIdx.x;
+  __shared__ uint32_t s_e;
+  if (t == 0) s_e = p.epoch[b] + 1u;
+  __syncthreads();
+  const uint32_t e = s_e;
+  const int parity = (int)(e & 1u);
+  const int W = p.world, R = p.rank;
+
+  Hyper h;
+  if (p.opt >= 0) {
+    h.lr = p.hp->lr; h.mu = p.hp->momentum; h.b1 = p.hp->beta1; h.b2 = p.hp->beta2; h.eps = p.hp->eps;
+    h.gs = p.hp->grad_scale;
+    const float b1p = p.hp->beta1_pow * h.b1, b2p = p.hp->beta2_pow * h.b2;
+    h.lr_t = (p.opt == 3) ? h.lr * sqrtf(1.f - b2p) / (1.f - b1p) : h.lr;
+  } else {
+    h.lr = h.mu = h.b1 = h.b2 = h.eps = h.lr_t = 0.f; h.gs = 1.f;
+  }
+
+  const long slot = p.slot_floats;
+  if (p.mode == 0) {
+    // ------------------------------- one-shot -------------------------------------------
+    long chunk = (p.n_total + nb - 1) / nb; chunk = (chunk + 3) & ~3L;
+    const long lo = min((long)b * chunk, p.n_total), hi = min(lo + chunk, p.n_total);
+    const long cnt = hi - lo;
+    for (int i = 1; i < W; ++i) {
+      const int peer = (R + i) % W;
+      float* dst = p.recv[peer] + ((size_t)parity * W + R) * slot;
+      if (p.wire_bf16) push_bf16(reinterpret_cast<float*>(reinterpret_cast<unsigned short*>(dst) + lo), p.g + lo, cnt);
+      else             push_f32(dst + lo, p.g + lo, cnt);
+    }
+    flag_barrier(p, 0, b, e);
+    const float* base = p.recv[R] + (size_t)parity * W * slot;
+    for (long i = lo + t; i < hi; i += blockDim.x) {
+      float s = 0.f;
+      for (int r = 0; r < W; ++r) {
+        float v;
+        if (r == R) { v = __ldg(p.g + i); if (p.wire_bf16) v = bf16_round(v); }
+        else v = slot_load(base + (size_t)r * slot, i, p.wire_bf16);
+        s += v;
+      }
+      float nw;
+      if (i < p.n) nw = update_one(p.opt, p.w[i], s, p.s1, p.s2, i, h);
+      else { nw = s; if (p.metrics && i - p.n < p.n_extra) p.metrics[i - p.n] += s; }
+      p.w[i] = nw;
+      if (p.w_bf16 && i < p.n) p.w_bf16[i] = __float2bfloat16(nw);
+    }
+  } else {
+    // ------------------------------- two-shot -------------------------------------------
+    // slice j = [j*slot, (j+1)*slot) ; this block handles sub-range [lo, hi) of every slice.
+    long chunk = (slot + nb - 1) / nb; chunk = (chunk + 3) & ~3L;
+    const long lo = min((long)b * chunk, slot), hi = min(lo + chunk, slot);
+    for (int i = 1; i < W; ++i) {
+      const int peer = (R + i) % W;
+      const long gbeg = (long)peer * slot + lo;
+      long cnt = min((long)peer * slot + hi, p.n_total) - gbeg;
+      if (cnt <= 0) continue;
+      float* dst = p.recv[peer] + ((size_t)parity * W + R) * slot;
+      if (p.wire_bf16) push_bf16(reinterpret_cast<float*>(reinterpret_cast<unsigned short*>(dst) + lo), p.g + gbeg, cnt);
+      else             push_f32(dst + lo, p.g + gbeg, cnt);
+    }
+    flag_barrier(p, 0, b, e);
+    const float* base = p.recv[R] + (size_t)parity * W * slot;
+    const long own0 = (long)R * slot;
+    for (long li = lo + t; li < hi; li += blockDim.x) {
+      const long i = own0 + li;
+      if (i >= p.n_total) break;
+      float s = 0.f;
+      for (int r = 0; r < W; ++r) {
+        float v;
+        if (r == R) { v = __ldg(p.g + i); if (p.wire_bf16) v = bf16_round(v); }
+        else v = slot_load(base + (size_t)r * slot, li, p.wire_bf16);
+        s += v;
+      }
+      const float nw = (i < p.n) ? update_one(p.opt, p.w[i], s, p.s1, p.s2, li, h) : s;
+      // all-gather: write the new value into every replica (own included)
+      for (int r = 0; r < W; ++r) {
+        const int peer = (R + r) % W;
+        __stcg(p.wpeer[peer] + i, nw);
+        if (p.w_bf16 && i < p.n) p.wbf_peer[peer][i] = __float2bfloat16(nw);
+      }
+    }
+    flag_barrier(p, 1, b, e);
+    // every slice's sub-range [lo,hi) has now landed locally: accumulate the metrics tail once.
+    if (p.metrics) {
+      for (int j = t; j < p.n_extra; j += blockDim.x) {
+        const long i = p.n + j;
+        const long li = i % slot;
+        if (li >= lo && li < hi) p.metrics[j] += __ldcg(p.w + i);
+      }
+    }
+  }
+
+  __syncthreads();
+  if (t == 0) {
+    p.epoch[b] = e;
+    if (atomicAdd(p.done_counter, 1u) == (unsigned)nb - 1u) {
+      // last block of this launch: every block has consumed the old hyper-parameters by now
+      if (p.opt >= 0) {
+        p.hp->beta1_pow *= p.hp->beta1;
+        p.hp->beta2_pow *= p.hp->beta2;
+        p.hp->step += 1u;
+      }
+      *p.done_counter = 0u;
+    }
+  }
+}
+
+// Pull copy used for the initial broadcast (G13): dst(local) <- src(peer-mapped), float4 granularity.
+__global__ void p2p_copy_kernel(float* __restrict__ dst, const float* __restrict__ src, long n) {
+  const long n4 = n / 4;
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+  float4* d4 = reinterpret_cast<float4*>(dst);
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x)
+    d4[i] = s4[i];
+  for (long i = n4 * 4 + (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+    dst[i] = src[i];
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// Host side: symmetric allocation + IPC plumbing (setup only) and the launch wrapper.
+// ---------------------------------------------------------------------------------------------
+TFDE_API int tfde_set_device(int dev) { return (int)cudaSetDevice(dev); }
+
+TFDE_API int tfde_symm_alloc(size_t bytes, void** out) {
+  cudaError_t e = cudaMalloc(out, bytes);
+  if (e != cudaSuccess) return (int)e;
+  return (int)cudaMemset(*out, 0, bytes);
+}
+TFDE_API int tfde_symm_free(void* p) { return (int)cudaFree(p); }
+TFDE_API int tfde_ipc_get_handle(void* p, void* handle64) {
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) return (int)e;
+  memcpy(handle64, &h, sizeof(h));
+  return 0;
+}
+TFDE_API int tfde_ipc_open_handle(const void* handle64, void** out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  return (int)cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess);
+}
+TFDE_API int tfde_ipc_close_handle(void* p) { return (int)cudaIpcCloseMemHandle(p); }
+TFDE_API int tfde_ipc_handle_bytes() { return (int)sizeof(cudaIpcMemHandle_t); }
+TFDE_API int tfde_ar_max_ranks() { return MAX_RANKS; }
+TFDE_API int tfde_ar_max_blocks() { return MAX_BLOCKS; }
+TFDE_API size_t tfde_ar_flag_bytes(int world) { return (size_t)2 * world * MAX_BLOCKS * sizeof(uint32_t); }
+
+// Descriptor filled by the Python side once (pointers are stable), then passed by value per launch.
+struct TfdeARDesc {
+  int rank, world, mode, opt, wire_bf16, n_extra, blocks, reserved;
+  long n, n_total, slot_floats;
+  const float* g; float* w; float* s1; float* s2; void* w_bf16;
+  void* recv[MAX_RANKS]; void* wpeer[MAX_RANKS]; void* wbf_peer[MAX_RANKS]; void* flags[MAX_RANKS];
+  void* epoch; float* metrics; void* hp; void* done_counter; void* status;
+  unsigned long long timeout_ns;
+};
+
+TFDE_API size_t tfde_ar_desc_bytes() { return sizeof(TfdeARDesc); }
+
+TFDE_API int tfde_allreduce_fused(const TfdeARDesc* d, cudaStream_t stream) {
+  if (d->world < 1 || d->world > MAX_RANKS || d->blocks < 1 || d->blocks > MAX_BLOCKS) return TFDE_ERR_INVALID;
+  if ((d->n_total & 3) || (d->slot_floats & 3) || d->n_extra > 32) return TFDE_ERR_INVALID;
+  if (d->opt >= 1 && !d->s1) return TFDE_ERR_INVALID;
+  if (d->opt == 3 && !d->s2) return TFDE_ERR_INVALID;
+  ARParams p{};
+  p.rank = d->rank; p.world = d->world; p.mode = d->mode; p.opt = d->opt; p.wire_bf16 = d->wire_bf16;
+  p.n = d->n; p.n_total = d->n_total; p.slot_floats = d->slot_floats;
+  p.g = d->g; p.w = d->w; p.s1 = d->s1; p.s2 = d->s2; p.w_bf16 = (__nv_bfloat16*)d->w_bf16;
+  for (int i = 0; i < MAX_RANKS; ++i) {
+    p.recv[i] = (float*)d->recv[i]; p.wpeer[i] = (float*)d->wpeer[i];
+    p.wbf_peer[i] = (__nv_bfloat16*)d->wbf_peer[i]; p.flags[i] = (uint32_t*)d->flags[i];
+  }
+  p.epoch = (uint32_t*)d->epoch; p.metrics = d->metrics; p.n_extra = d->n_extra;
+  p.hp = (TfdeHParams*)d->hp; p.done_counter = (unsigned*)d->done_counter; p.status = (int*)d->status;
+  p.timeout_ns = d->timeout_ns ? d->timeout_ns : 20000000000ULL;
+  allreduce_fused_kernel<<<d->blocks, AR_THREADS, 0, stream>>>(p);
+  TFDE_RETURN_LAUNCH_STATUS();
+}
+
+TFDE_API int tfde_p2p_copy(float* dst, const float* src, long n, cudaStream_t stream) {
+  long grid = (n / 4 + 255) / 256;
+  if (grid > 148L * 4) grid = 148L * 4;
+  if (grid < 1) grid = 1;
+  p2p_copy_kernel<<<(int)grid, 256, 0, stream>>>(dst, src, n);
+  TFDE_RETURN_LAUNCH_STATUS();
+}

@@ -1,0 +1,172 @@
+// Fused first layer of "Model A" (distributed_with_keras.py:34-35):
+//   Conv2D(32, 3, activation='relu', input_shape=(28,28,1)) -> MaxPooling2D()
+// Forward writes only the pooled activation [B,13,13,32] and a 2-bit arg-max per element (G1+G6 in
+// SURVEY.md section 2.7); the 26x26x32 conv output (5.5 MB at B=64) never exists in memory.
+// Backward fuses pool routing + ReLU mask + conv filter/bias gradient (G2+G6+G8); as this is the
+// first layer there is no data gradient.
+//
+// Mapping: Cin == 1 makes K = 9, far below any tensor-core tile and below TMA's 16-byte inner
+// box rule, so this is a CUDA-core kernel: one warp per pooled pixel, lane == output channel
+// (Cout must be 32). The 4x4 input patch is read once by 16 lanes and broadcast with shuffles.
+// The input may be uint8 (raw MNIST) -- the /255 scaling of distributed_with_keras.py:20-23 is
+// folded into the load (G15).
+#include "common.cuh"
+
+namespace {
+
+constexpr int WARPS = 8;
+
+template <bool U8>
+__global__ void __launch_bounds__(WARPS * 32)
+conv3x3c1_relu_pool_fwd_kernel(const void* __restrict__ xin, const float* __restrict__ w,
+                               const float* __restrict__ bias, float* __restrict__ pooled,
+                               uint8_t* __restrict__ idx, int Bn, int H, int W, int PH, int PW,
+                               float in_scale) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float wr[9];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) wr[i] = __ldg(w + i * 32 + lane);
+  const float b = bias ? __ldg(bias + lane) : 0.f;
+  const long total = (long)Bn * PH * PW;
+  for (long p = (long)blockIdx.x * WARPS + warp; p < total; p += (long)gridDim.x * WARPS) {
+    const int pw = (int)(p % PW);
+    const long t = p / PW;
+    const int ph = (int)(t % PH);
+    const long bi = t / PH;
+    float v = 0.f;
+    if (lane < 16) {
+      const long off = (bi * H + (2 * ph + (lane >> 2))) * W + (2 * pw + (lane & 3));
+      if (U8) v = (float)__ldg(reinterpret_cast<const uint8_t*>(xin) + off) * in_scale;
+      else    v = __ldg(reinterpret_cast<const float*>(xin) + off);
+    }
+    float patch[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) patch[i] = __shfl_sync(0xffffffffu, v, i);
+    float best = -1.f;
+    int besti = 0;
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        float o = b;
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+          for (int kw = 0; kw < 3; ++kw) o = fmaf(wr[kh * 3 + kw], patch[(dy + kh) * 4 + dx + kw], o);
+        o = fmaxf(o, 0.f);
+        if (o > best) { best = o; besti = dy * 2 + dx; }
+      }
+    pooled[p * 32 + lane] = best;
+    idx[p * 32 + lane] = (uint8_t)besti;
+  }
+}
+
+// Partials layout: [gridDim.x][320] floats (288 filter taps, then 32 bias entries).
+template <bool U8>
+__global__ void __launch_bounds__(WARPS * 32)
+conv3x3c1_relu_pool_bwd_kernel(const void* __restrict__ xin, const float* __restrict__ pooled,
+                               const uint8_t* __restrict__ idx, const float* __restrict__ dpooled,
+                               float* __restrict__ dw, float* __restrict__ db,
+                               float* __restrict__ partials, unsigned* __restrict__ counter,
+                               int Bn, int H, int W, int PH, int PW, float in_scale) {
+  __shared__ float s_patch[WARPS][16];
+  __shared__ float s_red[WARPS][10][32];
+  __shared__ int s_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float acc[10];
+#pragma unroll
+  for (int i = 0; i < 10; ++i) acc[i] = 0.f;
+  const long total = (long)Bn * PH * PW;
+  for (long p = (long)blockIdx.x * WARPS + warp; p < total; p += (long)gridDim.x * WARPS) {
+    const int pw = (int)(p % PW);
+    const long t = p / PW;
+    const int ph = (int)(t % PH);
+    const long bi = t / PH;
+    __syncwarp();
+    if (lane < 16) {
+      const long off = (bi * H + (2 * ph + (lane >> 2))) * W + (2 * pw + (lane & 3));
+      float v;
+      if (U8) v = (float)__ldg(reinterpret_cast<const uint8_t*>(xin) + off) * in_scale;
+      else    v = __ldg(reinterpret_cast<const float*>(xin) + off);
+      s_patch[warp][lane] = v;
+    }
+    __syncwarp();
+    float g = __ldg(dpooled + p * 32 + lane);
+    if (!(__ldg(pooled + p * 32 + lane) > 0.f)) g = 0.f;
+    const int bsel = idx[p * 32 + lane];
+    const int dy = bsel >> 1, dx = bsel & 1;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw)
+        acc[kh * 3 + kw] = fmaf(g, s_patch[warp][(dy + kh) * 4 + dx + kw], acc[kh * 3 + kw]);
+    acc[9] += g;
+  }
+#pragma unroll
+  for (int i = 0; i < 10; ++i) s_red[warp][i][lane] = acc[i];
+  __syncthreads();
+  // fixed-order reductions => bit-reproducible gradients
+  for (int e = threadIdx.x; e < 320; e += blockDim.x) {
+    const int i = e >> 5, c = e & 31;
+    float s = 0.f;
+#pragma unroll
+    for (int wv = 0; wv < WARPS; ++wv) s += s_red[wv][i][c];
+    __stcg(partials + (size_t)blockIdx.x * 320 + e, s);
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  for (int e = threadIdx.x; e < 320; e += blockDim.x) {
+    float s = 0.f;
+    for (unsigned blk = 0; blk < gridDim.x; ++blk) s += __ldcg(partials + (size_t)blk * 320 + e);
+    if (e < 288) dw[e] = s;          // [kh][kw][ci=0][co]  == e = (kh*3+kw)*32 + co
+    else if (db != nullptr) db[e - 288] = s;
+  }
+  if (threadIdx.x == 0) *counter = 0u;
+}
+
+int grid_for(long total_pixels) {
+  long blocks = (total_pixels + WARPS - 1) / WARPS;
+  const long cap = 148L * 4;
+  return (int)(blocks < cap ? (blocks < 1 ? 1 : blocks) : cap);
+}
+
+}  // namespace
+
+TFDE_API int tfde_conv3x3c1_relu_pool_fwd(const void* x, int x_is_u8, float in_scale,
+                                          const float* w, const float* bias, float* pooled,
+                                          uint8_t* idx, int Bn, int H, int W, int Cout,
+                                          cudaStream_t stream) {
+  if (Cout != 32 || H < 4 || W < 4) return TFDE_ERR_INVALID;
+  const int PH = (H - 2) / 2, PW = (W - 2) / 2;
+  const int grid = grid_for((long)Bn * PH * PW);
+  if (x_is_u8)
+    conv3x3c1_relu_pool_fwd_kernel<true><<<grid, WARPS * 32, 0, stream>>>(x, w, bias, pooled, idx, Bn, H, W, PH, PW, in_scale);
+  else
+    conv3x3c1_relu_pool_fwd_kernel<false><<<grid, WARPS * 32, 0, stream>>>(x, w, bias, pooled, idx, Bn, H, W, PH, PW, 1.f);
+  TFDE_RETURN_LAUNCH_STATUS();
+}
+
+// Number of floats of scratch the backward needs (partials), independent of the batch size.
+TFDE_API size_t tfde_conv3x3c1_relu_pool_bwd_ws_floats() { return (size_t)148 * 4 * 320; }
+
+TFDE_API int tfde_conv3x3c1_relu_pool_bwd(const void* x, int x_is_u8, float in_scale,
+                                          const float* pooled, const uint8_t* idx,
+                                          const float* dpooled, float* dw, float* db,
+                                          float* partials, unsigned* counter, int Bn, int H, int W,
+                                          int Cout, cudaStream_t stream) {
+  if (Cout != 32 || H < 4 || W < 4) return TFDE_ERR_INVALID;
+  const int PH = (H - 2) / 2, PW = (W - 2) / 2;
+  long blocks = ((long)Bn * PH * PW + WARPS * 16 - 1) / (WARPS * 16);  // >= 16 pixels per warp
+  if (blocks < 1) blocks = 1;
+  if (blocks > 148L * 2) blocks = 148L * 2;
+  const int grid = (int)blocks;
+  if (x_is_u8)
+    conv3x3c1_relu_pool_bwd_kernel<true><<<grid, WARPS * 32, 0, stream>>>(x, pooled, idx, dpooled, dw, db, partials, counter, Bn, H, W, PH, PW, in_scale);
+  else
+    conv3x3c1_relu_pool_bwd_kernel<false><<<grid, WARPS * 32, 0, stream>>>(x, pooled, idx, dpooled, dw, db, partials, counter, Bn, H, W, PH, PW, 1.f);
+  TFDE_RETURN_LAUNCH_STATUS();
+}

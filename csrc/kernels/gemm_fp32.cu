@@ -1,0 +1,473 @@
+// fp32 CUDA-core GEMM family with gather loaders (dense, transposed, im2col, im2col^T, dgrad
+// gather), deterministic split-K and fused epilogues. This is the exact-fp32 path: the reference
+// trains in fp32 (distributed_with_keras.py:21, mnist_keras_distributed.py:159) and its layers have
+// N = 6..64 output channels and K = 9..5408, i.e. shapes that are bandwidth/latency bound, not
+// tensor-core bound. Large bf16 GEMMs go to gemm_tcgen05.cu instead.
+//
+// One kernel template covers:
+//   G1 conv fwd      C[(b,oh,ow), co] = im2col(x) . W[(kh,kw,ci), co]  (+bias, ReLU)
+//   G2 conv wgrad    dW[(kh,kw,ci), co] = im2col(x)^T . dy   (+ bias-grad as an extra all-ones row)
+//   G3 conv dgrad    dx[(b,h,w), ci] = gather(dy) . Wrot[(kh,kw,co), ci]
+//   G4 dense fwd     y = x . W (+bias)(+ReLU)
+//   G5 dense wgrad   dW = x^T . dy (+db as ones row), dense dgrad dx = dy . W^T
+// ReLU backward never runs as its own kernel: the loaders multiply dy by (y > 0) on the fly (G8).
+#include "common.cuh"
+
+namespace {
+
+constexpr int BK = 16;
+constexpr int NTHREADS = 256;
+
+enum AMode { A_DENSE = 0, A_DENSE_T = 1, A_IM2COL = 2, A_IM2COL_T = 3, A_DGRAD = 4 };
+enum BMode { B_DENSE = 0, B_DENSE_T = 1, B_WROT = 2 };
+
+struct ConvGeom {
+  int H, W, C;      // input spatial size and channels
+  int KH, KW;       // kernel
+  int Ho, Wo;       // output spatial size
+  int sh, sw;       // strides
+  int pt, pl;       // top / left padding
+  int Cout;
+};
+
+struct GemmParams {
+  const float* A; const float* Amask; int lda;
+  const float* B; const float* Bmask; int ldb;
+  float* C; int ldc;
+  float* C2;            // destination of the all-ones row (bias gradient), or nullptr
+  const float* bias;    // added per output column, or nullptr
+  int M, N, K;
+  int ones_row;         // A_op row that is identically 1 (== M-1 when used), else -1
+  int relu;
+  int splits;
+  float* ws;            // split-K partials [splits][M][N]
+  unsigned* counters;   // one ticket per output tile, zero on entry, left zero on exit
+  ConvGeom g;
+};
+
+// ------------------------------------------------------------------------------------------
+// A-operand loaders. row() precomputes whatever depends only on the A_op row index.
+// ------------------------------------------------------------------------------------------
+template <int MODE> struct ALoader;
+
+template <> struct ALoader<A_DENSE> {  // A_op[m,k] = A[m*lda + k]
+  static constexpr bool kFast = true;
+  struct Row { long off; bool ok; };
+  static __device__ __forceinline__ Row row(const GemmParams& p, int m) {
+    return Row{(long)m * p.lda, m < p.M};
+  }
+  static __device__ __forceinline__ float load(const GemmParams& p, const Row& r, int m, int k) {
+    if (!r.ok || k >= p.K) return 0.f;
+    float v = __ldg(p.A + r.off + k);
+    if (p.Amask != nullptr && !(__ldg(p.Amask + r.off + k) > 0.f)) v = 0.f;
+    return v;
+  }
+};
+
+template <> struct ALoader<A_DENSE_T> {  // A_op[m,k] = A[k*lda + m]; optional ones row
+  static constexpr bool kFast = false;
+  struct Row { int m; int kind; };  // kind: 0 = out of range, 1 = data, 2 = ones
+  static __device__ __forceinline__ Row row(const GemmParams& p, int m) {
+    return Row{m, m >= p.M ? 0 : (m == p.ones_row ? 2 : 1)};
+  }
+  static __device__ __forceinline__ float load(const GemmParams& p, const Row& r, int m, int k) {
+    if (r.kind == 0 || k >= p.K) return 0.f;
+    if (r.kind == 2) return 1.f;
+    return __ldg(p.A + (long)k * p.lda + r.m);
+  }
+};
+
+template <> struct ALoader<A_IM2COL> {  // A_op[(b,oh,ow), (kh,kw,ci)] = x[b, oh*sh-pt+kh, ow*sw-pl+kw, ci]
+  static constexpr bool kFast = true;
+  struct Row { long base; int ih0, iw0; bool ok; };
+  static __device__ __forceinline__ Row row(const GemmParams& p, int m) {
+    Row r; r.ok = m < p.M;
+    const int mm = r.ok ? m : 0;
+    const int ow = mm % p.g.Wo; const int t = mm / p.g.Wo;
+    const int oh = t % p.g.Ho; const int b = t / p.g.Ho;
+    r.ih0 = oh * p.g.sh - p.g.pt; r.iw0 = ow * p.g.sw - p.g.pl;
+    r.base = (long)b * p.g.H * p.g.W * p.g.C;
+    return r;
+  }
+  static __device__ __forceinline__ float load(const GemmParams& p, const Row& r, int m, int k) {
+    if (!r.ok || k >= p.K) return 0.f;
+    const int ci = k % p.g.C; const int t = k / p.g.C;
+    const int kw = t % p.g.KW; const int kh = t / p.g.KW;
+    const int ih = r.ih0 + kh, iw = r.iw0 + kw;
+    if ((unsigned)ih >= (unsigned)p.g.H || (unsigned)iw >= (unsigned)p.g.W) return 0.f;
+    return __ldg(p.A + r.base + ((long)ih * p.g.W + iw) * p.g.C + ci);
+  }
+};
+
+template <> struct ALoader<A_IM2COL_T> {  // A_op[(kh,kw,ci), (b,oh,ow)] ; optional ones row
+  static constexpr bool kFast = false;
+  struct Row { int kh, kw, ci; int kind; };
+  static __device__ __forceinline__ Row row(const GemmParams& p, int m) {
+    Row r; r.kind = m >= p.M ? 0 : (m == p.ones_row ? 2 : 1);
+    const int mm = r.kind == 1 ? m : 0;
+    r.ci = mm % p.g.C; const int t = mm / p.g.C;
+    r.kw = t % p.g.KW; r.kh = t / p.g.KW;
+    return r;
+  }
+  static __device__ __forceinline__ float load(const GemmParams& p, const Row& r, int m, int k) {
+    if (r.kind == 0 || k >= p.K) return 0.f;
+    if (r.kind == 2) return 1.f;
+    const int ow = k % p.g.Wo; const int t = k / p.g.Wo;
+    const int oh = t % p.g.Ho; const int b = t / p.g.Ho;
+    const int ih = oh * p.g.sh - p.g.pt + r.kh, iw = ow * p.g.sw - p.g.pl + r.kw;
+    if ((unsigned)ih >= (unsigned)p.g.H || (unsigned)iw >= (unsigned)p.g.W) return 0.f;
+    return __ldg(p.A + (((long)b * p.g.H + ih) * p.g.W + iw) * p.g.C + r.ci);
+  }
+};
+
+template <> struct ALoader<A_DGRAD> {  // A_op[(b,h,w), (kh,kw,co)] = dy[b,(h+pt-kh)/sh,(w+pl-kw)/sw,co]
+  static constexpr bool kFast = true;
+  struct Row { long base; int h, w; bool ok; };
+  static __device__ __forceinline__ Row row(const GemmParams& p, int m) {
+    Row r; r.ok = m < p.M;
+    const int mm = r.ok ? m : 0;
+    r.w = mm % p.g.W; const int t = mm / p.g.W;
+    r.h = t % p.g.H; const int b = t / p.g.H;
+    r.base = (long)b * p.g.Ho * p.g.Wo * p.g.Cout;
+    return r;
+  }
+  static __device__ __forceinline__ float load(const GemmParams& p, const Row& r, int m, int k) {
+    if (!r.ok || k >= p.K) return 0.f;
+    const int co = k % p.g.Cout; const int t = k / p.g.Cout;
+    const int kw = t % p.g.KW; const int kh = t / p.g.KW;
+    const int th = r.h + p.g.pt - kh, tw = r.w + p.g.pl - kw;
+    if (th < 0 || tw < 0) return 0.f;
+    const int oh = th / p.g.sh, ow = tw / p.g.sw;
+    if (oh * p.g.sh != th || ow * p.g.sw != tw || oh >= p.g.Ho || ow >= p.g.Wo) return 0.f;
+    const long off = r.base + ((long)oh * p.g.Wo + ow) * p.g.Cout + co;
+    float v = __ldg(p.A + off);
+    if (p.Amask != nullptr && !(__ldg(p.Amask + off) > 0.f)) v = 0.f;
+    return v;
+  }
+};
+
+// ------------------------------------------------------------------------------------------
+// B-operand loaders
+// ------------------------------------------------------------------------------------------
+template <int MODE> struct BLoader;
+template <> struct BLoader<B_DENSE> {  // B_op[k,n] = B[k*ldb + n]
+  static constexpr bool kFast = false;
+  static __device__ __forceinline__ float load(const GemmParams& p, int k, int n) {
+    if (k >= p.K || n >= p.N) return 0.f;
+    const long off = (long)k * p.ldb + n;
+    float v = __ldg(p.B + off);
+    if (p.Bmask != nullptr && !(__ldg(p.Bmask + off) > 0.f)) v = 0.f;
+    return v;
+  }
+};
+template <> struct BLoader<B_DENSE_T> {  // B_op[k,n] = B[n*ldb + k]
+  static constexpr bool kFast = true;
+  static __device__ __forceinline__ float load(const GemmParams& p, int k, int n) {
+    if (k >= p.K || n >= p.N) return 0.f;
+    return __ldg(p.B + (long)n * p.ldb + k);
+  }
+};
+template <> struct BLoader<B_WROT> {  // B_op[(kh,kw,co), ci] = W[kh,kw,ci,co]
+  static constexpr bool kFast = true;
+  static __device__ __forceinline__ float load(const GemmParams& p, int k, int n) {
+    if (k >= p.K || n >= p.N) return 0.f;
+    const int co = k % p.g.Cout; const int t = k / p.g.Cout;  // t = kh*KW + kw
+    return __ldg(p.B + ((long)t * p.g.C + n) * p.g.Cout + co);
+  }
+};
+
+// ------------------------------------------------------------------------------------------
+// The kernel. grid = (tiles_n, tiles_m, splits); 256 threads; each thread owns TM x TN outputs.
+// ------------------------------------------------------------------------------------------
+template <int AM, int BM_, int BMODE, int BN_, int TM, int TN>
+__global__ void __launch_bounds__(NTHREADS) gemm_fp32_kernel(const GemmParams p) {
+  static_assert((BM_ / TM) * (BN_ / TN) == NTHREADS, "tile/thread mismatch");
+  constexpr int APAD = 4;
+  __shared__ __align__(16) float As[BK][BM_ + APAD];
+  __shared__ __align__(16) float Bs[BK][BN_ + APAD];
+  __shared__ int s_last;
+
+  using AL = ALoader<AM>;
+  using BL = BLoader<BMODE>;
+  const int t = threadIdx.x;
+  const int m0 = blockIdx.y * BM_, n0 = blockIdx.x * BN_;
+  const int tx = t % (BN_ / TN), ty = t / (BN_ / TN);
+
+  // K range of this split (whole BK tiles)
+  const int ktiles = (p.K + BK - 1) / BK;
+  const int per = (ktiles + p.splits - 1) / p.splits;
+  const int kt0 = blockIdx.z * per;
+  const int kt1 = min(ktiles, kt0 + per);
+
+  constexpr int A_ELEMS = BM_ * BK / NTHREADS;
+  constexpr int B_ELEMS = BN_ * BK / NTHREADS;
+  static_assert(A_ELEMS >= 1 && B_ELEMS >= 1, "tile too small");
+
+  // Per-thread A rows are the same for every k tile: precompute them.
+  constexpr int A_ROWS = AL::kFast ? A_ELEMS : 1;
+  typename AL::Row arow[A_ROWS];
+  if (AL::kFast) {
+#pragma unroll
+    for (int i = 0; i < A_ROWS; ++i) arow[i] = AL::row(p, m0 + (t + i * NTHREADS) / BK);
+  } else {
+    arow[0] = AL::row(p, m0 + t % BM_);
+  }
+
+  float acc[TM][TN];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+
+  for (int kt = kt0; kt < kt1; ++kt) {
+    const int k0 = kt * BK;
+    float areg[A_ELEMS], breg[B_ELEMS];
+#pragma unroll
+    for (int i = 0; i < A_ELEMS; ++i) {
+      const int e = t + i * NTHREADS;
+      if (AL::kFast) areg[i] = AL::load(p, arow[i], m0 + e / BK, k0 + e % BK);
+      else           areg[i] = AL::load(p, arow[0], m0 + e % BM_, k0 + e / BM_);
+    }
+#pragma unroll
+    for (int i = 0; i < B_ELEMS; ++i) {
+      const int e = t + i * NTHREADS;
+      if (BL::kFast) breg[i] = BL::load(p, k0 + e % BK, n0 + e / BK);
+      else           breg[i] = BL::load(p, k0 + e / BN_, n0 + e % BN_);
+    }
+    __syncthreads();  // previous tile fully consumed
+#pragma unroll
+    for (int i = 0; i < A_ELEMS; ++i) {
+      const int e = t + i * NTHREADS;
+      if (AL::kFast) As[e % BK][e / BK] = areg[i];
+      else           As[e / BM_][e % BM_] = areg[i];
+    }
+#pragma unroll
+    for (int i = 0; i < B_ELEMS; ++i) {
+      const int e = t + i * NTHREADS;
+      if (BL::kFast) Bs[e % BK][e / BK] = breg[i];
+      else           Bs[e / BN_][e % BN_] = breg[i];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < BK; ++k) {
+      float a[TM], b[TN];
+#pragma unroll
+      for (int i = 0; i < TM; ++i) a[i] = As[k][ty * TM + i];
+#pragma unroll
+      for (int j = 0; j < TN; ++j) b[j] = Bs[k][tx * TN + j];
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+  }
+
+  if (p.splits > 1) {
+    // Deterministic split-K: every split stores its partial, the last block to finish a tile sums
+    // the partials in split order (independent of arrival order) and runs the epilogue.
+    float* mine = p.ws + (size_t)blockIdx.z * p.M * p.N;
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+      const int m = m0 + ty * TM + i;
+      if (m >= p.M) continue;
+#pragma unroll
+      for (int j = 0; j < TN; ++j) {
+        const int n = n0 + tx * TN + j;
+        if (n < p.N) __stcg(mine + (size_t)m * p.N + n, acc[i][j]);
+      }
+    }
+    __threadfence();
+    __syncthreads();
+    const unsigned tile = blockIdx.y * gridDim.x + blockIdx.x;
+    if (t == 0) {
+      const unsigned ticket = atomicAdd(p.counters + tile, 1u);
+      s_last = (ticket == (unsigned)p.splits - 1u);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+#pragma unroll
+    for (int i = 0; i < TM; ++i)
+#pragma unroll
+      for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+    for (int z = 0; z < p.splits; ++z) {
+      const float* part = p.ws + (size_t)z * p.M * p.N;
+#pragma unroll
+      for (int i = 0; i < TM; ++i) {
+        const int m = m0 + ty * TM + i;
+        if (m >= p.M) continue;
+#pragma unroll
+        for (int j = 0; j < TN; ++j) {
+          const int n = n0 + tx * TN + j;
+          if (n < p.N) acc[i][j] += __ldcg(part + (size_t)m * p.N + n);
+        }
+      }
+    }
+    if (t == 0) p.counters[tile] = 0u;  // self-cleaning for the next launch
+  }
+
+  // Epilogue: bias, ReLU, ones-row routing.
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    const int m = m0 + ty * TM + i;
+    if (m >= p.M) continue;
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      const int n = n0 + tx * TN + j;
+      if (n >= p.N) continue;
+      float v = acc[i][j];
+      if (m == p.ones_row) {
+        if (p.C2 != nullptr) p.C2[n] = v;
+        continue;
+      }
+      if (p.bias != nullptr) v += __ldg(p.bias + n);
+      if (p.relu) v = fmaxf(v, 0.f);
+      p.C[(size_t)m * p.ldc + n] = v;
+    }
+  }
+}
+
+template <int AM, int BMODE>
+int launch_cfg(const GemmParams& p, cudaStream_t stream) {
+  // Tile shape by N: the reference's layers have N in {6,10,12,24,32,64,200}.
+  if (p.N <= 16) {
+    dim3 grid((p.N + 15) / 16, (p.M + 255) / 256, p.splits);
+    gemm_fp32_kernel<AM, 256, BMODE, 16, 4, 4><<<grid, NTHREADS, 0, stream>>>(p);
+  } else if (p.N <= 32) {
+    dim3 grid((p.N + 31) / 32, (p.M + 127) / 128, p.splits);
+    gemm_fp32_kernel<AM, 128, BMODE, 32, 4, 4><<<grid, NTHREADS, 0, stream>>>(p);
+  } else {
+    dim3 grid((p.N + 63) / 64, (p.M + 63) / 64, p.splits);
+    gemm_fp32_kernel<AM, 64, BMODE, 64, 4, 4><<<grid, NTHREADS, 0, stream>>>(p);
+  }
+  TFDE_RETURN_LAUNCH_STATUS();
+}
+
+int tile_m_for(int N) { return N <= 16 ? 256 : (N <= 32 ? 128 : 64); }
+int tile_n_for(int N) { return N <= 16 ? 16 : (N <= 32 ? 32 : 64); }
+
+// Pick the split-K factor: fill ~2 CTAs per SM, keep >= 4 k-tiles per split, respect workspace.
+int choose_splits(int M, int N, int K, size_t ws_bytes, int max_tiles_counters) {
+  const int tiles = ((M + tile_m_for(N) - 1) / tile_m_for(N)) * ((N + tile_n_for(N) - 1) / tile_n_for(N));
+  if (tiles > max_tiles_counters) return 1;
+  const int ktiles = (K + BK - 1) / BK;
+  int s = min(ktiles / 4, (2 * 148) / max(tiles, 1));
+  s = max(1, min(s, 256));
+  const size_t per = (size_t)M * N * sizeof(float);
+  if (per == 0) return 1;
+  const size_t fit = ws_bytes / per;
+  if ((size_t)s > fit) s = (int)max((size_t)1, fit);
+  return s;
+}
+
+int dispatch(int amode, int bmode, const GemmParams& p, cudaStream_t s) {
+  if (p.M <= 0 || p.N <= 0) return 0;
+  if (amode == A_DENSE && bmode == B_DENSE) return launch_cfg<A_DENSE, B_DENSE>(p, s);
+  if (amode == A_DENSE_T && bmode == B_DENSE) return launch_cfg<A_DENSE_T, B_DENSE>(p, s);
+  if (amode == A_DENSE && bmode == B_DENSE_T) return launch_cfg<A_DENSE, B_DENSE_T>(p, s);
+  if (amode == A_IM2COL && bmode == B_DENSE) return launch_cfg<A_IM2COL, B_DENSE>(p, s);
+  if (amode == A_IM2COL_T && bmode == B_DENSE) return launch_cfg<A_IM2COL_T, B_DENSE>(p, s);
+  if (amode == A_DGRAD && bmode == B_WROT) return launch_cfg<A_DGRAD, B_WROT>(p, s);
+  return TFDE_ERR_INVALID;
+}
+
+constexpr int kMaxCounters = TFDE_MAX_COUNTERS;  // tickets available in the caller-provided counter buffer
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// C ABI (declarations with reference citations: include/tfde_kernels.h)
+// ---------------------------------------------------------------------------------------------
+
+// y[M,N] = act(x[M,K] . w[K,N] + bias)
+TFDE_API int tfde_dense_fwd(const float* x, const float* w, const float* bias, float* y, int M,
+                            int K, int N, int relu, float* ws, size_t ws_bytes,
+                            unsigned* counters, cudaStream_t stream) {
+  GemmParams p{};
+  p.A = x; p.lda = K; p.B = w; p.ldb = N; p.C = y; p.ldc = N; p.bias = bias;
+  p.M = M; p.N = N; p.K = K; p.ones_row = -1; p.relu = relu;
+  p.ws = ws; p.counters = counters;
+  p.splits = (ws && counters) ? choose_splits(M, N, K, ws_bytes, kMaxCounters) : 1;
+  return dispatch(A_DENSE, B_DENSE, p, stream);
+}
+
+// dw[K,N] = x[M,K]^T . (dy[M,N] * (ymask > 0));  db[N] = column sums (optional)
+TFDE_API int tfde_dense_wgrad(const float* x, const float* dy, const float* ymask, float* dw,
+                              float* db, int M, int K, int N, float* ws, size_t ws_bytes,
+                              unsigned* counters, cudaStream_t stream) {
+  GemmParams p{};
+  p.A = x; p.lda = K;               // A_op[k_in, m] = x[m*K + k_in]
+  p.B = dy; p.Bmask = ymask; p.ldb = N;
+  p.C = dw; p.ldc = N; p.C2 = db;
+  p.M = db ? K + 1 : K; p.N = N; p.K = M;
+  p.ones_row = db ? K : -1;
+  p.ws = ws; p.counters = counters;
+  p.splits = (ws && counters) ? choose_splits(p.M, N, M, ws_bytes, kMaxCounters) : 1;
+  return dispatch(A_DENSE_T, B_DENSE, p, stream);
+}
+
+// dx[M,K] = (dy[M,N] * (ymask > 0)) . w[K,N]^T
+TFDE_API int tfde_dense_dgrad(const float* dy, const float* ymask, const float* w, float* dx,
+                              int M, int K, int N, float* ws, size_t ws_bytes,
+                              unsigned* counters, cudaStream_t stream) {
+  GemmParams p{};
+  p.A = dy; p.Amask = ymask; p.lda = N;
+  p.B = w; p.ldb = N;               // B_op[n, k_in] = w[k_in*N + n]
+  p.C = dx; p.ldc = K;
+  p.M = M; p.N = K; p.K = N; p.ones_row = -1;
+  p.ws = ws; p.counters = counters;
+  p.splits = (ws && counters) ? choose_splits(M, K, N, ws_bytes, kMaxCounters) : 1;
+  return dispatch(A_DENSE, B_DENSE_T, p, stream);
+}
+
+static ConvGeom make_geom(int H, int W, int C, int KH, int KW, int Ho, int Wo, int sh, int sw,
+                          int pt, int pl, int Cout) {
+  ConvGeom g; g.H = H; g.W = W; g.C = C; g.KH = KH; g.KW = KW; g.Ho = Ho; g.Wo = Wo;
+  g.sh = sh; g.sw = sw; g.pt = pt; g.pl = pl; g.Cout = Cout;
+  return g;
+}
+
+// y[B,Ho,Wo,Cout] = act(conv(x[B,H,W,C], w[KH,KW,C,Cout]) + bias)
+TFDE_API int tfde_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int Bn,
+                             int H, int W, int C, int KH, int KW, int Ho, int Wo, int sh, int sw,
+                             int pt, int pl, int Cout, int relu, float* ws, size_t ws_bytes,
+                             unsigned* counters, cudaStream_t stream) {
+  GemmParams p{};
+  p.g = make_geom(H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout);
+  p.A = x; p.B = w; p.ldb = Cout; p.C = y; p.ldc = Cout; p.bias = bias;
+  p.M = Bn * Ho * Wo; p.N = Cout; p.K = KH * KW * C; p.ones_row = -1; p.relu = relu;
+  p.ws = ws; p.counters = counters;
+  p.splits = (ws && counters) ? choose_splits(p.M, p.N, p.K, ws_bytes, kMaxCounters) : 1;
+  return dispatch(A_IM2COL, B_DENSE, p, stream);
+}
+
+// dw[KH,KW,C,Cout] = im2col(x)^T . (dy * (ymask>0)); db optional
+TFDE_API int tfde_conv2d_wgrad(const float* x, const float* dy, const float* ymask, float* dw,
+                               float* db, int Bn, int H, int W, int C, int KH, int KW, int Ho,
+                               int Wo, int sh, int sw, int pt, int pl, int Cout, float* ws,
+                               size_t ws_bytes, unsigned* counters, cudaStream_t stream) {
+  GemmParams p{};
+  p.g = make_geom(H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout);
+  const int Kc = KH * KW * C;
+  p.A = x; p.B = dy; p.Bmask = ymask; p.ldb = Cout; p.C = dw; p.ldc = Cout; p.C2 = db;
+  p.M = db ? Kc + 1 : Kc; p.N = Cout; p.K = Bn * Ho * Wo; p.ones_row = db ? Kc : -1;
+  p.ws = ws; p.counters = counters;
+  p.splits = (ws && counters) ? choose_splits(p.M, p.N, p.K, ws_bytes, kMaxCounters) : 1;
+  return dispatch(A_IM2COL_T, B_DENSE, p, stream);
+}
+
+// dx[B,H,W,C] = gather(dy * (ymask>0)) . rot(w)
+TFDE_API int tfde_conv2d_dgrad(const float* dy, const float* ymask, const float* w, float* dx,
+                               int Bn, int H, int W, int C, int KH, int KW, int Ho, int Wo, int sh,
+                               int sw, int pt, int pl, int Cout, float* ws, size_t ws_bytes,
+                               unsigned* counters, cudaStream_t stream) {
+  GemmParams p{};
+  p.g = make_geom(H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout);
+  p.A = dy; p.Amask = ymask; p.B = w; p.C = dx; p.ldc = C;
+  p.M = Bn * H * W; p.N = C; p.K = KH * KW * Cout; p.ones_row = -1;
+  p.ws = ws; p.counters = counters;
+  p.splits = (ws && counters) ? choose_splits(p.M, p.N, p.K, ws_bytes, kMaxCounters) : 1;
+  return dispatch(A_DGRAD, B_WROT, p, stream);
+}
+
+TFDE_API int tfde_gemm_max_counters() { return kMaxCounters; }

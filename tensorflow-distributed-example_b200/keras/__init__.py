@@ -1,0 +1,21 @@
+"""tf.keras surface: Sequential, layers, losses, optimizers, callbacks, datasets."""
+from . import layers, losses, optimizers, callbacks  # noqa: F401
+from .models import Sequential, set_seed  # noqa: F401
+
+
+class datasets:  # tf.keras.datasets.mnist.load_data()
+    class mnist:
+        @staticmethod
+        def load_data(*a, **k):
+            from ..data.mnist import load_data
+            return load_data(*a, **k)
+
+
+class backend:
+    _learning_phase = None
+
+    @staticmethod
+    def set_learning_phase(value):
+        """tf.keras.backend.set_learning_phase (mnist_keras_distributed.py:116). Training/inference is an
+        explicit argument of every forward here, so this only records the value."""
+        backend._learning_phase = value

@@ -1,0 +1,541 @@
+"""Keras-like ``Sequential`` with ``compile / fit / evaluate / predict / summary`` and weight I/O.
+
+Reference surface: ``tf.keras.Sequential([...])`` + ``compile(loss, optimizer, metrics)`` +
+``fit(x, epochs, steps_per_epoch)`` (distributed_with_keras.py:33-43,63), ``model.summary()``
+(mnist_keras_distributed.py:117).
+
+Execution model (B200-first, no tracing compiler): ``build()`` lays every trainable variable into ONE
+flat fp32 parameter arena and every gradient into ONE flat gradient arena (what the fused
+all-reduce+optimizer kernel consumes in a single launch); a fusion pass merges Conv+ReLU+MaxPool and
+BN+ReLU into single kernels; the training step is a fixed sequence of hand-written kernels with static
+buffers, so after two eager warm-up steps the whole step (forward, loss, backward, cross-replica
+reduction, update, metric accumulation) is captured once in a CUDA graph and replayed with one launch.
+"""
+from __future__ import annotations
+
+import logging
+import os
+import time
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from .. import ops
+from ..parallel.comm import Arena
+from ..parallel.strategy import get_strategy
+from . import layers as L
+from . import losses as losses_mod
+from . import optimizers as opt_mod
+from .callbacks import CallbackList, History
+
+log = logging.getLogger("tfde_b200")
+
+_global_seed: Optional[int] = None
+
+
+def set_seed(seed: int):
+    """tf.random.set_seed analogue: makes initialisation and dropout reproducible."""
+    global _global_seed
+    _global_seed = int(seed)
+
+
+def _fresh_seed() -> int:
+    if _global_seed is not None:
+        return _global_seed
+    return int.from_bytes(os.urandom(4), "little")
+
+
+class _GraphState:
+    def __init__(self):
+        self.in_x = None
+        self.in_y = None
+        self.eager_steps = 0
+        self.graph = None
+
+
+class Sequential:
+    def __init__(self, layers: Optional[Sequence[L.Layer]] = None, name: Optional[str] = None,
+                 seed: Optional[int] = None):
+        self.name = name or "sequential"
+        self.strategy = get_strategy()
+        self.device = self.strategy.device
+        self.replica_id = self.strategy.replica_id
+        self.layers: List[L.Layer] = []
+        self.built = False
+        self.compiled = False
+        self.seed = _fresh_seed() if seed is None else int(seed)
+        self.arena: Optional[Arena] = None
+        self.state: Optional[torch.Tensor] = None     # non-trainable flat buffer (BN moving stats)
+        self.variables: List[L.Variable] = []
+        self.exec_plan: List[L.Layer] = []
+        self.loss = None
+        self.optimizer: Optional[opt_mod.Optimizer] = None
+        self.metrics_names: List[str] = ["loss"]
+        self.use_cuda_graph = os.environ.get("TFDE_CUDA_GRAPH", "1") == "1"
+        self.graph_warmup_steps = 2
+        self._graphs: Dict[tuple, _GraphState] = {}
+        self._stream = None
+        self._type_counts: Dict[str, int] = {}
+        self.stop_training = False
+        self.gpu_launches_per_step = 0
+        for l in layers or []:
+            self.add(l)
+
+    # ------------------------------------------------------------------------------------------
+    # construction
+    # ------------------------------------------------------------------------------------------
+    def add(self, layer: L.Layer):
+        if self.built:
+            raise RuntimeError("cannot add layers after the model was built")
+        if layer.name is None:
+            k = self._type_counts.get(layer._type_name, 0)
+            layer.name = layer._type_name if k == 0 else f"{layer._type_name}_{k}"
+            self._type_counts[layer._type_name] = k + 1
+        layer.model = self
+        self.layers.append(layer)
+        if len(self.layers) == 1 and layer.input_shape_arg is not None:
+            pass  # built lazily in build()/compile()
+        return self
+
+    @property
+    def hparams(self):
+        return self.optimizer.hparams if self.optimizer is not None else None
+
+    @property
+    def host_step(self) -> int:
+        return self.optimizer.iterations if self.optimizer is not None else 0
+
+    def build(self, input_shape=None):
+        """``input_shape`` excludes the batch dimension."""
+        if self.built:
+            return
+        if input_shape is None:
+            input_shape = self.layers[0].input_shape_arg if self.layers else None
+        if input_shape is None:
+            raise ValueError("the first layer needs input_shape=... (or call build(input_shape))")
+        shape = tuple(int(s) for s in input_shape)
+        self.input_shape = shape
+        first_weighted = True
+        for layer in self.layers:
+            shape = layer.build(shape)
+            if layer.variables and first_weighted:
+                layer.need_dx = False   # nothing upstream needs a data gradient
+                first_weighted = False
+            elif not first_weighted:
+                layer.need_dx = True
+        self.output_shape = shape
+        self.variables = [v for layer in self.layers for v in layer.variables]
+        self._allocate()
+        self._initialize()
+        self._fuse()
+        self.built = True
+
+    def _allocate(self):
+        def lay(vs):
+            off = 0
+            for v in vs:
+                v.offset = off
+                off += (v.size + 3) // 4 * 4   # 16-byte aligned slices (vector loads / TMA friendly)
+            return off
+
+        train = [v for v in self.variables if v.trainable]
+        frozen = [v for v in self.variables if not v.trainable]
+        n = lay(train)
+        m = lay(frozen)
+        comm = self.strategy.comm() if self.strategy.num_replicas_in_sync > 1 else None
+        self.arena = Arena(n, self.device, comm=comm)
+        self.state = torch.zeros(max(m, 4), dtype=torch.float32, device=self.device)
+        for v in train:
+            v.value = self.arena.w[v.offset:v.offset + v.size].view(v.shape)
+            v.grad = self.arena.g[v.offset:v.offset + v.size].view(v.shape)
+        for v in frozen:
+            v.value = self.state[v.offset:v.offset + v.size].view(v.shape)
+
+    def _initialize(self):
+        gen = torch.Generator(device="cpu")
+        gen.manual_seed(self.seed & 0x7FFFFFFFFFFFFFFF)
+        self.arena.w.zero_()
+        for v in self.variables:
+            v.value.copy_(v.initializer(v.shape, gen).to(self.device))
+        if self.strategy.num_replicas_in_sync > 1:
+            # initial values come from the chief (N3 / G13); also aligns the seed used by dropout
+            self.strategy.broadcast_(self.arena.w, src=0)
+            self.strategy.broadcast_(self.state, src=0)
+
+    def _fuse(self):
+        """Fusion pass: Conv2D(relu)+MaxPool(2x2) -> one kernel (first layer of Model A);
+        BatchNormalization + Activation('relu') -> BN with fused ReLU (Model B)."""
+        plan: List[L.Layer] = []
+        i = 0
+        ls = self.layers
+        allow = os.environ.get("TFDE_FUSION", "1") == "1"
+        while i < len(ls):
+            cur = ls[i]
+            nxt = ls[i + 1] if i + 1 < len(ls) else None
+            if allow and nxt is not None and L.FusedConvReluPool.matches(cur, nxt):
+                plan.append(L.FusedConvReluPool(cur, nxt))
+                i += 2
+                continue
+            if (allow and isinstance(cur, L.BatchNormalization) and isinstance(nxt, L.Activation)
+                    and nxt.activation == "relu"):
+                cur.fused_relu = True
+                nxt.fused_away = True
+            plan.append(cur)
+            i += 1
+        self.exec_plan = plan
+
+    # ------------------------------------------------------------------------------------------
+    # compile
+    # ------------------------------------------------------------------------------------------
+    def compile(self, optimizer="sgd", loss=None, metrics=None, **_ignored):
+        self.loss = losses_mod.get(loss)
+        self.optimizer = opt_mod.get(optimizer)
+        self.metrics_names = ["loss"]
+        for m in metrics or []:
+            if m in ("accuracy", "acc", "sparse_categorical_accuracy"):
+                self.metrics_names.append("accuracy")
+            else:
+                raise ValueError(f"unsupported metric {m!r}; the reference uses 'accuracy' only")
+        self.compiled = True
+        if self.layers and self.layers[0].input_shape_arg is not None and not self.built:
+            self.build()
+        if self.built:
+            self._bind_optimizer()
+
+    def _bind_optimizer(self):
+        if getattr(self.optimizer, "_bound_to", None) is self:
+            return
+        self.optimizer.bind(self.device, seed=self.seed, step=self.optimizer.iterations)
+        self.optimizer._bound_to = self
+        if self.strategy.num_replicas_in_sync > 1:
+            self.strategy.comm().prepare(self.arena, self.optimizer)
+        else:
+            self.optimizer.ensure_slots(self.arena)
+
+    # ------------------------------------------------------------------------------------------
+    # forward / backward
+    # ------------------------------------------------------------------------------------------
+    def _prep_input(self, x: torch.Tensor) -> torch.Tensor:
+        """Accepts [B,H,W], [B,H,W,C] or flat [B,prod] inputs (uint8 or float)."""
+        want = (x.shape[0],) + self.input_shape
+        if tuple(x.shape) != want:
+            n = 1
+            for s in self.input_shape:
+                n *= s
+            if x[0].numel() != n:
+                raise ValueError(f"input of shape {tuple(x.shape)} does not match model input {self.input_shape}")
+            x = x.reshape(want)
+        if x.dtype == torch.uint8:
+            first = self.exec_plan[0]
+            if not isinstance(first, L.FusedConvReluPool):
+                x = ops.u8_to_f32(x, 1.0 / 255.0, out=self._in_buf("x_f32", x.shape))
+        elif x.dtype != torch.float32:
+            x = x.to(torch.float32)
+        return x
+
+    def _in_buf(self, tag, shape, dtype=torch.float32):
+        key = ("__model__", tag, tuple(shape), dtype)
+        b = self._graphs.get(key)
+        if b is None:
+            b = torch.empty(tuple(shape), dtype=dtype, device=self.device)
+            self._graphs[key] = b
+        return b
+
+    def _forward(self, x, training: bool):
+        x = self._prep_input(x)
+        for node in self.exec_plan:
+            x = node.forward(x, training)
+        return x
+
+    def _backward(self, dy):
+        for node in reversed(self.exec_plan):
+            if dy is None:
+                break
+            dy = node.backward(dy)
+
+    def __call__(self, x, training=False):
+        if not self.built:
+            self.build(tuple(x.shape[1:]))
+        x = self._to_device(x)
+        return self._forward(x, training)
+
+    def _to_device(self, t, dtype=None):
+        if isinstance(t, np.ndarray):
+            t = torch.from_numpy(np.ascontiguousarray(t))
+        if dtype is not None and t.dtype != dtype:
+            t = t.to(dtype)
+        if t.device != self.device:
+            t = t.to(self.device, non_blocking=True)
+        return t.contiguous()
+
+    # ------------------------------------------------------------------------------------------
+    # the training step
+    # ------------------------------------------------------------------------------------------
+    def _step_body(self, x, y, global_batch: int):
+        """forward -> fused loss/grad/accuracy -> backward -> (cross-replica reduce +) optimizer."""
+        out = self._forward(x, True)
+        a = self.arena
+        dgrad = self._in_buf("dloss", out.shape)
+        ops.xent(out, y, 1.0 / float(global_batch), self.loss.from_probs, out_grad=dgrad, out4=a.grad_tail)
+        self._backward(dgrad)
+        if self.strategy.num_replicas_in_sync > 1:
+            self.strategy.comm().reduce_and_apply(a, self.optimizer)
+            self.optimizer.iterations += 1
+        else:
+            self.optimizer.apply_local(a)
+
+    def train_on_batch(self, x, y, global_batch: Optional[int] = None):
+        """One optimizer step on this replica's slice of the global batch. Returns nothing (metrics are
+        accumulated on device; read them with ``read_metrics()``) so no host sync is forced per step."""
+        if not self.compiled:
+            raise RuntimeError("compile() the model first")
+        if not self.built:
+            self.build(tuple(x.shape[1:]))
+            self._bind_optimizer()
+        elif getattr(self.optimizer, "_bound_to", None) is not self:
+            self._bind_optimizer()
+        b = int(x.shape[0])
+        gb = global_batch if global_batch is not None else b * self.strategy.num_replicas_in_sync
+        if self.device.type != "cuda":
+            xd = self._to_device(x)
+            yd = self._to_device(y).reshape(-1).long()
+            self._step_body(xd, yd, gb)
+            return
+        if self._stream is None:
+            self._stream = torch.cuda.Stream(device=self.device)
+            ops.native.Workspace.current(self.device)
+        key = (b, tuple(x.shape[1:]), str(x.dtype), gb)
+        st = self._graphs.get(key)
+        if st is None:
+            st = _GraphState()
+            xdtype = x.dtype if isinstance(x, torch.Tensor) else torch.from_numpy(x).dtype
+            if xdtype not in (torch.uint8, torch.float32):
+                xdtype = torch.float32
+            st.in_x = torch.empty((b,) + tuple(x.shape[1:]), dtype=xdtype, device=self.device)
+            st.in_y = torch.empty((b,), dtype=torch.int64, device=self.device)
+            self._graphs[key] = st
+        if isinstance(x, np.ndarray):
+            x = torch.from_numpy(x)
+        if isinstance(y, np.ndarray):
+            y = torch.from_numpy(y)
+        with torch.cuda.stream(self._stream):
+            ops.native.Workspace.current(self.device)
+            st.in_x.copy_(x if x.dtype == st.in_x.dtype else x.to(st.in_x.dtype), non_blocking=True)
+            yy = y.reshape(-1)
+            st.in_y.copy_(yy if yy.dtype == torch.int64 else yy.to(torch.int64), non_blocking=True)
+            if st.graph is not None:
+                st.graph.replay()
+                self.optimizer.iterations += 1
+            elif not self.use_cuda_graph or st.eager_steps < self.graph_warmup_steps:
+                self._step_body(st.in_x, st.in_y, gb)
+                st.eager_steps += 1
+            else:
+                it0 = self.optimizer.iterations
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=self._stream):
+                    self._step_body(st.in_x, st.in_y, gb)
+                self.optimizer.iterations = it0   # capture did not execute anything
+                st.graph = g
+                g.replay()
+                self.optimizer.iterations += 1
+
+    def sync(self):
+        if self.device.type == "cuda":
+            if self._stream is not None:
+                self._stream.synchronize()
+            else:
+                torch.cuda.synchronize(self.device)
+
+    def read_metrics(self, steps: int, reset=True) -> Dict[str, float]:
+        """Host read of the device-side running sums accumulated since the last reset (one sync)."""
+        self.sync()
+        m = self.arena.metrics.detach().cpu().tolist()
+        if self.strategy.num_replicas_in_sync > 1:
+            self.strategy.comm().check_health()
+        out = {"loss": m[0] / max(steps, 1)}
+        if "accuracy" in self.metrics_names:
+            out["accuracy"] = m[1] / max(m[2], 1.0)
+        if reset:
+            if self._stream is not None:
+                with torch.cuda.stream(self._stream):
+                    self.arena.metrics.zero_()
+            else:
+                self.arena.metrics.zero_()
+        return out
+
+    def last_step_loss(self) -> float:
+        """Loss of the most recent step (global mean); forces a device->host read."""
+        self.sync()
+        return float(self.arena.tail[0].item())
+
+    # ------------------------------------------------------------------------------------------
+    # fit / evaluate / predict
+    # ------------------------------------------------------------------------------------------
+    def fit(self, x=None, y=None, batch_size=None, epochs=1, steps_per_epoch=None, callbacks=None,
+            verbose=1, validation_data=None, initial_epoch=0, shuffle=True):
+        from ..data.dataset import Dataset, DistributedDataset, as_distributed
+        if not self.compiled:
+            raise RuntimeError("compile() the model first")
+        if not isinstance(x, (Dataset, DistributedDataset)):
+            if y is None:
+                raise ValueError("fit(x, y): y is required when x is an array")
+            n_rep = self.strategy.num_replicas_in_sync
+            gbs = (batch_size or 32) * 1
+            ds = Dataset.from_tensor_slices((np.asarray(x), np.asarray(y)))
+            if shuffle:
+                ds = ds.shuffle(min(len(x), 10000), seed=self.seed)
+            x = ds.batch(gbs)
+            del n_rep
+        dist_ds = as_distributed(x, self.strategy)
+        history = History()
+        cbs = CallbackList([history] + list(callbacks or []), self)
+        self.stop_training = False
+        cbs.on_train_begin()
+        it = iter(dist_ds)
+        chief_verbose = verbose and self.strategy.is_chief
+        for epoch in range(initial_epoch, epochs):
+            cbs.on_epoch_begin(epoch)
+            t0 = time.time()
+            steps = 0
+            while steps_per_epoch is None or steps < steps_per_epoch:
+                try:
+                    xb, yb, gb = next(it)
+                except StopIteration:
+                    if steps_per_epoch is None:
+                        it = iter(dist_ds)   # next epoch restarts the dataset
+                        break
+                    if steps == 0 and epoch > initial_epoch:
+                        it = iter(dist_ds)
+                        continue
+                    log.warning("input ran out of data after %d steps of epoch %d", steps, epoch + 1)
+                    self.stop_training = True
+                    break
+                cbs.on_train_batch_begin(steps)
+                self.train_on_batch(xb, yb, global_batch=gb)
+                steps += 1
+                cbs.on_train_batch_end(steps - 1)
+            logs = self.read_metrics(steps)
+            dt = time.time() - t0
+            if validation_data is not None:
+                val = self.evaluate(*validation_data, batch_size=batch_size, verbose=0, return_dict=True)
+                logs.update({f"val_{k}": v for k, v in val.items()})
+            if chief_verbose:
+                extra = " - ".join(f"{k}: {v:.4f}" for k, v in logs.items())
+                print(f"Epoch {epoch + 1}/{epochs}\n{steps}/{steps} - {dt:.2f}s - "
+                      f"{1e3 * dt / max(steps, 1):.2f}ms/step - {extra}", flush=True)
+            cbs.on_epoch_end(epoch, logs)
+            if self.stop_training:
+                break
+        cbs.on_train_end()
+        return history
+
+    def evaluate(self, x=None, y=None, batch_size=None, steps=None, verbose=0, return_dict=False):
+        """Distributed evaluation (the MirroredStrategy eval of mnist_keras_distributed.py:243): each
+        replica scores its slice of every batch; (loss_sum, correct, count) are SUM-reduced (G14)."""
+        from ..data.dataset import Dataset, DistributedDataset, as_distributed
+        if not isinstance(x, (Dataset, DistributedDataset)):
+            ds = Dataset.from_tensor_slices((np.asarray(x), np.asarray(y))).batch(batch_size or 32)
+            x = ds
+        dist_ds = as_distributed(x, self.strategy, for_eval=True)
+        tot = torch.zeros(4, dtype=torch.float64)
+        n_steps = 0
+        for xb, yb, gb in dist_ds:
+            if steps is not None and n_steps >= steps:
+                break
+            if xb.shape[0] > 0:
+                xd = self._to_device(xb)
+                yd = self._to_device(yb).reshape(-1).long()
+                if not self.built:
+                    self.build(tuple(xd.shape[1:]))
+                out = self._forward(xd, False)
+                o4, _ = ops.xent(out, yd, 1.0, self.loss.from_probs if self.loss else False,
+                                 out_grad=self._in_buf("dloss_eval", out.shape))
+                tot += o4.detach().to("cpu", torch.float64)
+            n_steps += 1
+        red = tot.to(torch.float32).to(self.device)
+        self.strategy.all_reduce_sum_(red)
+        r = red.cpu().tolist()
+        count = max(r[2], 1.0)
+        res = {"loss": r[0] / count}
+        if "accuracy" in self.metrics_names or not self.compiled:
+            res["accuracy"] = r[1] / count
+        if verbose and self.strategy.is_chief:
+            print(" - ".join(f"{k}: {v:.4f}" for k, v in res.items()), flush=True)
+        return res if return_dict else [res[k] for k in res]
+
+    def predict(self, x, batch_size=32):
+        xs = np.asarray(x) if not isinstance(x, torch.Tensor) else x
+        outs = []
+        for i in range(0, len(xs), batch_size):
+            xb = self._to_device(xs[i:i + batch_size])
+            if not self.built:
+                self.build(tuple(xb.shape[1:]))
+            outs.append(self._forward(xb, False).detach().cpu().clone())
+        return torch.cat(outs, 0).numpy()
+
+    # ------------------------------------------------------------------------------------------
+    # introspection / weights
+    # ------------------------------------------------------------------------------------------
+    def count_params(self):
+        return sum(v.size for v in self.variables)
+
+    def summary(self, print_fn=print):
+        if not self.built:
+            self.build()
+        lines = [f'Model: "{self.name}"', "_" * 65,
+                 f"{'Layer (type)':<29}{'Output Shape':<26}{'Param #':<10}", "=" * 65]
+        for l in self.layers:
+            shape = "(None, " + ", ".join(str(s) for s in l.out_shape) + ")"
+            lines.append(f"{(l.name + ' (' + type(l).__name__ + ')'):<29}{shape:<26}{l.count_params():<10}")
+            lines.append("_" * 65)
+        train = sum(v.size for v in self.variables if v.trainable)
+        total = self.count_params()
+        lines[-1] = "=" * 65
+        lines += [f"Total params: {total:,}", f"Trainable params: {train:,}",
+                  f"Non-trainable params: {total - train:,}", "_" * 65]
+        text = "\n".join(lines)
+        print_fn(text)
+        return text
+
+    @property
+    def trainable_variables(self):
+        return [v for v in self.variables if v.trainable]
+
+    @property
+    def non_trainable_variables(self):
+        return [v for v in self.variables if not v.trainable]
+
+    def get_weights(self) -> List[np.ndarray]:
+        """Keras order: per layer, in creation order (kernel, bias | gamma, beta, moving_mean, moving_variance)."""
+        self.sync()
+        return [v.numpy() for v in self.variables]
+
+    def set_weights(self, weights: Sequence[np.ndarray]):
+        if len(weights) != len(self.variables):
+            raise ValueError(f"expected {len(self.variables)} arrays, got {len(weights)}")
+        for v, w in zip(self.variables, weights):
+            w = np.asarray(w, dtype=np.float32)
+            if tuple(w.shape) != v.shape:
+                raise ValueError(f"{v.name}: expected shape {v.shape}, got {w.shape}")
+            v.value.copy_(torch.from_numpy(w).to(self.device))
+
+    def named_weights(self) -> Dict[str, np.ndarray]:
+        self.sync()
+        return {v.name: v.numpy() for v in self.variables}
+
+    def save_weights(self, path: str):
+        from ..ckpt.checkpoint import save_weights
+        save_weights(self, path)
+
+    def load_weights(self, path: str):
+        from ..ckpt.checkpoint import load_weights
+        load_weights(self, path)
+
+    def invalidate_graphs(self):
+        """Drop captured CUDA graphs (e.g. after set_weights changed nothing address-wise this is not
+        needed; it is needed only if buffers were re-allocated)."""
+        for k, v in list(self._graphs.items()):
+            if isinstance(v, _GraphState):
+                v.graph = None
+                v.eager_steps = 0
