@@ -13,6 +13,8 @@ views of the model's flat gradient arena, which is what the fused all-reduce con
 """
 from __future__ import annotations
 
+import functools
+import inspect
 import math
 from typing import List, Optional, Sequence, Tuple
 
@@ -78,6 +80,34 @@ class Layer:
     _type_name = "layer"
     has_relu_output = False  # set by fusion pass consumers
 
+    def __init_subclass__(cls, **kw):
+        """Records the constructor arguments of every layer so get_config()/layer_from_config() can
+        rebuild it (used by the serving export)."""
+        super().__init_subclass__(**kw)
+        orig = cls.__init__
+        if getattr(orig, "_records_config", False):
+            return
+        sig = inspect.signature(orig)
+
+        @functools.wraps(orig)
+        def init(self, *a, **k):
+            if not hasattr(self, "_ctor_config"):
+                try:
+                    ba = sig.bind(self, *a, **k)
+                    cfg = {}
+                    for n, v in list(ba.arguments.items())[1:]:
+                        if sig.parameters[n].kind is inspect.Parameter.VAR_KEYWORD:
+                            cfg.update(v)
+                        else:
+                            cfg[n] = v
+                    self._ctor_config = cfg
+                except TypeError:
+                    self._ctor_config = {}
+            orig(self, *a, **k)
+
+        init._records_config = True
+        cls.__init__ = init
+
     def __init__(self, name: Optional[str] = None, input_shape=None, **_ignored):
         self.name = name
         self.input_shape_arg = tuple(input_shape) if input_shape is not None else None
@@ -127,7 +157,11 @@ class Layer:
         raise NotImplementedError
 
     def get_config(self):
-        return {"name": self.name}
+        cfg = {}
+        for k, v in getattr(self, "_ctor_config", {}).items():
+            cfg[k] = list(v) if isinstance(v, tuple) else v
+        cfg["name"] = self.name
+        return cfg
 
 
 class InputLayer(Layer):
@@ -392,8 +426,7 @@ class Dropout(Layer):
         super().__init__(**kw)
         self.rate = float(rate)
         self.seed = seed
-        self.stream_id = Dropout._next_stream
-        Dropout._next_stream += 1
+        self.stream_id = 1   # Sequential.add() replaces it with the layer's position in the model
 
     def forward(self, x, training):
         self._training = training
@@ -461,3 +494,16 @@ class FusedConvReluPool(Layer):
         ops.conv_relu_pool_bwd(self._x, self.conv.kernel.value, self._y, self._idx, dy, self.in_scale,
                                out_dw=self.conv.kernel.grad, out_db=self.conv.bias.grad)
         return None
+
+
+def layer_from_config(class_name: str, config: dict) -> Layer:
+    """Inverse of ``Layer.get_config`` for the layers a Sequential can hold."""
+    table = {c.__name__: c for c in (InputLayer, Conv2D, MaxPooling2D, Flatten, Reshape, Dense,
+                                     BatchNormalization, Activation, Dropout, GlobalAveragePooling2D)}
+    if class_name not in table:
+        raise ValueError(f"unknown layer class {class_name!r}")
+    cfg = dict(config)
+    for k in ("input_shape", "target_shape", "kernel_size", "strides", "pool_size"):
+        if isinstance(cfg.get(k), list):
+            cfg[k] = tuple(cfg[k])
+    return table[class_name](**cfg)

@@ -93,6 +93,8 @@ class Sequential:
             layer.name = layer._type_name if k == 0 else f"{layer._type_name}_{k}"
             self._type_counts[layer._type_name] = k + 1
         layer.model = self
+        if isinstance(layer, L.Dropout):
+            layer.stream_id = len(self.layers) + 1   # RNG stream = position in the model (deterministic)
         self.layers.append(layer)
         if len(self.layers) == 1 and layer.input_shape_arg is not None:
             pass  # built lazily in build()/compile()
