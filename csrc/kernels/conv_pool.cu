@@ -77,23 +77,33 @@ conv3x3c1_relu_pool_bwd_kernel(const void* __restrict__ xin, const float* __rest
 #pragma unroll
   for (int i = 0; i < 10; ++i) acc[i] = 0.f;
   const long total = (long)Bn * PH * PW;
-  for (long p = (long)blockIdx.x * WARPS + warp; p < total; p += (long)gridDim.x * WARPS) {
+  const long stride = (long)gridDim.x * WARPS;
+  // Software-pipelined: the loads of pixel p+stride are issued before pixel p is consumed.
+  auto fetch = [&](long p, float& xv, float& g, int& bsel) {
+    xv = 0.f; g = 0.f; bsel = 0;
+    if (p >= total) return;
     const int pw = (int)(p % PW);
     const long t = p / PW;
     const int ph = (int)(t % PH);
     const long bi = t / PH;
-    __syncwarp();
     if (lane < 16) {
       const long off = (bi * H + (2 * ph + (lane >> 2))) * W + (2 * pw + (lane & 3));
-      float v;
-      if (U8) v = (float)__ldg(reinterpret_cast<const uint8_t*>(xin) + off) * in_scale;
-      else    v = __ldg(reinterpret_cast<const float*>(xin) + off);
-      s_patch[warp][lane] = v;
+      if (U8) xv = (float)__ldg(reinterpret_cast<const uint8_t*>(xin) + off) * in_scale;
+      else    xv = __ldg(reinterpret_cast<const float*>(xin) + off);
     }
-    __syncwarp();
-    float g = __ldg(dpooled + p * 32 + lane);
+    g = __ldg(dpooled + p * 32 + lane);
     if (!(__ldg(pooled + p * 32 + lane) > 0.f)) g = 0.f;
-    const int bsel = idx[p * 32 + lane];
+    bsel = idx[p * 32 + lane];
+  };
+  float xv_n, g_n; int b_n;
+  long p = (long)blockIdx.x * WARPS + warp;
+  fetch(p, xv_n, g_n, b_n);
+  for (; p < total; p += stride) {
+    const float xv = xv_n, g = g_n; const int bsel = b_n;
+    fetch(p + stride, xv_n, g_n, b_n);
+    __syncwarp();
+    if (lane < 16) s_patch[warp][lane] = xv;
+    __syncwarp();
     const int dy = bsel >> 1, dx = bsel & 1;
 #pragma unroll
     for (int kh = 0; kh < 3; ++kh)
@@ -121,7 +131,14 @@ conv3x3c1_relu_pool_bwd_kernel(const void* __restrict__ xin, const float* __rest
   __threadfence();
   for (int e = threadIdx.x; e < 320; e += blockDim.x) {
     float s = 0.f;
-    for (unsigned blk = 0; blk < gridDim.x; ++blk) s += __ldcg(partials + (size_t)blk * 320 + e);
+    for (unsigned b0 = 0; b0 < gridDim.x; b0 += 8) {   // 8 loads in flight, summed in block order
+      float v[8];
+#pragma unroll
+      for (unsigned j = 0; j < 8; ++j)
+        v[j] = (b0 + j < gridDim.x) ? __ldcg(partials + (size_t)(b0 + j) * 320 + e) : 0.f;
+#pragma unroll
+      for (unsigned j = 0; j < 8; ++j) s += v[j];
+    }
     if (e < 288) dw[e] = s;          // [kh][kw][ci=0][co]  == e = (kh*3+kw)*32 + co
     else if (db != nullptr) db[e - 288] = s;
   }
@@ -160,9 +177,9 @@ TFDE_API int tfde_conv3x3c1_relu_pool_bwd(const void* x, int x_is_u8, float in_s
                                           int Cout, cudaStream_t stream) {
   if (Cout != 32 || H < 4 || W < 4) return TFDE_ERR_INVALID;
   const int PH = (H - 2) / 2, PW = (W - 2) / 2;
-  long blocks = ((long)Bn * PH * PW + WARPS * 16 - 1) / (WARPS * 16);  // >= 16 pixels per warp
+  long blocks = ((long)Bn * PH * PW + WARPS * 8 - 1) / (WARPS * 8);  // >= 8 pixels per warp
   if (blocks < 1) blocks = 1;
-  if (blocks > 148L * 2) blocks = 148L * 2;
+  if (blocks > 148L) blocks = 148L;
   const int grid = (int)blocks;
   if (x_is_u8)
     conv3x3c1_relu_pool_bwd_kernel<true><<<grid, WARPS * 32, 0, stream>>>(x, pooled, idx, dpooled, dw, db, partials, counter, Bn, H, W, PH, PW, in_scale);

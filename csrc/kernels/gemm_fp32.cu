@@ -12,6 +12,7 @@
 //   G5 dense wgrad   dW = x^T . dy (+db as ones row), dense dgrad dx = dy . W^T
 // ReLU backward never runs as its own kernel: the loaders multiply dy by (y > 0) on the fly (G8).
 #include "common.cuh"
+#include <cmath>
 
 namespace {
 
@@ -219,9 +220,12 @@ __global__ void __launch_bounds__(NTHREADS) gemm_fp32_kernel(const GemmParams p)
 #pragma unroll
     for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
 
-  for (int kt = kt0; kt < kt1; ++kt) {
+  // Software pipeline: the global loads of tile kt+1 are in flight while tile kt is multiplied out of
+  // shared memory (these GEMMs have only a handful of k tiles per CTA, so exposed load latency -- not
+  // FLOPs -- is what the step pays for).
+  float areg[A_ELEMS], breg[B_ELEMS];
+  auto load_tile = [&](int kt) {
     const int k0 = kt * BK;
-    float areg[A_ELEMS], breg[B_ELEMS];
 #pragma unroll
     for (int i = 0; i < A_ELEMS; ++i) {
       const int e = t + i * NTHREADS;
@@ -234,6 +238,9 @@ __global__ void __launch_bounds__(NTHREADS) gemm_fp32_kernel(const GemmParams p)
       if (BL::kFast) breg[i] = BL::load(p, k0 + e % BK, n0 + e / BK);
       else           breg[i] = BL::load(p, k0 + e / BN_, n0 + e % BN_);
     }
+  };
+  if (kt0 < kt1) load_tile(kt0);
+  for (int kt = kt0; kt < kt1; ++kt) {
     __syncthreads();  // previous tile fully consumed
 #pragma unroll
     for (int i = 0; i < A_ELEMS; ++i) {
@@ -248,6 +255,7 @@ __global__ void __launch_bounds__(NTHREADS) gemm_fp32_kernel(const GemmParams p)
       else           Bs[e / BN_][e % BN_] = breg[i];
     }
     __syncthreads();
+    if (kt + 1 < kt1) load_tile(kt + 1);
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
       float a[TM], b[TN];
@@ -264,17 +272,21 @@ __global__ void __launch_bounds__(NTHREADS) gemm_fp32_kernel(const GemmParams p)
 
   if (p.splits > 1) {
     // Deterministic split-K: every split stores its partial, the last block to finish a tile sums
-    // the partials in split order (independent of arrival order) and runs the epilogue.
-    float* mine = p.ws + (size_t)blockIdx.z * p.M * p.N;
+    // the partials in split order (independent of arrival order) and runs the epilogue. Partials are
+    // stored with a leading dimension padded to 4 so both sides use 16-byte accesses, and the
+    // reduction keeps 4 splits x TM float4 loads in flight per thread (L2 latency, not bandwidth,
+    // bounds it).
+    static_assert(TN == 4, "split-K partial layout assumes 4 columns per thread");
+    const int ldw = (p.N + 3) & ~3;
+    const size_t zstride = (size_t)p.M * ldw;
+    float* mine = p.ws + (size_t)blockIdx.z * zstride;
+    const int ncol = n0 + tx * TN;
 #pragma unroll
     for (int i = 0; i < TM; ++i) {
       const int m = m0 + ty * TM + i;
-      if (m >= p.M) continue;
-#pragma unroll
-      for (int j = 0; j < TN; ++j) {
-        const int n = n0 + tx * TN + j;
-        if (n < p.N) __stcg(mine + (size_t)m * p.N + n, acc[i][j]);
-      }
+      if (m < p.M && ncol < ldw)
+        __stcg(reinterpret_cast<float4*>(mine + (size_t)m * ldw + ncol),
+               make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
     }
     __threadfence();
     __syncthreads();
@@ -290,17 +302,27 @@ __global__ void __launch_bounds__(NTHREADS) gemm_fp32_kernel(const GemmParams p)
     for (int i = 0; i < TM; ++i)
 #pragma unroll
       for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
-    for (int z = 0; z < p.splits; ++z) {
-      const float* part = p.ws + (size_t)z * p.M * p.N;
+    if (ncol < ldw) {
+      constexpr int ZU = 4;
+      for (int z0 = 0; z0 < p.splits; z0 += ZU) {
+        float4 v[ZU][TM];
 #pragma unroll
-      for (int i = 0; i < TM; ++i) {
-        const int m = m0 + ty * TM + i;
-        if (m >= p.M) continue;
+        for (int u = 0; u < ZU; ++u) {
+          const float* part = p.ws + (size_t)(z0 + u) * zstride;
 #pragma unroll
-        for (int j = 0; j < TN; ++j) {
-          const int n = n0 + tx * TN + j;
-          if (n < p.N) acc[i][j] += __ldcg(part + (size_t)m * p.N + n);
+          for (int i = 0; i < TM; ++i) {
+            const int m = m0 + ty * TM + i;
+            v[u][i] = (z0 + u < p.splits && m < p.M)
+                          ? __ldcg(reinterpret_cast<const float4*>(part + (size_t)m * ldw + ncol))
+                          : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
         }
+#pragma unroll
+        for (int u = 0; u < ZU; ++u)   // fixed z order => bit-reproducible
+#pragma unroll
+          for (int i = 0; i < TM; ++i) {
+            acc[i][0] += v[u][i].x; acc[i][1] += v[u][i].y; acc[i][2] += v[u][i].z; acc[i][3] += v[u][i].w;
+          }
       }
     }
     if (t == 0) p.counters[tile] = 0u;  // self-cleaning for the next launch
@@ -351,9 +373,12 @@ int choose_splits(int M, int N, int K, size_t ws_bytes, int max_tiles_counters) 
   const int tiles = ((M + tile_m_for(N) - 1) / tile_m_for(N)) * ((N + tile_n_for(N) - 1) / tile_n_for(N));
   if (tiles > max_tiles_counters) return 1;
   const int ktiles = (K + BK - 1) / BK;
-  int s = min(ktiles / 4, (2 * 148) / max(tiles, 1));
-  s = max(1, min(s, 256));
-  const size_t per = (size_t)M * N * sizeof(float);
+  // exposed-latency model: main loop ~ (ktiles/s) dependent tile loads, reduction ~ s/4 dependent L2
+  // round trips  =>  s ~ 2*sqrt(ktiles), capped by the SM count and by >= 2 k-tiles per split.
+  int s = (int)(2.0 * sqrt((double)ktiles) + 0.5);
+  s = min(s, min(ktiles / 2, (2 * 148) / max(tiles, 1)));
+  s = max(1, min(s, 128));
+  const size_t per = (size_t)M * ((N + 3) & ~3) * sizeof(float);
   if (per == 0) return 1;
   const size_t fit = ws_bytes / per;
   if ((size_t)s > fit) s = (int)max((size_t)1, fit);

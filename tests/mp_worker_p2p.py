@@ -1,0 +1,223 @@
+"""Multi-GPU worker (launched by torchrun, one rank per GPU): validates the fused peer-to-peer
+all-reduce + optimizer kernel against a gathered fp64 host reference, checks that replicas stay
+bit-identical, that the CUDA-graph-captured distributed step equals the eager one, and prints an
+all-reduce bandwidth sweep. Exit code 0 == all checks passed on every rank."""
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+import tfde_b200 as tf
+from tfde_b200.keras import optimizers as O
+from tfde_b200.ops import native, reference as ref
+from tfde_b200.parallel.comm import Arena
+
+
+def gather_cpu(t):
+    parts = [None] * dist.get_world_size()
+    dist.all_gather_object(parts, t.detach().cpu().numpy())
+    return parts
+
+
+def check_fused(strategy, n, opt_name, mode, steps=3, wire_bf16=False):
+    os.environ["TFDE_AR_MODE"] = mode
+    comm = strategy.comm()
+    comm.wire_bf16 = wire_bf16
+    rank, world = strategy.rank, strategy.world_size
+    mk = {"sgd": lambda: O.SGD(0.1), "momentum": lambda: O.SGD(0.1, momentum=0.9),
+          "adam": lambda: O.Adam(0.01)}[opt_name]
+    opt = mk().bind(strategy.device, seed=1)
+    arena = Arena(n, strategy.device, comm=comm)
+    g = torch.Generator().manual_seed(1234)
+    w0 = torch.randn(n, generator=g)
+    arena.w[:n] = w0.to(strategy.device)
+    comm.prepare(arena, opt)
+    # fp64 reference on the host
+    w_ref = w0.double().clone()
+    s1 = torch.zeros(n, dtype=torch.float64)
+    s2 = torch.zeros(n, dtype=torch.float64)
+    ok = True
+    for step in range(steps):
+        gl = torch.Generator().manual_seed(100 * step + rank)
+        grad = torch.randn(n, generator=gl)
+        arena.g[:n] = grad.to(strategy.device)
+        arena.g[n:n + 4] = torch.tensor([0.25 * (rank + 1), float(rank), 64.0, 0.0], device=strategy.device)
+        comm.reduce_and_apply(arena, opt)
+        opt.iterations += 1
+        torch.cuda.synchronize()
+        comm.check_health()
+        grads = gather_cpu(grad)
+        if wire_bf16:
+            grads = [torch.from_numpy(x).bfloat16().float().numpy() for x in grads]
+        gsum = torch.from_numpy(np.sum(np.stack(grads).astype(np.float64), axis=0))
+        if opt_name == "sgd":
+            w_ref = ref.sgd_update(w_ref, gsum, 0.1)
+        elif opt_name == "momentum":
+            w_ref, s1 = ref.momentum_update(w_ref, gsum, s1, 0.1, 0.9)
+        else:
+            w_ref, s1, s2 = ref.adam_update(w_ref, gsum, s1, s2, 0.01, 0.9, 0.999, 1e-7, step + 1)
+        got = arena.w[:n].cpu().double()
+        err = (got - w_ref).abs().max().item()
+        tol = 2e-4 if opt_name != "adam" else 2e-3
+        if wire_bf16:
+            tol *= 4
+        if not err <= tol * max(1.0, w_ref.abs().max().item()):
+            print(f"[rank {rank}] FAIL n={n} opt={opt_name} mode={mode} step={step} err={err:.3e}", flush=True)
+            ok = False
+        tail = arena.tail.cpu().tolist()
+        exp0 = sum(0.25 * (r + 1) for r in range(world))
+        if abs(tail[0] - exp0) > 1e-5 or abs(tail[2] - 64.0 * world) > 1e-3:
+            print(f"[rank {rank}] FAIL tail {tail} expected loss {exp0}", flush=True)
+            ok = False
+    # replicas bit-identical
+    ws = gather_cpu(arena.w[:n])
+    if not all(np.array_equal(ws[0], x) for x in ws[1:]):
+        print(f"[rank {rank}] FAIL replicas differ n={n} opt={opt_name} mode={mode}", flush=True)
+        ok = False
+    m = arena.metrics.cpu().tolist()
+    if abs(m[2] - 64.0 * world * steps) > 1e-2:
+        print(f"[rank {rank}] FAIL metrics {m}", flush=True)
+        ok = False
+    if native.hparams_get(opt.hparams)["step"] != steps:
+        print(f"[rank {rank}] FAIL device step {native.hparams_get(opt.hparams)['step']} != {steps}", flush=True)
+        ok = False
+    return ok
+
+
+def check_model(strategy, graph):
+    """2+ replicas, fixed data: weights identical across ranks and equal to a single-process CPU run on
+    the concatenated (global) batch."""
+    rank, world = strategy.rank, strategy.world_size
+    os.environ.pop("TFDE_AR_MODE", None)
+    with strategy.scope():
+        m = tf.models.build_and_compile_cnn_model(learning_rate=0.05, seed=21)
+    m.use_cuda_graph = graph
+    g = torch.Generator().manual_seed(5)
+    B = 32
+    X = torch.rand(6, world * B, 28, 28, 1, generator=g)
+    Y = torch.randint(0, 10, (6, world * B), generator=g)
+    losses = []
+    for s in range(6):
+        m.train_on_batch(X[s, rank * B:(rank + 1) * B], Y[s, rank * B:(rank + 1) * B], global_batch=world * B)
+        losses.append(m.last_step_loss())
+    strategy.comm().check_health()
+    from tfde_b200.parallel.strategy import Strategy
+    with Strategy(device="cpu").scope():
+        mc = tf.models.build_and_compile_cnn_model(learning_rate=0.05, seed=21)
+    lc = []
+    for s in range(6):
+        mc.train_on_batch(X[s], Y[s])
+        lc.append(mc.last_step_loss())
+    ok = np.allclose(losses, lc, rtol=2e-3, atol=2e-4)
+    if not ok:
+        print(f"[rank {rank}] FAIL model losses {losses} vs cpu {lc}", flush=True)
+    ws = gather_cpu(m.arena.w[:m.arena.n])
+    same = all(np.array_equal(ws[0], x) for x in ws[1:])
+    if not same:
+        print(f"[rank {rank}] FAIL model replicas differ (graph={graph})", flush=True)
+    close = all(np.allclose(a, b, rtol=5e-3, atol=2e-4) for a, b in zip(m.get_weights(), mc.get_weights()))
+    if not close:
+        print(f"[rank {rank}] FAIL model weights differ from cpu reference", flush=True)
+    if graph and not any(getattr(v, "graph", None) is not None for v in m._graphs.values()):
+        print(f"[rank {rank}] FAIL graph not captured", flush=True)
+        ok = False
+    return ok and same and close
+
+
+def sweep(strategy, out_path):
+    """Fused all-reduce(+SGD) bus bandwidth: S/t * 2(N-1)/N, device-timed, max over ranks."""
+    comm = strategy.comm()
+    rank, world = strategy.rank, strategy.world_size
+    rows = []
+    for mode in ("one_shot", "two_shot"):
+        for nbytes in (1 << 10, 1 << 14, 1 << 18, 1388584, 1 << 22, 1 << 24, 1 << 26, 1 << 28):
+            if mode == "one_shot" and nbytes * world > (1 << 28):
+                continue
+            n = nbytes // 4
+            os.environ["TFDE_AR_MODE"] = mode
+            opt = O.SGD(0.0).bind(strategy.device)
+            arena = Arena(n, strategy.device, comm=comm)
+            comm.prepare(arena, opt)
+            arena.g.normal_()
+            for _ in range(5):
+                comm.reduce_and_apply(arena, opt)
+            torch.cuda.synchronize(); dist.barrier()
+            iters = 20
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                comm.reduce_and_apply(arena, opt)
+            e1.record(); torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / iters
+            t = torch.tensor([ms], dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+            # NCCL all_reduce of the same size for comparison (library baseline)
+            buf = torch.randn(n, device=strategy.device)
+            for _ in range(5):
+                dist.all_reduce(buf)
+            torch.cuda.synchronize(); dist.barrier()
+            e0.record()
+            for _ in range(iters):
+                dist.all_reduce(buf)
+            e1.record(); torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            nccl_ms = t.item()
+            bus = lambda ms_: nbytes / (ms_ * 1e-3) * 2 * (world - 1) / world / 1e9
+            rows.append({"mode": mode, "bytes": nbytes, "world": world, "fused_us": ms * 1e3,
+                         "fused_bus_GBps": bus(ms), "nccl_allreduce_only_us": nccl_ms * 1e3,
+                         "nccl_bus_GBps": bus(nccl_ms)})
+            comm.check_health()
+            del arena, buf
+    if rank == 0:
+        with open(out_path, "w") as f:
+            json.dump(rows, f, indent=1)
+        for r in rows:
+            print(f"{r['mode']:9s} {r['bytes']:>10d} B  fused(all-reduce+SGD) {r['fused_us']:9.1f} us "
+                  f"{r['fused_bus_GBps']:7.1f} GB/s | nccl all-reduce only {r['nccl_allreduce_only_us']:9.1f} us "
+                  f"{r['nccl_bus_GBps']:7.1f} GB/s", flush=True)
+
+
+def main():
+    strategy = tf.distribute.MirroredStrategy()
+    rank, world = strategy.rank, strategy.world_size
+    assert world >= 2, "launch with torchrun --nproc-per-node >= 2"
+    ok = True
+    # small scalar all-reduce (G14)
+    t = torch.arange(7, dtype=torch.float32, device=strategy.device) + rank
+    strategy.all_reduce_sum_(t)
+    exp = torch.arange(7, dtype=torch.float32) * world + sum(range(world))
+    if not torch.equal(t.cpu(), exp):
+        print(f"[rank {rank}] FAIL scalar allreduce {t.cpu()} vs {exp}", flush=True)
+        ok = False
+    for n in (1000, 347146, 3_000_001):
+        for opt_name in ("sgd", "momentum", "adam"):
+            for mode in ("one_shot", "two_shot"):
+                ok &= check_fused(strategy, n, opt_name, mode)
+    ok &= check_fused(strategy, 347146, "sgd", "one_shot", wire_bf16=True)
+    ok &= check_fused(strategy, 347146, "adam", "two_shot", wire_bf16=True)
+    strategy.comm().wire_bf16 = False
+    ok &= check_model(strategy, graph=False)
+    ok &= check_model(strategy, graph=True)
+    flag = torch.tensor([1.0 if ok else 0.0], dtype=torch.float64)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("P2P CHECKS", "PASSED" if flag.item() == 1.0 else "FAILED", flush=True)
+    if "--sweep" in sys.argv and flag.item() == 1.0:
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        sweep(strategy, os.path.join(ROOT, "gpurun_out", f"allreduce_sweep_n{world}.json"))
+    strategy.shutdown()
+    dist.destroy_process_group()
+    sys.exit(0 if flag.item() == 1.0 else 1)
+
+
+if __name__ == "__main__":
+    main()
