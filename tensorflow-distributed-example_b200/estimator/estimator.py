@@ -402,14 +402,14 @@ class Estimator:
                 ckpt.save_checkpoint(model, self.model_dir, self.global_step, cfg.keep_checkpoint_max)
                 last_saved, t_ckpt = self.global_step, time.time()
         model.sync()
+        if hasattr(st, "on_train_end"):
+            st.on_train_end(model)      # parameter-server mode: final pull, release the ps tasks
         if (chief or getattr(model.arena, "state_sharded", False)) and last_saved != self.global_step:
             ckpt.save_checkpoint(model, self.model_dir, self.global_step, cfg.keep_checkpoint_max)
         for h in all_hooks:
             h.end(self)
         if writer is not None:
             writer.close()
-        if hasattr(st, "on_train_end"):
-            st.on_train_end(model)
         log.info("Loss for final step: %s.", model.last_step_loss())
         return self
 

@@ -276,12 +276,21 @@ class Sequential:
     # ------------------------------------------------------------------------------------------
     def _step_body(self, x, y, global_batch: int):
         """forward -> fused loss/grad/accuracy -> backward -> (cross-replica reduce +) optimizer."""
+        st = self.strategy
+        asynchronous = not st.synchronous
+        if asynchronous:
+            st.pull(self)              # parameter-server mode: fetch the current weights (N4)
         out = self._forward(x, True)
         a = self.arena
         dgrad = self._in_buf("dloss", out.shape)
         ops.xent(out, y, 1.0 / float(global_batch), self.loss.from_probs, out_grad=dgrad, out4=a.grad_tail)
         self._backward(dgrad)
-        if self.strategy.num_replicas_in_sync > 1:
+        if asynchronous:
+            st.push(self)              # the owner applies w -= lr*g without waiting for other workers
+            a.w[a.n:] = a.g[a.n:]
+            a.metrics += a.g[a.n:]
+            self.optimizer.iterations += 1
+        elif self.strategy.num_replicas_in_sync > 1:
             self.strategy.comm().reduce_and_apply(a, self.optimizer)
             self.optimizer.iterations += 1
         else:

@@ -283,16 +283,19 @@ class P2PComm(CommBase):
 
     # ---- the hot path ------------------------------------------------------------------------
     def prepare(self, arena: Arena, optimizer):
-        key = id(arena)
-        if key not in self._channels:
-            self._channels[key] = _Channel(self, arena.n_total, with_weights=True, arena=arena)
-        ch = self._channels[key]
+        # the channel lives ON the arena (an id()-keyed dict would hand a recycled id the stale channel
+        # of a dead arena on one rank only -> ranks disagree about epochs -> dead-lock)
+        ch = getattr(arena, "_channel", None)
+        if ch is None or ch.comm is not self:
+            ch = _Channel(self, arena.n_total, with_weights=True, arena=arena)
+            arena._channel = ch
+            self._channels[len(self._channels)] = ch
         ch.configure_optimizer(optimizer, arena)
         return ch
 
     def reduce_and_apply(self, arena: Arena, optimizer):
-        ch = self._channels.get(id(arena))
-        if ch is None:
+        ch = getattr(arena, "_channel", None)
+        if ch is None or ch.comm is not self:
             ch = self.prepare(arena, optimizer)
         ch.launch(opt=optimizer.native_code, hp=optimizer.hparams, s1=arena.s1, s2=arena.s2)
 

@@ -154,6 +154,9 @@ class Strategy:
 
 def _init_process_group(rank: int, world: int, host: str, port: int, device: torch.device):
     """Control-plane rendezvous. Idempotent: reuses an already initialised default group (torchrun)."""
+    if device.type == "cpu" and "OMP_NUM_THREADS" not in os.environ:
+        # several CPU workers on one host: split the cores instead of oversubscribing them N-fold
+        torch.set_num_threads(max(1, (os.cpu_count() or 1) // max(world, 1)))
     if dist.is_initialized():
         return
     backend = os.environ.get("TFDE_CONTROL_BACKEND")

@@ -70,7 +70,7 @@ def test_model_b_matches_cpu_reference():
     np.testing.assert_allclose(lg, lc, rtol=5e-3, atol=5e-4)
     wc, wg = mc.named_weights(), mg.named_weights()
     for k in wc:
-        np.testing.assert_allclose(wg[k], wc[k], rtol=2e-2, atol=1e-3, err_msg=k)
+        np.testing.assert_allclose(wg[k], wc[k], rtol=2e-2, atol=5e-3, err_msg=k)
     # inference path (moving statistics, no dropout)
     ec = mc.evaluate(x[:256], y[:256].reshape(-1, 1), batch_size=128, return_dict=True)
     eg = mg.evaluate(x[:256], y[:256].reshape(-1, 1), batch_size=128, return_dict=True)
