@@ -115,27 +115,113 @@ __device__ __forceinline__ float update_one(int opt, float w, float g, float* s1
   return w - h.lr_t * m / (sqrtf(v) + h.eps);
 }
 
-// Push `cnt` floats (multiple of 4, 16-byte aligned) from local src to a peer slot.
-__device__ __forceinline__ void push_f32(float* dst, const float* src, long cnt) {
-  const float4* s4 = reinterpret_cast<const float4*>(src);
-  float4* d4 = reinterpret_cast<float4*>(dst);
-  for (long i = threadIdx.x; i < cnt / 4; i += blockDim.x) __stcg(d4 + i, __ldg(s4 + i));
+// ---- vectorised data movement -------------------------------------------------------------------
+// Everything moves as 16-byte groups of 4 floats; loops keep PUSH_U independent groups in flight per
+// thread (posted NVLink stores need memory-level parallelism, not occupancy).
+constexpr int PUSH_U = 4;
+
+__device__ __forceinline__ uint2 pack_bf16x4(const float4 v) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+  uint2 o; o.x = *reinterpret_cast<uint32_t*>(&a); o.y = *reinterpret_cast<uint32_t*>(&b);
+  return o;
 }
-// bf16 wire format: slot holds cnt bf16 values (packed), cnt multiple of 4.
-__device__ __forceinline__ void push_bf16(float* dst, const float* src, long cnt) {
-  const float4* s4 = reinterpret_cast<const float4*>(src);
-  uint2* d2 = reinterpret_cast<uint2*>(dst);
-  for (long i = threadIdx.x; i < cnt / 4; i += blockDim.x) {
-    const float4 v = __ldg(s4 + i);
-    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
-    uint2 o; o.x = *reinterpret_cast<uint32_t*>(&a); o.y = *reinterpret_cast<uint32_t*>(&b);
-    __stcg(d2 + i, o);
+__device__ __forceinline__ float4 unpack_bf16x4(const uint2 r) {
+  float4 v;
+  v.x = __uint_as_float(r.x << 16); v.y = __uint_as_float(r.x & 0xffff0000u);
+  v.z = __uint_as_float(r.y << 16); v.w = __uint_as_float(r.y & 0xffff0000u);
+  return v;
+}
+__device__ __forceinline__ float4 round_bf16x4(const float4 v) { return unpack_bf16x4(pack_bf16x4(v)); }
+
+// Store group `i4` (index in 4-float groups relative to the slot start) of a slot.
+__device__ __forceinline__ void slot_store4(float* slot, long i4, const float4 v, int wire_bf16) {
+  if (wire_bf16) __stcg(reinterpret_cast<uint2*>(slot) + i4, pack_bf16x4(v));
+  else           __stcg(reinterpret_cast<float4*>(slot) + i4, v);
+}
+__device__ __forceinline__ float4 slot_load4(const float* slot, long i4, int wire_bf16) {
+  if (wire_bf16) return unpack_bf16x4(__ldcg(reinterpret_cast<const uint2*>(slot) + i4));
+  return __ldcg(reinterpret_cast<const float4*>(slot) + i4);
+}
+
+struct Vec4 { float v[4]; };
+__device__ __forceinline__ Vec4 to_vec(const float4 f) { Vec4 o; o.v[0] = f.x; o.v[1] = f.y; o.v[2] = f.z; o.v[3] = f.w; return o; }
+__device__ __forceinline__ float4 to_f4(const Vec4& o) { return make_float4(o.v[0], o.v[1], o.v[2], o.v[3]); }
+
+// Sum the W contributions of group (global float index gi, slot-relative group index si4) in RANK ORDER
+// (identical order on every rank => bit-identical replicas), own contribution read from g.
+__device__ __forceinline__ float4 reduce_group(const ARParams& p, const float* base, long slot, long gi, long si4) {
+  float4 v[MAX_RANKS];
+#pragma unroll
+  for (int r = 0; r < MAX_RANKS; ++r) {
+    if (r < p.world) {
+      if (r == p.rank) {
+        v[r] = __ldg(reinterpret_cast<const float4*>(p.g + gi));
+        if (p.wire_bf16) v[r] = round_bf16x4(v[r]);
+      } else {
+        v[r] = slot_load4(base + (size_t)r * slot, si4, p.wire_bf16);
+      }
+    }
   }
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int r = 0; r < MAX_RANKS; ++r)
+    if (r < p.world) { s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w; }
+  return s;
 }
-__device__ __forceinline__ float slot_load(const float* slot, long i, int wire_bf16) {
-  if (!wire_bf16) return __ldcg(slot + i);
-  const unsigned short raw = __ldcg(reinterpret_cast<const unsigned short*>(slot) + i);
-  return __uint_as_float(((uint32_t)raw) << 16);
+
+// Optimizer on one group. gi = global float index of the group, si = index into the optimizer slots.
+__device__ __forceinline__ float4 update_group(const ARParams& p, const Hyper& h, long gi, long si, const float4 sum,
+                                               bool accumulate_metrics) {
+  Vec4 s = to_vec(sum), nw;
+  if (gi + 3 < p.n && p.opt >= 0) {
+    const Vec4 w = to_vec(*reinterpret_cast<const float4*>(p.w + gi));
+    if (p.opt == 0) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) nw.v[c] = w.v[c] - h.lr * (s.v[c] * h.gs);
+    } else if (p.opt == 1 || p.opt == 2) {
+      Vec4 m = to_vec(*reinterpret_cast<const float4*>(p.s1 + si));
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const float g = s.v[c] * h.gs;
+        const float v = h.mu * m.v[c] - h.lr * g;
+        m.v[c] = v;
+        nw.v[c] = w.v[c] + (p.opt == 2 ? (h.mu * v - h.lr * g) : v);
+      }
+      *reinterpret_cast<float4*>(p.s1 + si) = to_f4(m);
+    } else {
+      Vec4 m = to_vec(*reinterpret_cast<const float4*>(p.s1 + si));
+      Vec4 q = to_vec(*reinterpret_cast<const float4*>(p.s2 + si));
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const float g = s.v[c] * h.gs;
+        m.v[c] = h.b1 * m.v[c] + (1.f - h.b1) * g;
+        q.v[c] = h.b2 * q.v[c] + (1.f - h.b2) * g * g;
+        nw.v[c] = w.v[c] - h.lr_t * m.v[c] / (sqrtf(q.v[c]) + h.eps);
+      }
+      *reinterpret_cast<float4*>(p.s1 + si) = to_f4(m);
+      *reinterpret_cast<float4*>(p.s2 + si) = to_f4(q);
+    }
+  } else {
+    // boundary group (parameters end inside it) or reduce-only: per component
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const long i = gi + c;
+      if (i < p.n) nw.v[c] = update_one(p.opt, p.w[i], s.v[c], p.s1, p.s2, si + c, h);
+      else {
+        nw.v[c] = s.v[c];
+        if (accumulate_metrics && p.metrics && i - p.n < p.n_extra) p.metrics[i - p.n] += s.v[c];
+      }
+    }
+  }
+  return to_f4(nw);
+}
+
+__device__ __forceinline__ void store_bf16_shadow(__nv_bfloat16* dst, long gi, const float4 nw, long n) {
+  if (gi + 3 < n) *reinterpret_cast<uint2*>(dst + gi) = pack_bf16x4(nw);
+  else {
+    const Vec4 o = to_vec(nw);
+    for (int c = 0; c < 4; ++c) if (gi + c < n) dst[gi + c] = __float2bfloat16(o.v[c]);
+  }
 }
 
 __global__ void __launch_bounds__(AR_THREADS)
@@ -159,66 +245,79 @@ allreduce_fused_kernel(const ARParams p) {
   }
 
   const long slot = p.slot_floats;
+  const float* base = p.recv[R] + (size_t)parity * W * slot;   // my receive slots of this parity
   if (p.mode == 0) {
     // ------------------------------- one-shot -------------------------------------------
     long chunk = (p.n_total + nb - 1) / nb; chunk = (chunk + 3) & ~3L;
     const long lo = min((long)b * chunk, p.n_total), hi = min(lo + chunk, p.n_total);
-    const long cnt = hi - lo;
-    for (int i = 1; i < W; ++i) {
-      const int peer = (R + i) % W;
-      float* dst = p.recv[peer] + ((size_t)parity * W + R) * slot;
-      if (p.wire_bf16) push_bf16(reinterpret_cast<float*>(reinterpret_cast<unsigned short*>(dst) + lo), p.g + lo, cnt);
-      else             push_f32(dst + lo, p.g + lo, cnt);
+    const long lo4 = lo >> 2, cnt4 = (hi - lo) >> 2;
+    const float4* g4 = reinterpret_cast<const float4*>(p.g) + lo4;
+    // push: read each group once, store it into slot[R] of every peer
+    for (long i0 = t; i0 < cnt4; i0 += (long)PUSH_U * blockDim.x) {
+      float4 v[PUSH_U];
+#pragma unroll
+      for (int u = 0; u < PUSH_U; ++u) {
+        const long i = i0 + (long)u * blockDim.x;
+        if (i < cnt4) v[u] = __ldg(g4 + i);
+      }
+      for (int k = 1; k < W; ++k) {
+        const int peer = (R + k) % W;
+        float* dst = p.recv[peer] + ((size_t)parity * W + R) * slot;
+#pragma unroll
+        for (int u = 0; u < PUSH_U; ++u) {
+          const long i = i0 + (long)u * blockDim.x;
+          if (i < cnt4) slot_store4(dst, lo4 + i, v[u], p.wire_bf16);
+        }
+      }
     }
     flag_barrier(p, 0, b, e);
-    const float* base = p.recv[R] + (size_t)parity * W * slot;
-    for (long i = lo + t; i < hi; i += blockDim.x) {
-      float s = 0.f;
-      for (int r = 0; r < W; ++r) {
-        float v;
-        if (r == R) { v = __ldg(p.g + i); if (p.wire_bf16) v = bf16_round(v); }
-        else v = slot_load(base + (size_t)r * slot, i, p.wire_bf16);
-        s += v;
-      }
-      float nw;
-      if (i < p.n) nw = update_one(p.opt, p.w[i], s, p.s1, p.s2, i, h);
-      else { nw = s; if (p.metrics && i - p.n < p.n_extra) p.metrics[i - p.n] += s; }
-      p.w[i] = nw;
-      if (p.w_bf16 && i < p.n) p.w_bf16[i] = __float2bfloat16(nw);
+    for (long i = t; i < cnt4; i += blockDim.x) {
+      const long gi = lo + (i << 2);
+      const float4 s = reduce_group(p, base, slot, gi, lo4 + i);
+      const float4 nw = update_group(p, h, gi, gi, s, true);
+      *reinterpret_cast<float4*>(p.w + gi) = nw;
+      if (p.w_bf16) store_bf16_shadow(p.w_bf16, gi, nw, p.n);
     }
   } else {
     // ------------------------------- two-shot -------------------------------------------
     // slice j = [j*slot, (j+1)*slot) ; this block handles sub-range [lo, hi) of every slice.
     long chunk = (slot + nb - 1) / nb; chunk = (chunk + 3) & ~3L;
     const long lo = min((long)b * chunk, slot), hi = min(lo + chunk, slot);
-    for (int i = 1; i < W; ++i) {
-      const int peer = (R + i) % W;
+    const long lo4 = lo >> 2;
+    for (int k = 1; k < W; ++k) {          // reduce-scatter by push: slice `peer` of my gradient -> peer
+      const int peer = (R + k) % W;
       const long gbeg = (long)peer * slot + lo;
-      long cnt = min((long)peer * slot + hi, p.n_total) - gbeg;
-      if (cnt <= 0) continue;
+      const long cnt4 = (min((long)peer * slot + hi, p.n_total) - gbeg) >> 2;
+      if (cnt4 <= 0) continue;
       float* dst = p.recv[peer] + ((size_t)parity * W + R) * slot;
-      if (p.wire_bf16) push_bf16(reinterpret_cast<float*>(reinterpret_cast<unsigned short*>(dst) + lo), p.g + gbeg, cnt);
-      else             push_f32(dst + lo, p.g + gbeg, cnt);
+      const float4* g4 = reinterpret_cast<const float4*>(p.g + gbeg);
+      for (long i0 = t; i0 < cnt4; i0 += (long)PUSH_U * blockDim.x) {
+        float4 v[PUSH_U];
+#pragma unroll
+        for (int u = 0; u < PUSH_U; ++u) {
+          const long i = i0 + (long)u * blockDim.x;
+          if (i < cnt4) v[u] = __ldg(g4 + i);
+        }
+#pragma unroll
+        for (int u = 0; u < PUSH_U; ++u) {
+          const long i = i0 + (long)u * blockDim.x;
+          if (i < cnt4) slot_store4(dst, lo4 + i, v[u], p.wire_bf16);
+        }
+      }
     }
     flag_barrier(p, 0, b, e);
-    const float* base = p.recv[R] + (size_t)parity * W * slot;
     const long own0 = (long)R * slot;
-    for (long li = lo + t; li < hi; li += blockDim.x) {
-      const long i = own0 + li;
-      if (i >= p.n_total) break;
-      float s = 0.f;
-      for (int r = 0; r < W; ++r) {
-        float v;
-        if (r == R) { v = __ldg(p.g + i); if (p.wire_bf16) v = bf16_round(v); }
-        else v = slot_load(base + (size_t)r * slot, li, p.wire_bf16);
-        s += v;
-      }
-      const float nw = (i < p.n) ? update_one(p.opt, p.w[i], s, p.s1, p.s2, li, h) : s;
-      // all-gather: write the new value into every replica (own included)
-      for (int r = 0; r < W; ++r) {
-        const int peer = (R + r) % W;
-        __stcg(p.wpeer[peer] + i, nw);
-        if (p.w_bf16 && i < p.n) p.wbf_peer[peer][i] = __float2bfloat16(nw);
+    const long own_cnt4 = (min(own0 + hi, p.n_total) - (own0 + lo)) >> 2;
+    for (long i = t; i < own_cnt4; i += blockDim.x) {
+      const long li = lo + (i << 2);
+      const long gi = own0 + li;
+      const float4 s = reduce_group(p, base, slot, gi, lo4 + i);
+      const float4 nw = update_group(p, h, gi, li, s, false);
+      // all-gather by push: the new values go into every replica (own included)
+      for (int k = 0; k < W; ++k) {
+        const int peer = (R + k) % W;
+        __stcg(reinterpret_cast<float4*>(p.wpeer[peer] + gi), nw);
+        if (p.w_bf16) store_bf16_shadow(p.wbf_peer[peer], gi, nw, p.n);
       }
     }
     flag_barrier(p, 1, b, e);

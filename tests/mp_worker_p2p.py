@@ -146,31 +146,46 @@ def sweep(strategy, out_path):
             arena = Arena(n, strategy.device, comm=comm)
             comm.prepare(arena, opt)
             arena.g.normal_()
-            for _ in range(5):
-                comm.reduce_and_apply(arena, opt)
-            torch.cuda.synchronize(); dist.barrier()
             iters = 20
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for _ in range(iters):
-                comm.reduce_and_apply(arena, opt)
-            e1.record(); torch.cuda.synchronize()
-            ms = e0.elapsed_time(e1) / iters
-            t = torch.tensor([ms], dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = t.item()
-            # NCCL all_reduce of the same size for comparison (library baseline)
+
+            def timed(fn):
+                """CUDA-graph replay of `iters` back-to-back launches (removes host launch overhead);
+                falls back to eager launches if capture is not possible. Device time, max over ranks."""
+                stream = torch.cuda.Stream()
+                with torch.cuda.stream(stream):
+                    for _ in range(3):
+                        fn()
+                stream.synchronize(); dist.barrier()
+                graph = None
+                try:
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph, stream=stream):
+                        for _ in range(iters):
+                            fn()
+                except Exception as ex:  # noqa: BLE001
+                    if rank == 0:
+                        print("graph capture failed, timing eager launches:", ex, flush=True)
+                    graph = None
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                with torch.cuda.stream(stream):
+                    if graph is not None:
+                        graph.replay()
+                    stream.synchronize(); dist.barrier()
+                    e0.record(stream)
+                    if graph is not None:
+                        graph.replay()
+                    else:
+                        for _ in range(iters):
+                            fn()
+                    e1.record(stream)
+                stream.synchronize()
+                tt = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                return tt.item()
+
+            ms = timed(lambda: comm.reduce_and_apply(arena, opt))
             buf = torch.randn(n, device=strategy.device)
-            for _ in range(5):
-                dist.all_reduce(buf)
-            torch.cuda.synchronize(); dist.barrier()
-            e0.record()
-            for _ in range(iters):
-                dist.all_reduce(buf)
-            e1.record(); torch.cuda.synchronize()
-            t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            nccl_ms = t.item()
+            nccl_ms = timed(lambda: dist.all_reduce(buf))
             bus = lambda ms_: nbytes / (ms_ * 1e-3) * 2 * (world - 1) / world / 1e9
             rows.append({"mode": mode, "bytes": nbytes, "world": world, "fused_us": ms * 1e3,
                          "fused_bus_GBps": bus(ms), "nccl_allreduce_only_us": nccl_ms * 1e3,
