@@ -1,0 +1,134 @@
+/* C ABI of libtfde_kernels.so -- the hand-written sm_100a kernels of tfde_b200.
+ *
+ * Conventions
+ *  - every function returns a cudaError_t as int (0 == success, 1 == invalid argument);
+ *  - tensors are dense, channels-last (NHWC), fp32 unless stated; conv kernels are HWIO, dense kernels
+ *    (in, out) -- the Keras variable layout of the reference, which is also the GEMM-native layout;
+ *  - `stream` is a cudaStream_t; all launches are asynchronous and CUDA-graph capturable;
+ *  - `ws`/`counters`/`partials`: caller-provided scratch. `counters` must be zero on first use and is
+ *    left zero by every kernel (self-cleaning tickets); kernels sharing scratch must share a stream.
+ *
+ * "ref:" comments cite the reference call site whose TensorFlow op the kernel replaces
+ * (paths relative to the reference repository root).
+ */
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* tfde_stream_t; /* cudaStream_t */
+
+/* ---- GEMM family (csrc/kernels/gemm_fp32.cu) ------------------------------------------------------ */
+/* y[M,N] = act(x[M,K] . w[K,N] + bias).  ref: Dense, distributed_with_keras.py:37-38,
+ * mnist_keras_distributed.py:103,108 (cuBLAS GEMM + Eigen bias/relu in TF). */
+int tfde_dense_fwd(const float* x, const float* w, const float* bias, float* y, int M, int K, int N,
+                   int relu, float* ws, size_t ws_bytes, unsigned* counters, tfde_stream_t stream);
+/* dw[K,N] = x^T . (dy * (ymask > 0)), db[N] = column sums (db may be NULL). ref: Dense backward. */
+int tfde_dense_wgrad(const float* x, const float* dy, const float* ymask, float* dw, float* db, int M,
+                     int K, int N, float* ws, size_t ws_bytes, unsigned* counters, tfde_stream_t stream);
+/* dx[M,K] = (dy * (ymask > 0)) . w^T. ref: Dense backward. */
+int tfde_dense_dgrad(const float* dy, const float* ymask, const float* w, float* dx, int M, int K, int N,
+                     float* ws, size_t ws_bytes, unsigned* counters, tfde_stream_t stream);
+/* NHWC x HWIO convolution as implicit GEMM. ref: Conv2D, distributed_with_keras.py:34,
+ * mnist_keras_distributed.py:83-98 (cuDNN in TF). pt/pl = top/left padding (TF SAME rule). */
+int tfde_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int B, int H, int W,
+                    int C, int KH, int KW, int Ho, int Wo, int sh, int sw, int pt, int pl, int Cout,
+                    int relu, float* ws, size_t ws_bytes, unsigned* counters, tfde_stream_t stream);
+int tfde_conv2d_wgrad(const float* x, const float* dy, const float* ymask, float* dw, float* db, int B,
+                      int H, int W, int C, int KH, int KW, int Ho, int Wo, int sh, int sw, int pt, int pl,
+                      int Cout, float* ws, size_t ws_bytes, unsigned* counters, tfde_stream_t stream);
+int tfde_conv2d_dgrad(const float* dy, const float* ymask, const float* w, float* dx, int B, int H, int W,
+                      int C, int KH, int KW, int Ho, int Wo, int sh, int sw, int pt, int pl, int Cout,
+                      float* ws, size_t ws_bytes, unsigned* counters, tfde_stream_t stream);
+int tfde_gemm_max_counters(void);
+
+/* ---- fused first layer of Model A (csrc/kernels/conv_pool.cu) -------------------------------------- */
+/* Conv2D(32,3,relu) + MaxPooling2D() in one pass; x may be uint8 (scaled by in_scale on load).
+ * ref: distributed_with_keras.py:20-23,34-35. */
+int tfde_conv3x3c1_relu_pool_fwd(const void* x, int x_is_u8, float in_scale, const float* w,
+                                 const float* bias, float* pooled, uint8_t* idx, int B, int H, int W,
+                                 int Cout, tfde_stream_t stream);
+size_t tfde_conv3x3c1_relu_pool_bwd_ws_floats(void);
+int tfde_conv3x3c1_relu_pool_bwd(const void* x, int x_is_u8, float in_scale, const float* pooled,
+                                 const uint8_t* idx, const float* dpooled, float* dw, float* db,
+                                 float* partials, unsigned* counter, int B, int H, int W, int Cout,
+                                 tfde_stream_t stream);
+
+/* ---- normalisation / pooling / elementwise (csrc/kernels/nn_ops.cu) -------------------------------- */
+/* ref: BatchNormalization(scale=False, center=True) + Activation('relu'),
+ * mnist_keras_distributed.py:86-88,93-94,99-100,104-105 (cuDNN FusedBatchNormV3 in TF). */
+size_t tfde_bn_ws_floats(long M, int C);
+int tfde_bn_fwd_train(const float* x, float* y, long M, int C, const float* gamma, const float* beta,
+                      float* moving_mean, float* moving_var, float* save_mean, float* save_invstd,
+                      float momentum, float eps, int relu, int unbiased_moving, float* partials,
+                      unsigned* counters, tfde_stream_t stream);
+int tfde_bn_fwd_infer(const float* x, float* y, long M, int C, const float* gamma, const float* beta,
+                      const float* moving_mean, const float* moving_var, float eps, int relu,
+                      tfde_stream_t stream);
+int tfde_bn_bwd(const float* x, const float* y, const float* dy, float* dx, long M, int C,
+                const float* gamma, const float* save_mean, const float* save_invstd, int relu,
+                float* dbeta, float* dgamma_full, float* partials, unsigned* counters,
+                tfde_stream_t stream);
+/* ref: MaxPooling2D, distributed_with_keras.py:35 (generic window/stride/padding). */
+int tfde_maxpool_fwd(const float* x, float* y, uint8_t* idx, int B, int H, int W, int C, int PH, int PW,
+                     int sh, int sw, int pt, int pl, int Ho, int Wo, tfde_stream_t stream);
+int tfde_maxpool_bwd(const float* dy, const uint8_t* idx, float* dx, int B, int H, int W, int C, int PH,
+                     int PW, int sh, int sw, int pt, int pl, int Ho, int Wo, tfde_stream_t stream);
+/* ref: Activation('relu'), mnist_keras_distributed.py:88. */
+int tfde_relu_fwd(const float* x, float* y, long n, tfde_stream_t stream);
+int tfde_relu_bwd(const float* y, const float* dy, float* dx, long n, tfde_stream_t stream);
+int tfde_add(const float* a, const float* b, float* y, long n, int relu, tfde_stream_t stream);
+/* ref: image cast + /255, distributed_with_keras.py:20-23, mnist_keras_distributed.py:211. */
+int tfde_u8_to_f32(const uint8_t* x, float* y, long n, float scale, tfde_stream_t stream);
+/* ref: Dropout(0.5), mnist_keras_distributed.py:106. Philox mask from (seed, step, stream_id, index);
+ * seed/step are read from the device hparams block. Same call for forward and backward. */
+int tfde_dropout(const float* x, float* y, long n, float rate, const void* hparams, unsigned stream_id,
+                 int training, tfde_stream_t stream);
+/* ref: Dense(10, activation='softmax'), mnist_keras_distributed.py:108. */
+int tfde_softmax_fwd(const float* z, float* p, int rows, int C, tfde_stream_t stream);
+int tfde_softmax_bwd(const float* p, const float* dp, float* dz, int rows, int C, tfde_stream_t stream);
+int tfde_gap_fwd(const float* x, float* y, int B, int HW, int C, tfde_stream_t stream);
+int tfde_gap_bwd(const float* dy, float* dx, int B, int HW, int C, tfde_stream_t stream);
+
+/* ---- loss + single-GPU optimizer (csrc/kernels/loss_optim.cu) -------------------------------------- */
+/* Sparse categorical cross-entropy (+gradient +accuracy). out4 = [loss_sum*scale, correct, rows, 0].
+ * ref: distributed_with_keras.py:41, tf2_mnist_distributed.py:81-83, mnist_keras_distributed.py:114. */
+size_t tfde_xent_ws_floats(void);
+int tfde_xent(const float* in, const void* labels, int label_is_i64, float* dgrad, int rows, int C,
+              float scale, int from_probs, float* partials, unsigned* counter, float* out4,
+              tfde_stream_t stream);
+/* opt: 0 SGD, 1 momentum, 2 nesterov, 3 Adam, applied to the flat arena; advances the device-side
+ * step. ref: SGD, distributed_with_keras.py:42; GradientDescentOptimizer, mnist_keras_distributed.py:111. */
+int tfde_optimizer_apply(float* w, const float* g, float* s1, float* s2, void* w_bf16, long n,
+                         int n_extra, float* metrics, float* last_extra, int opt, void* hparams,
+                         unsigned* counter, tfde_stream_t stream);
+int tfde_hparams_advance(void* hparams, tfde_stream_t stream);
+
+/* ---- peer-to-peer collectives (csrc/kernels/allreduce_p2p.cu) -------------------------------------- */
+/* Symmetric memory + CUDA IPC plumbing (set-up only). */
+int tfde_set_device(int dev);
+int tfde_symm_alloc(size_t bytes, void** out);
+int tfde_symm_free(void* p);
+int tfde_ipc_get_handle(void* p, void* handle64);
+int tfde_ipc_open_handle(const void* handle64, void** out);
+int tfde_ipc_close_handle(void* p);
+int tfde_ipc_handle_bytes(void);
+int tfde_ar_max_ranks(void);
+int tfde_ar_max_blocks(void);
+size_t tfde_ar_flag_bytes(int world);
+size_t tfde_ar_desc_bytes(void);
+/* Fused gradient all-reduce (one-shot / two-shot push over NVLink) + scale + optional bf16 wire cast +
+ * SGD/momentum/Adam update; `desc` is a TfdeARDesc (layout in allreduce_p2p.cu, mirrored by
+ * parallel/comm.py::_ARDesc). ref: the NCCL all-reduce + apply_gradients implied by
+ * MultiWorkerMirroredStrategy, distributed_with_keras.py:16,63; MirroredStrategy,
+ * mnist_keras_distributed.py:243. */
+int tfde_allreduce_fused(const void* desc, tfde_stream_t stream);
+/* dst(local) <- src(peer mapped): initial broadcast from the chief. ref: distributed_with_keras.py:58. */
+int tfde_p2p_copy(float* dst, const float* src, long n, tfde_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
