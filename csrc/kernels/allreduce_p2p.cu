@@ -80,7 +80,8 @@ __device__ __forceinline__ void flag_barrier(const ARParams& p, int phase, int b
   __syncthreads();  // all pushes of this block issued
   const int t = threadIdx.x;
   if (t < p.world && t != p.rank) {
-    __threadfence_system();
+    // st.release.sys orders every write that happened-before it (the block's pushes, via the
+    // bar.sync above) before the flag becomes visible; no separate membar.sys round trip needed.
     st_release_sys(p.flags[t] + ((size_t)phase * p.world + p.rank) * MAX_BLOCKS + b, e);
     const uint32_t* mine = p.flags[p.rank] + ((size_t)phase * p.world + t) * MAX_BLOCKS + b;
     const unsigned long long t0 = globaltimer_ns();

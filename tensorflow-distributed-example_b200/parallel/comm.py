@@ -352,7 +352,7 @@ class _Channel:
             self.wbuf = comm.buffer_of(self.w)
             self.metrics = None
             self.n, self.n_extra = n_total, 0
-        default_blocks = 32 if bytes_total <= (4 << 20) else 144
+        default_blocks = 16 if bytes_total <= (256 << 10) else (64 if bytes_total <= (4 << 20) else 144)
         self.blocks = int(os.environ.get("TFDE_AR_BLOCKS", str(default_blocks)))
         self.blocks = max(1, min(self.blocks, MAX_BLOCKS))
         self.desc = _ARDesc()
