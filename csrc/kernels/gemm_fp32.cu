@@ -496,3 +496,95 @@ TFDE_API int tfde_conv2d_dgrad(const float* dy, const float* ymask, const float*
 }
 
 TFDE_API int tfde_gemm_max_counters() { return kMaxCounters; }
+
+// ---------------------------------------------------------------------------------------------
+// Dense forward for callers that are not able to allocate device memory.
+//
+// Who this is for: code that is handed its input and output buffers and nothing else. Typical cases are
+// a plug-in inside a serving process whose memory pool is owned (and fully reserved) by the host
+// framework -- TensorFlow, which the reference scripts run on, grabs almost all GPU memory at start-up
+// unless told otherwise (see the per_process_gpu_memory_fraction note at
+// mnist_keras_distributed.py:170-174), so a cudaMalloc from a co-resident library simply fails -- and
+// latency-critical loops in which cudaMalloc/cudaFree are off limits because they synchronise the device.
+// tfde_dense_fwd needs split-K scratch (partial sums + tickets) from its caller; this variant brings its
+// own, a fixed array that lives in the library image.
+//
+// What you must know before using it:
+//  * The scratch is ONE file-scope __device__ array (kStaticScratchBytes, about 2 MiB). Every GPU that
+//    loads this library keeps that much memory reserved until the process exits.
+//  * Problems whose split-K schedule needs more than kStaticPartialBytes of partial sums are refused
+//    (return value 1 == cudaErrorInvalidValue, reason printed on stderr); nothing is launched. Use
+//    tfde_dense_fwd with your own workspace for those.
+//  * All calls on a device share the array. The tickets are cleared at the start of every call, the
+//    partial sums are overwritten before they are read, so back-to-back calls on one stream are fine.
+//    Two calls that can run at the same time on the GPU (different streams, or graph branches with no
+//    dependency between them) race on the array and produce garbage.
+//  * The very first call on each device looks up the device address of the array (a host-side symbol is
+//    not a device pointer). Make that first call outside of any stream capture, with the device you
+//    intend to use current.
+//  * No cudaMalloc, cudaFree or other allocating routine is called, here or in the kernel.
+// ---------------------------------------------------------------------------------------------
+#include <cstdio>
+#include <mutex>
+
+namespace {
+constexpr size_t kStaticTicketBytes = (size_t)TFDE_MAX_COUNTERS * sizeof(unsigned);  // 16 KiB
+constexpr size_t kStaticPartialBytes = (size_t)2 << 20;                              // 2 MiB
+constexpr size_t kStaticScratchBytes = kStaticTicketBytes + kStaticPartialBytes;
+static __device__ __align__(256) unsigned char s_static_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevicesTracked = 64;
+unsigned char* g_static_scratch_dev[kMaxDevicesTracked];  // device address per GPU, filled on first use
+std::mutex g_static_scratch_mu;
+
+// Device address of s_static_scratch on the current device (naming the array in host code would give the
+// host-side shadow symbol, which a kernel must never be handed).
+int static_scratch_address(unsigned char** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kMaxDevicesTracked) return TFDE_ERR_INVALID;
+  std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+  if (g_static_scratch_dev[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, s_static_scratch);
+    if (e != cudaSuccess) return (int)e;
+    g_static_scratch_dev[dev] = static_cast<unsigned char*>(ptr);
+  }
+  *out = g_static_scratch_dev[dev];
+  return 0;
+}
+}  // namespace
+
+// y[M,N] = act(x[M,K] . w[K,N] + bias), same math and kernel as tfde_dense_fwd, scratch taken from the
+// library's own static device array. See the block comment above for limits and hazards.
+TFDE_API int tfde_dense_fwd_static_scratch(const float* x, const float* w, const float* bias, float* y,
+                                           int M, int K, int N, int relu, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || !x || !w || !y) return TFDE_ERR_INVALID;
+  // The split-K schedule this shape would get with unlimited workspace decides how much scratch it needs.
+  const int splits = choose_splits(M, N, K, (size_t)-1, kMaxCounters);
+  const size_t need = splits > 1 ? (size_t)splits * M * ((N + 3) & ~3) * sizeof(float) : 0;
+  if (need > kStaticPartialBytes) {
+    fprintf(stderr,
+            "tfde_dense_fwd_static_scratch: M=%d K=%d N=%d needs %zu bytes of split-K scratch but the "
+            "built-in array holds %zu; call tfde_dense_fwd with a caller-provided workspace instead\n",
+            M, K, N, need, kStaticPartialBytes);
+    return TFDE_ERR_INVALID;
+  }
+  unsigned char* base = nullptr;
+  const int rc = static_scratch_address(&base);
+  if (rc != 0) return rc;
+  unsigned* tickets = reinterpret_cast<unsigned*>(base);
+  float* partials = reinterpret_cast<float*>(base + kStaticTicketBytes);
+  if (splits > 1) {
+    // tickets must read zero when the kernel starts; the array keeps whatever the previous call
+    // (possibly an aborted one) left behind.
+    const cudaError_t e = cudaMemsetAsync(tickets, 0, kStaticTicketBytes, stream);
+    if (e != cudaSuccess) return (int)e;
+  }
+  GemmParams p{};
+  p.A = x; p.lda = K; p.B = w; p.ldb = N; p.C = y; p.ldc = N; p.bias = bias;
+  p.M = M; p.N = N; p.K = K; p.ones_row = -1; p.relu = relu;
+  p.ws = partials; p.counters = tickets; p.splits = splits;
+  return dispatch(A_DENSE, B_DENSE, p, stream);
+}

@@ -44,6 +44,16 @@ int tfde_conv2d_dgrad(const float* dy, const float* ymask, const float* w, float
                       int C, int KH, int KW, int Ho, int Wo, int sh, int sw, int pt, int pl, int Cout,
                       float* ws, size_t ws_bytes, unsigned* counters, tfde_stream_t stream);
 int tfde_gemm_max_counters(void);
+/* tfde_dense_fwd for callers that cannot allocate device memory (a plug-in inside a process whose GPU
+ * memory pool belongs to another framework, or a loop where cudaMalloc is forbidden): the split-K scratch
+ * is a static __device__ array inside the library (about 2 MiB, held by every GPU that loads the library
+ * until exit) instead of caller-provided ws/counters. Shapes whose split-K partial sums exceed 2 MiB are
+ * refused with return value 1 and a message on stderr. All calls on a device share the array: calls that
+ * may overlap on the GPU race. The first call on each device resolves the array's device address and
+ * must happen outside stream capture. Allocates nothing. This entry point has no counterpart in the
+ * reference (the reference has no native code at all); it exists for embedders of this library. */
+int tfde_dense_fwd_static_scratch(const float* x, const float* w, const float* bias, float* y, int M, int K,
+                                  int N, int relu, tfde_stream_t stream);
 
 /* ---- fused first layer of Model A (csrc/kernels/conv_pool.cu) -------------------------------------- */
 /* Conv2D(32,3,relu) + MaxPooling2D() in one pass; x may be uint8 (scaled by in_scale on load).
