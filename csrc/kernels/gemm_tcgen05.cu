@@ -1,0 +1,337 @@
+// bf16 GEMM on the 5th-generation tensor cores: tcgen05.mma with the accumulator in TMEM, operands
+// staged in shared memory by TMA (cp.async.bulk.tensor, 128-byte swizzle), warp-specialised roles.
+//
+//   C[M,N] = act( A[M,K] . B[N,K]^T + bias[N] )        A, B bf16 K-major ("TN"), C fp32 or bf16
+//
+// This is the tensor-core path for the dense layers of the reference when they are big enough to feed
+// it -- Dense(64) over the 5408-wide flattened activation at large batch, BASELINE.json config 3
+// ("distributed_with_keras.py model at large global batch (8192) bf16"), i.e. the G4/G5 rows of
+// SURVEY.md section 2.7 (cuBLAS GEMM + Eigen bias/relu in TensorFlow: distributed_with_keras.py:37-38).
+// The three GEMMs of a dense layer all map onto this one TN kernel:
+//   forward  y  = x . W          A = x  [M,K],        B = W^T [N,K]   (+bias, ReLU in the epilogue)
+//   dgrad    dx = dy . W^T       A = dy [M,N],        B = W   [K,N]   (Keras (in,out) layout as stored)
+//   wgrad    dW = x^T . dy       A = x^T [K,M],       B = dy^T [N,M]
+//
+// Structure (one 128 x BN output tile per CTA, 192 threads):
+//   warp 0      TMA producer: one elected lane arms full[s] with expect_tx and issues two bulk tensor
+//               loads per k-block into a 4-stage ring (A: 128x64 bf16 = 16 KB, B: BNx64 bf16)
+//   warp 1      allocates BN TMEM columns; one elected lane issues 4 x tcgen05.mma (K=16 each) per
+//               k-block and releases the stage with tcgen05.commit -> empty[s]; final commit -> tmem_full
+//   warps 2..5  epilogue: tcgen05.ld (32 lanes x 32 columns per instruction) -> bias/ReLU -> global
+// M/N/K tails are handled by TMA zero fill on loads and by bounds checks on stores.
+#include "common.cuh"
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <mutex>
+
+namespace {
+
+constexpr int TC_BM = 128;
+constexpr int TC_BK = 64;          // 64 bf16 = 128 bytes = one swizzle row
+constexpr int TC_STAGES = 4;
+constexpr int TC_THREADS = 192;
+constexpr int UMMA_K = 16;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) { }
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c_inner, int c_outer) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c_inner), "r"(c_outer) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
+// [0,14) start address >> 4 | [16,30) leading byte offset >> 4 (unused for swizzled K-major, 1) |
+// [32,46) stride byte offset >> 4 (8 rows x 128 B = 1024 B) | [46,48) version = 1 | [61,64) layout = 2.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) |
+         (2ull << 61);
+}
+// kind::f16 instruction descriptor: fp32 accumulate, bf16 A/B, both K-major, N>>3 at [17,23), M>>4 at [24,29).
+__device__ __forceinline__ uint32_t make_instr_desc(int umma_m, int umma_n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(umma_n >> 3) << 17) | ((uint32_t)(umma_m >> 4) << 24);
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+struct TcEpilogue {
+  float* c_f32; __nv_bfloat16* c_bf16; long ldc;
+  const float* bias; int relu;
+  int M, N;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const TcEpilogue ep, const int K) {
+  constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2;   // 16 KB
+  constexpr uint32_t B_BYTES = BN * TC_BK * 2;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment is required by the 128-byte swizzle atoms (base_offset field left at 0)
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  __shared__ __align__(8) uint64_t full_bar[TC_STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[TC_STAGES];
+  __shared__ __align__(8) uint64_t tmem_full_bar;
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * TC_BM, n0 = blockIdx.x * BN;
+  const int num_k = (K + TC_BK - 1) / TC_BK;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < TC_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(&tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  if (warp == 1) {   // whole warp: allocate BN TMEM columns (power of two >= 32), publish the base address
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"((uint32_t)BN) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_d = tmem_base_smem;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < num_k; ++kb) {
+        const int s = kb % TC_STAGES;
+        const uint32_t ph = (uint32_t)(kb / TC_STAGES) & 1u;
+        mbar_wait(&empty_bar[s], ph ^ 1u);            // slot free (fresh barrier: passes immediately)
+        mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+        uint8_t* a_dst = smem + (size_t)s * STAGE_BYTES;
+        tma_load_2d(a_dst, &tmA, &full_bar[s], kb * TC_BK, m0);
+        tma_load_2d(a_dst + A_BYTES, &tmB, &full_bar[s], kb * TC_BK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_instr_desc(TC_BM, BN);
+      for (int kb = 0; kb < num_k; ++kb) {
+        const int s = kb % TC_STAGES;
+        const uint32_t ph = (uint32_t)(kb / TC_STAGES) & 1u;
+        mbar_wait(&full_bar[s], ph);                  // TMA bytes have landed
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + (size_t)s * STAGE_BYTES);
+        const uint32_t b_addr = a_addr + A_BYTES;
+#pragma unroll
+        for (int k = 0; k < TC_BK / UMMA_K; ++k) {
+          // advancing K by 16 bf16 = 32 bytes inside the 128-byte swizzle row: bump the start address
+          const uint64_t da = make_smem_desc(a_addr + k * UMMA_K * 2);
+          const uint64_t db = make_smem_desc(b_addr + k * UMMA_K * 2);
+          umma_bf16(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);                   // stage reusable once these MMAs have read it
+      }
+      umma_commit(&tmem_full_bar);                    // accumulator complete
+    }
+  } else {
+    // epilogue warps 2..5: TMEM lane quarter = warp % 4
+    mbar_wait(&tmem_full_bar, 0);
+    tc_fence_after();
+    const int q = warp & 3;
+    const int row = m0 + q * 32 + lane;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+      if (row < ep.M) {
+        const int nbase = n0 + c0;
+        if (ep.c_f32 != nullptr) {
+          float* dst = ep.c_f32 + (size_t)row * ep.ldc + nbase;
+          const bool vec = (nbase + 32 <= ep.N) && ((ep.ldc & 3) == 0);
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            float v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              float x = __uint_as_float(r[j + u]);
+              if (ep.bias != nullptr && nbase + j + u < ep.N) x += __ldg(ep.bias + nbase + j + u);
+              if (ep.relu) x = fmaxf(x, 0.f);
+              v[u] = x;
+            }
+            if (vec) *reinterpret_cast<float4*>(dst + j) = make_float4(v[0], v[1], v[2], v[3]);
+            else {
+#pragma unroll
+              for (int u = 0; u < 4; ++u) if (nbase + j + u < ep.N) dst[j + u] = v[u];
+            }
+          }
+        }
+        if (ep.c_bf16 != nullptr) {
+          __nv_bfloat16* dst = ep.c_bf16 + (size_t)row * ep.ldc + nbase;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float x = __uint_as_float(r[j]);
+            if (ep.bias != nullptr && nbase + j < ep.N) x += __ldg(ep.bias + nbase + j);
+            if (ep.relu) x = fmaxf(x, 0.f);
+            if (nbase + j < ep.N) dst[j] = __float2bfloat16(x);
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)BN) : "memory");
+  }
+}
+
+// ---- elementwise helpers for the bf16 path ------------------------------------------------------
+__global__ void cast_f32_to_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long n) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+    y[i] = __float2bfloat16(__ldg(x + i));
+}
+// y[C,R] (bf16) = transpose(x[R,C] (fp32)), optionally masked by (mask[R,C] > 0): 32x32 tiles via smem.
+__global__ void cast_transpose_bf16_kernel(const float* __restrict__ x, const float* __restrict__ mask,
+                                           __nv_bfloat16* __restrict__ y, int R, int C) {
+  __shared__ float tile[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    float v = 0.f;
+    if (r < R && c < C) {
+      v = __ldg(x + (size_t)r * C + c);
+      if (mask != nullptr && !(__ldg(mask + (size_t)r * C + c) > 0.f)) v = 0.f;
+    }
+    tile[i][threadIdx.x] = v;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, r = r0 + threadIdx.x;
+    if (c < C && r < R) y[(size_t)c * R + r] = __float2bfloat16(tile[threadIdx.x][i]);
+  }
+}
+
+// ---- host: tensor maps through the driver entry point (no link-time dependency on libcuda) ---------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+std::mutex g_encode_mu;
+
+int get_encode(EncodeTiledFn* out) {
+  std::lock_guard<std::mutex> lock(g_encode_mu);
+  if (g_encode == nullptr) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess) return (int)e;
+    if (qres != cudaDriverEntryPointSuccess || fn == nullptr) return (int)cudaErrorNotSupported;
+    g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  *out = g_encode;
+  return 0;
+}
+
+// 2-D bf16 tensor [rows, cols] (cols contiguous), box = [box_rows, 64 cols], 128-byte swizzle.
+int make_map(CUtensorMap* map, const void* ptr, long rows, long cols, int box_rows) {
+  EncodeTiledFn enc;
+  const int rc = get_encode(&enc);
+  if (rc != 0) return rc;
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)cols * 2};
+  cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+}
+
+template <int BN>
+int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcEpilogue& ep, int M, int N, int K, cudaStream_t stream) {
+  constexpr size_t smem = (size_t)TC_STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + 1024;
+  static bool configured = false;
+  if (!configured) {
+    const cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    configured = true;
+  }
+  dim3 grid((N + BN - 1) / BN, (M + TC_BM - 1) / TC_BM);
+  gemm_bf16_tcgen05_kernel<BN><<<grid, TC_THREADS, smem, stream>>>(ta, tb, ep, K);
+  TFDE_RETURN_LAUNCH_STATUS();
+}
+
+}  // namespace
+
+// C[M,N] = act(A[M,K] . B[N,K]^T + bias). A, B: bf16, row-major with K contiguous, 16-byte aligned,
+// K % 8 == 0 (TMA global strides are multiples of 16 bytes). Exactly one of c_f32 / c_bf16 may be NULL.
+// The first call per tile shape sets a function attribute: make it outside of stream capture.
+TFDE_API int tfde_gemm_bf16_tn(const void* A, const void* B, float* c_f32, void* c_bf16, long ldc,
+                               const float* bias, int relu, int M, int N, int K, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || (K & 7) || !A || !B || (!c_f32 && !c_bf16)) return TFDE_ERR_INVALID;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return TFDE_ERR_INVALID;
+  const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+  CUtensorMap ta, tb;
+  int rc = make_map(&ta, A, M, K, TC_BM);
+  if (rc != 0) return rc;
+  rc = make_map(&tb, B, N, K, BN);
+  if (rc != 0) return rc;
+  TcEpilogue ep{c_f32, (__nv_bfloat16*)c_bf16, ldc, bias, relu, M, N};
+  if (BN == 64) return launch_tc<64>(ta, tb, ep, M, N, K, stream);
+  if (BN == 128) return launch_tc<128>(ta, tb, ep, M, N, K, stream);
+  return launch_tc<256>(ta, tb, ep, M, N, K, stream);
+}
+
+TFDE_API int tfde_cast_bf16(const float* x, void* y, long n, cudaStream_t stream) {
+  long grid = (n + 255) / 256;
+  if (grid > 148L * 8) grid = 148L * 8;
+  if (grid < 1) grid = 1;
+  cast_f32_to_bf16_kernel<<<(int)grid, 256, 0, stream>>>(x, (__nv_bfloat16*)y, n);
+  TFDE_RETURN_LAUNCH_STATUS();
+}
+
+// y[C,R] bf16 = transpose(x[R,C] fp32 * (mask > 0))
+TFDE_API int tfde_cast_transpose_bf16(const float* x, const float* mask, void* y, int R, int C, cudaStream_t stream) {
+  dim3 grid((C + 31) / 32, (R + 31) / 32), block(32, 8);
+  cast_transpose_bf16_kernel<<<grid, block, 0, stream>>>(x, mask, (__nv_bfloat16*)y, R, C);
+  TFDE_RETURN_LAUNCH_STATUS();
+}

@@ -541,3 +541,62 @@ def optimizer_apply(w, g, hparams, opt=OPT_SGD, s1=None, s2=None, w_bf16=None, n
                                  n_extra, ptr(metrics), ptr(last_extra), opt, hparams.data_ptr(),
                                  wsp.counters.data_ptr() + 4 * (MAX_COUNTERS - 1), stream_ptr()),
           "optimizer_apply")
+
+
+# ----------------------------------------------------------------------------------------------
+# bf16 tensor-core path (csrc/kernels/gemm_tcgen05.cu)
+# ----------------------------------------------------------------------------------------------
+register_optional("tfde_gemm_bf16_tn", [c_p, c_p, c_p, c_p, c_l, c_p, c_i, c_i, c_i, c_i, c_p])
+register_optional("tfde_cast_bf16", [c_p, c_p, c_l, c_p])
+register_optional("tfde_cast_transpose_bf16", [c_p, c_p, c_p, c_i, c_i, c_p])
+register_optional("tfde_dense_fwd_static_scratch", [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p])
+
+
+def gemm_bf16_tn(a, b, bias=None, relu=False, out_dtype=torch.float32, out=None):
+    """C[M,N] = act(A[M,K] @ B[N,K]^T + bias) on tcgen05 tensor cores (TMEM accumulator, TMA-fed).
+    ``a``/``b`` are bf16, row-major, K contiguous, K % 8 == 0."""
+    L = load()
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
+        raise TypeError("gemm_bf16_tn expects bf16 operands")
+    if not (a.is_contiguous() and b.is_contiguous()):
+        raise ValueError("operands must be contiguous")
+    M, K = a.shape
+    N, K2 = b.shape
+    if K != K2:
+        raise ValueError(f"K mismatch: {K} vs {K2}")
+    c = out if out is not None else torch.empty((M, N), dtype=out_dtype, device=a.device)
+    f32 = c.data_ptr() if c.dtype == torch.float32 else None
+    b16 = c.data_ptr() if c.dtype == torch.bfloat16 else None
+    check(L.tfde_gemm_bf16_tn(a.data_ptr(), b.data_ptr(), f32, b16, c.stride(0), ptr(bias), 1 if relu else 0,
+                              M, N, K, stream_ptr()), "gemm_bf16_tn")
+    return c
+
+
+def cast_bf16(x, out=None):
+    L = load()
+    y = out if out is not None else torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    check(L.tfde_cast_bf16(_f32c(x, "x").data_ptr(), y.data_ptr(), x.numel(), stream_ptr()), "cast_bf16")
+    return y
+
+
+def cast_transpose_bf16(x, mask=None, out=None):
+    """y[C,R] (bf16) = (x * (mask > 0))^T for fp32 x[R,C]."""
+    L = load()
+    R, C = x.shape
+    y = out if out is not None else torch.empty((C, R), dtype=torch.bfloat16, device=x.device)
+    check(L.tfde_cast_transpose_bf16(_f32c(x, "x").data_ptr(), ptr(mask), y.data_ptr(), R, C, stream_ptr()),
+          "cast_transpose_bf16")
+    return y
+
+
+def dense_fwd_static_scratch(x, w, bias=None, relu=False, out=None):
+    """Dense forward whose split-K scratch is the library's built-in static device array (no allocation
+    besides the output unless ``out`` is given). See include/tfde_kernels.h for the limits."""
+    L = load()
+    _f32c(x, "x"); _f32c(w, "w")
+    M, K = x.shape
+    N = w.shape[1]
+    y = out if out is not None else torch.empty((M, N), dtype=torch.float32, device=x.device)
+    check(L.tfde_dense_fwd_static_scratch(x.data_ptr(), w.data_ptr(), ptr(bias), y.data_ptr(), M, K, N,
+                                          1 if relu else 0, stream_ptr()), "dense_fwd_static_scratch")
+    return y
