@@ -40,6 +40,9 @@ class SparseCategoricalCrossentropy(Loss):
         NONE returns the per-example vector."""
         import torch
         from ..ops import reference as ref
+        from ..estimator.symbolic import SymbolicLoss, SymbolicOutput
+        if isinstance(y_pred, SymbolicOutput):    # model_fn graph mode: defer to the fused loss kernel
+            return SymbolicLoss(y_pred.model, self, reduced=self.reduction != Reduction.NONE)
         y_pred = y_pred.detach().float().cpu()
         labels = y_true.reshape(-1).long().cpu()
         if self.from_logits:

@@ -257,6 +257,9 @@ class Sequential:
             dy = node.backward(dy)
 
     def __call__(self, x, training=False):
+        from ..estimator.symbolic import SymbolicOutput, SymbolicTensor
+        if isinstance(x, SymbolicTensor):     # graph-building call inside an Estimator model_fn
+            return SymbolicOutput(self, x, training)
         if not self.built:
             self.build(tuple(x.shape[1:]))
         x = self._to_device(x)

@@ -73,6 +73,15 @@ class Optimizer:
         n = arena.n
         arena.w[:n] = ref.sgd_update(arena.w[:n], arena.g[:n], self.learning_rate)
 
+    def minimize(self, loss, global_step=None, var_list=None):
+        """``optimizer.minimize(loss, global_step)`` inside an Estimator model_fn
+        (tf2_mnist_distributed.py:90-91): returns the train op the Estimator runs each step."""
+        from ..estimator.symbolic import SymbolicLoss, TrainOp
+        if not isinstance(loss, SymbolicLoss):
+            raise TypeError("minimize() expects the symbolic loss built inside a model_fn; use "
+                            "model.compile()/fit() or train_on_batch() for eager training")
+        return TrainOp(loss.model, self, loss, global_step)
+
     def get_config(self):
         return {"name": self.name, "learning_rate": self.learning_rate}
 
