@@ -70,7 +70,7 @@ conv3x3c1_relu_pool_bwd_kernel(const void* __restrict__ xin, const float* __rest
                                float* __restrict__ partials, unsigned* __restrict__ counter,
                                int Bn, int H, int W, int PH, int PW, float in_scale) {
   __shared__ float s_patch[WARPS][16];
-  __shared__ float s_red[WARPS][10][32];
+  __shared__ __align__(16) float s_red[WARPS][10][32];
   __shared__ int s_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float acc[10];
@@ -129,18 +129,34 @@ conv3x3c1_relu_pool_bwd_kernel(const void* __restrict__ xin, const float* __rest
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  for (int e = threadIdx.x; e < 320; e += blockDim.x) {
-    float s = 0.f;
-    for (unsigned b0 = 0; b0 < gridDim.x; b0 += 8) {   // 8 loads in flight, summed in block order
-      float v[8];
+  // Final reduction over the per-block partials: 80 float4 columns x 3 interleaved row groups (240
+  // threads), 8 independent 16-byte L2 loads in flight per thread; groups are then combined in a fixed
+  // order, so the result does not depend on which block arrived last.
+  float4* s_grp = reinterpret_cast<float4*>(&s_red[0][0][0]);   // [3][80] float4, re-uses s_red
+  __syncthreads();
+  if (threadIdx.x < 240) {
+    const unsigned grp = threadIdx.x / 80, c4 = threadIdx.x % 80;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (unsigned b0 = grp; b0 < gridDim.x; b0 += 24) {
+      float4 v[8];
 #pragma unroll
-      for (unsigned j = 0; j < 8; ++j)
-        v[j] = (b0 + j < gridDim.x) ? __ldcg(partials + (size_t)(b0 + j) * 320 + e) : 0.f;
+      for (unsigned j = 0; j < 8; ++j) {
+        const unsigned blk = b0 + 3 * j;
+        v[j] = blk < gridDim.x ? __ldcg(reinterpret_cast<const float4*>(partials + (size_t)blk * 320) + c4)
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
 #pragma unroll
-      for (unsigned j = 0; j < 8; ++j) s += v[j];
+      for (unsigned j = 0; j < 8; ++j) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
     }
-    if (e < 288) dw[e] = s;          // [kh][kw][ci=0][co]  == e = (kh*3+kw)*32 + co
-    else if (db != nullptr) db[e - 288] = s;
+    s_grp[grp * 80 + c4] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < 80) {
+    const float4 a = s_grp[threadIdx.x], b = s_grp[80 + threadIdx.x], c = s_grp[160 + threadIdx.x];
+    const float4 s = make_float4((a.x + b.x) + c.x, (a.y + b.y) + c.y, (a.z + b.z) + c.z, (a.w + b.w) + c.w);
+    const int e = threadIdx.x * 4;   // [kh][kw][ci=0][co] == e = (kh*3+kw)*32 + co ; e >= 288 is the bias
+    if (e < 288) *reinterpret_cast<float4*>(dw + e) = s;
+    else if (db != nullptr) *reinterpret_cast<float4*>(db + (e - 288)) = s;
   }
   if (threadIdx.x == 0) *counter = 0u;
 }

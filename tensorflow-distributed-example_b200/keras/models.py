@@ -283,11 +283,28 @@ class Sequential:
         asynchronous = not st.synchronous
         if asynchronous:
             st.pull(self)              # parameter-server mode: fetch the current weights (N4)
-        out = self._forward(x, True)
         a = self.arena
-        dgrad = self._in_buf("dloss", out.shape)
-        ops.xent(out, y, 1.0 / float(global_batch), self.loss.from_probs, out_grad=dgrad, out4=a.grad_tail)
-        self._backward(dgrad)
+        head = self._fusable_head(x)
+        if head is not None:
+            # classifier head in one launch: Dense + loss/accuracy + d(logits) + dW/db + dh
+            h = self._prep_input(x)
+            for node in self.exec_plan[:-1]:
+                h = node.forward(h, True)
+            dh = head.buf("dx", h.shape) if head.need_dx else None
+            ops.head_fwd_bwd(h, head.kernel.value, head.bias.value if head.bias else None, y,
+                             1.0 / float(global_batch), self.loss.from_probs, False, head.need_dx,
+                             out_dh=dh, out_dw=head.kernel.grad, out_db=head.bias.grad if head.bias else None,
+                             out4=a.grad_tail)
+            dy = dh
+            for node in reversed(self.exec_plan[:-1]):
+                if dy is None:
+                    break
+                dy = node.backward(dy)
+        else:
+            out = self._forward(x, True)
+            dgrad = self._in_buf("dloss", out.shape)
+            ops.xent(out, y, 1.0 / float(global_batch), self.loss.from_probs, out_grad=dgrad, out4=a.grad_tail)
+            self._backward(dgrad)
         if asynchronous:
             st.push(self)              # the owner applies w -= lr*g without waiting for other workers
             a.w[a.n:] = a.g[a.n:]
@@ -298,6 +315,18 @@ class Sequential:
             self.optimizer.iterations += 1
         else:
             self.optimizer.apply_local(a)
+
+    def _fusable_head(self, x):
+        """The last Dense layer when Dense + loss + its backward can run as the fused head kernel."""
+        if os.environ.get("TFDE_FUSION", "1") != "1" or len(self.exec_plan) < 2:
+            return None
+        last = self.exec_plan[-1]
+        if not isinstance(last, L.Dense) or not x.is_cuda:
+            return None
+        want = "softmax" if self.loss.from_probs else "none"
+        if last.activation != want or not ops.head_supported(x, last.kernel.value):
+            return None
+        return last
 
     def train_on_batch(self, x, y, global_batch: Optional[int] = None):
         """One optimizer step on this replica's slice of the global batch. Returns nothing (metrics are

@@ -168,3 +168,25 @@ def xent(inp, labels, scale, from_probs=False, out_grad=None, out4=None):
     o4 = torch.stack([loss, correct, torch.tensor(float(inp.shape[0]), dtype=inp.dtype),
                       torch.tensor(0.0, dtype=inp.dtype)])
     return _put(out4, o4), _put(out_grad, dg)
+
+
+def head_supported(h, w) -> bool:
+    """True when the fused classifier-head kernel (Dense + loss + its backward in one launch) applies."""
+    return _cuda(h) and native.head_supported(int(w.shape[0]), int(w.shape[1]))
+
+
+def head_fwd_bwd(h, w, bias, labels, scale, from_probs=False, relu_mask=False, need_dh=True, out=None,
+                 out_dh=None, out_dw=None, out_db=None, out4=None):
+    """Dense(N) -> sparse categorical cross-entropy (+accuracy) -> backward of that Dense.
+    ``relu_mask``: the producer of ``h`` had a fused ReLU, so dh is multiplied by (h > 0).
+    Returns (out4, out, dh, dw, db); ``out`` holds logits (from_probs=False) or probabilities."""
+    if _cuda(h):
+        return native.head_fwd_bwd(h, w, bias, labels, scale, from_probs, relu_mask, need_dh, out, out_dh,
+                                   out_dw, out_db, out4)
+    z = ref.dense_fwd(h, w, bias, "softmax" if from_probs else "none")
+    o4, dgrad = xent(z, labels, scale, from_probs)
+    dx, dw, db = ref.dense_bwd(h, w, z, dgrad, "softmax" if from_probs else "none", need_dh, bias is not None)
+    if dx is not None and relu_mask:
+        dx = dx * (h > 0).to(dx.dtype)
+    return (_put(out4, o4), _put(out, z) if out is not None else z, _put(out_dh, dx) if dx is not None else None,
+            _put(out_dw, dw), _put(out_db, db) if db is not None else None)

@@ -236,8 +236,14 @@ def dense_fwd(x, w, bias=None, act="none", out=None):
     N = w.shape[1]
     y = out if out is not None else torch.empty((M, N), dtype=torch.float32, device=x.device)
     wsp = Workspace.current(x.device)
-    check(L.tfde_dense_fwd(x.data_ptr(), w.data_ptr(), ptr(bias), y.data_ptr(), M, K, N,
-                           1 if act == "relu" else 0, *_gemm_tail(wsp)), "dense_fwd")
+    if _SKINNY and L.tfde_dense_skinny_supported(M, K, N):
+        # small M*N, long K (Dense(64) over 5408 inputs at batch 64): cluster/DSMEM split-K kernel
+        check(L.tfde_dense_skinny_fwd(x.data_ptr(), w.data_ptr(), ptr(bias), y.data_ptr(), M, K, N,
+                                      1 if act == "relu" else 0, wsp.ws.data_ptr(), wsp.counters.data_ptr(),
+                                      stream_ptr()), "dense_skinny_fwd")
+    else:
+        check(L.tfde_dense_fwd(x.data_ptr(), w.data_ptr(), ptr(bias), y.data_ptr(), M, K, N,
+                               1 if act == "relu" else 0, *_gemm_tail(wsp)), "dense_fwd")
     if act == "softmax":
         check(L.tfde_softmax_fwd(y.data_ptr(), y.data_ptr(), M, N, stream_ptr()), "softmax_fwd")
     elif act not in ("none", "relu"):
@@ -600,3 +606,47 @@ def dense_fwd_static_scratch(x, w, bias=None, relu=False, out=None):
     check(L.tfde_dense_fwd_static_scratch(x.data_ptr(), w.data_ptr(), ptr(bias), y.data_ptr(), M, K, N,
                                           1 if relu else 0, stream_ptr()), "dense_fwd_static_scratch")
     return y
+
+
+# ----------------------------------------------------------------------------------------------
+# small-batch latency kernels (csrc/kernels/small_batch.cu)
+# ----------------------------------------------------------------------------------------------
+_SKINNY = os.environ.get("TFDE_SKINNY", "1") == "1"
+register_optional("tfde_dense_skinny_supported", [c_i, c_i, c_i])
+register_optional("tfde_dense_skinny_ws_floats", [c_i, c_i, c_i], c_z)
+register_optional("tfde_dense_skinny_fwd", [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_p])
+register_optional("tfde_head_supported", [c_i, c_i])
+register_optional("tfde_head_ws_floats", [c_i, c_i, c_i], c_z)
+register_optional("tfde_head_fwd_bwd", [c_p, c_p, c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i,
+                                        c_f, c_p, c_p, c_p])
+
+
+def head_supported(K: int, N: int) -> bool:
+    return bool(load().tfde_head_supported(K, N))
+
+
+def head_fwd_bwd(h, w, bias, labels, scale, from_probs=False, relu_mask=False, need_dh=True, out=None,
+                 out_dh=None, out_dw=None, out_db=None, out4=None):
+    """Fused Dense(N<=32) + sparse-CE (+accuracy) + backward of that Dense. Returns (out4, out, dh, dw, db)."""
+    L = load()
+    _f32c(h, "h"); _f32c(w, "w")
+    M, K = h.shape
+    N = w.shape[1]
+    dev = h.device
+    labels = labels.reshape(-1)
+    if labels.dtype not in (torch.int64, torch.int32):
+        raise TypeError("labels must be int32/int64")
+    wsp = Workspace.current(dev)
+    if L.tfde_head_ws_floats(M, K, N) > wsp.ws.numel():
+        raise RuntimeError("head workspace too small")
+    dh = (out_dh if out_dh is not None else torch.empty((M, K), dtype=torch.float32, device=dev)) if need_dh else None
+    dw = out_dw if out_dw is not None else torch.empty((K, N), dtype=torch.float32, device=dev)
+    db = None
+    if bias is not None:
+        db = out_db if out_db is not None else torch.empty((N,), dtype=torch.float32, device=dev)
+    o4 = out4 if out4 is not None else torch.empty((4,), dtype=torch.float32, device=dev)
+    check(L.tfde_head_fwd_bwd(h.data_ptr(), w.data_ptr(), ptr(bias), labels.data_ptr(),
+                              1 if labels.dtype == torch.int64 else 0, ptr(out), ptr(dh), dw.data_ptr(), ptr(db),
+                              o4.data_ptr(), M, K, N, 1 if relu_mask else 0, 1 if from_probs else 0, scale,
+                              wsp.ws.data_ptr(), wsp.counters.data_ptr(), stream_ptr()), "head_fwd_bwd")
+    return o4, out, dh, dw, db
