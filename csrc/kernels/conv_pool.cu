@@ -193,9 +193,9 @@ TFDE_API int tfde_conv3x3c1_relu_pool_bwd(const void* x, int x_is_u8, float in_s
                                           int Cout, cudaStream_t stream) {
   if (Cout != 32 || H < 4 || W < 4) return TFDE_ERR_INVALID;
   const int PH = (H - 2) / 2, PW = (W - 2) / 2;
-  long blocks = ((long)Bn * PH * PW + WARPS * 8 - 1) / (WARPS * 8);  // >= 8 pixels per warp
+  long blocks = ((long)Bn * PH * PW + WARPS * 4 - 1) / (WARPS * 4);  // >= 4 pixels per warp
   if (blocks < 1) blocks = 1;
-  if (blocks > 148L) blocks = 148L;
+  if (blocks > 148L * 2) blocks = 148L * 2;
   const int grid = (int)blocks;
   if (x_is_u8)
     conv3x3c1_relu_pool_bwd_kernel<true><<<grid, WARPS * 32, 0, stream>>>(x, pooled, idx, dpooled, dw, db, partials, counter, Bn, H, W, PH, PW, in_scale);

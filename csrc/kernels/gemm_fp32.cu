@@ -180,9 +180,12 @@ template <> struct BLoader<B_WROT> {  // B_op[(kh,kw,co), ci] = W[kh,kw,ci,co]
 // ------------------------------------------------------------------------------------------
 // The kernel. grid = (tiles_n, tiles_m, splits); 256 threads; each thread owns TM x TN outputs.
 // ------------------------------------------------------------------------------------------
-template <int AM, int BM_, int BMODE, int BN_, int TM, int TN>
+template <int AM, int BM_, int BMODE, int BN_, int TM, int TN, int BK_ = 16>
 __global__ void __launch_bounds__(NTHREADS) gemm_fp32_kernel(const GemmParams p) {
   static_assert((BM_ / TM) * (BN_ / TN) == NTHREADS, "tile/thread mismatch");
+  // k-tile depth of this instantiation (shadows the file-level default). BK_ = 64 is used when the whole
+  // reduction fits one tile (K <= 64: the batch-64 wgrad/dgrad GEMMs) so every load is in flight at once.
+  constexpr int BK = BK_;
   constexpr int APAD = 4;
   __shared__ __align__(16) float As[BK][BM_ + APAD];
   __shared__ __align__(16) float Bs[BK][BN_ + APAD];
@@ -360,7 +363,10 @@ int launch_cfg(const GemmParams& p, cudaStream_t stream) {
     gemm_fp32_kernel<AM, 128, BMODE, 32, 4, 4><<<grid, NTHREADS, 0, stream>>>(p);
   } else {
     dim3 grid((p.N + 63) / 64, (p.M + 63) / 64, p.splits);
-    gemm_fp32_kernel<AM, 64, BMODE, 64, 4, 4><<<grid, NTHREADS, 0, stream>>>(p);
+    if (p.K <= 64 && p.splits == 1 && (AM == A_DENSE || AM == A_DENSE_T))
+      gemm_fp32_kernel<AM, 64, BMODE, 64, 4, 4, 64><<<grid, NTHREADS, 0, stream>>>(p);   // one deep k tile
+    else
+      gemm_fp32_kernel<AM, 64, BMODE, 64, 4, 4><<<grid, NTHREADS, 0, stream>>>(p);
   }
   TFDE_RETURN_LAUNCH_STATUS();
 }
@@ -372,6 +378,7 @@ int tile_n_for(int N) { return N <= 16 ? 16 : (N <= 32 ? 32 : 64); }
 int choose_splits(int M, int N, int K, size_t ws_bytes, int max_tiles_counters) {
   const int tiles = ((M + tile_m_for(N) - 1) / tile_m_for(N)) * ((N + tile_n_for(N) - 1) / tile_n_for(N));
   if (tiles > max_tiles_counters) return 1;
+  if (K <= 64) return 1;   // one deep k tile covers the whole reduction: nothing to split
   const int ktiles = (K + BK - 1) / BK;
   // exposed-latency model: main loop ~ (ktiles/s) dependent tile loads, reduction ~ s/4 dependent L2
   // round trips  =>  s ~ 2*sqrt(ktiles), capped by the SM count and by >= 2 k-tiles per split.

@@ -157,7 +157,7 @@ dense_skinny_fwd_kernel(const SkinnyParams p) {
 // ================================================================================================
 // 2. fused classifier head: Dense(N<=32) + softmax cross-entropy + backward of that Dense
 // ================================================================================================
-constexpr int HD_ROWS = 64;      // rows of h per block
+constexpr int HD_ROWS_MAX = 64;  // max rows of h per block (small batches use 16 for more CTAs)
 constexpr int HD_THREADS = 256;
 constexpr int HD_NMAX = 32;
 
@@ -170,16 +170,18 @@ struct HeadParams {
   int M, K, N;
   int relu_mask;     // multiply dh by (h > 0) (the producing layer had a fused ReLU)
   int from_probs;
+  int rpb;           // rows per block (16 or 64)
   float scale;
   float* partials;   // [gridDim.x][K*N + N + 2]
   unsigned* counter;
 };
 
-// dynamic shared memory: hs[HD_ROWS][K+1] | wsm[K][N] | zs[HD_ROWS][N] (logits -> probs -> dz) | red
+// dynamic shared memory: hs[rpb][K+1] | wsm[K][N] | zs[rpb][N] (logits -> probs -> dz) | bias | red
 __global__ void __launch_bounds__(HD_THREADS)
 head_fwd_bwd_kernel(const HeadParams p) {
   extern __shared__ __align__(16) float hsm[];
   const int K = p.K, N = p.N, KP = K + 1;
+  const int HD_ROWS = p.rpb;
   float* hs = hsm;
   float* wsm = hs + HD_ROWS * KP;
   float* zs = wsm + K * N;
@@ -305,9 +307,10 @@ head_fwd_bwd_kernel(const HeadParams p) {
   if (t == 0) { p.out4[2] = (float)p.M; p.out4[3] = 0.f; *p.counter = 0u; }
 }
 
-size_t head_smem_bytes(int K, int N) {
-  return ((size_t)HD_ROWS * (K + 1) + (size_t)K * N + (size_t)HD_ROWS * N + N + 16) * sizeof(float);
+size_t head_smem_bytes(int K, int N, int rpb = HD_ROWS_MAX) {
+  return ((size_t)rpb * (K + 1) + (size_t)K * N + (size_t)rpb * N + N + 16) * sizeof(float);
 }
+int head_rows_per_block(int M) { return M <= 256 ? 16 : HD_ROWS_MAX; }
 
 }  // namespace
 
@@ -353,7 +356,8 @@ TFDE_API int tfde_head_supported(int K, int N) {
   return (N >= 1 && N <= HD_NMAX && K >= 1 && head_smem_bytes(K, N) <= 200 * 1024) ? 1 : 0;
 }
 TFDE_API size_t tfde_head_ws_floats(int M, int K, int N) {
-  return (size_t)((M + HD_ROWS - 1) / HD_ROWS) * ((size_t)K * N + N + 2);
+  const int rpb = head_rows_per_block(M);
+  return (size_t)((M + rpb - 1) / rpb) * ((size_t)K * N + N + 2);
 }
 
 // Fused Dense(N) + sparse categorical cross-entropy (+accuracy) + backward of the Dense.
@@ -364,15 +368,16 @@ TFDE_API int tfde_head_fwd_bwd(const float* h, const float* w, const float* bias
                                int M, int K, int N, int relu_mask, int from_probs, float scale,
                                float* partials, unsigned* counter, cudaStream_t stream) {
   if (!tfde_head_supported(K, N) || M <= 0) return TFDE_ERR_INVALID;
-  const size_t smem = head_smem_bytes(K, N);
+  const int rpb = head_rows_per_block(M);
+  const size_t smem = head_smem_bytes(K, N, rpb);
   static size_t configured = 48 * 1024;
   if (smem > configured) {
     const cudaError_t e = cudaFuncSetAttribute(head_fwd_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     configured = smem;
   }
-  HeadParams p{h, w, bias, labels, label_is_i64, out, dh, dw, db, out4, M, K, N, relu_mask, from_probs, scale,
+  HeadParams p{h, w, bias, labels, label_is_i64, out, dh, dw, db, out4, M, K, N, relu_mask, from_probs, rpb, scale,
                partials, counter};
-  head_fwd_bwd_kernel<<<(M + HD_ROWS - 1) / HD_ROWS, HD_THREADS, smem, stream>>>(p);
+  head_fwd_bwd_kernel<<<(M + rpb - 1) / rpb, HD_THREADS, smem, stream>>>(p);
   TFDE_RETURN_LAUNCH_STATUS();
 }

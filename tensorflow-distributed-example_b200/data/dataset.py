@@ -274,8 +274,53 @@ class Dataset:
             return src, mk_shard
         return None
 
+    # ---- native (C++) fast path -------------------------------------------------------------------
+    def _native_iter(self):
+        """``source [-> shard] [-> shuffle] [-> repeat] -> batch [-> prefetch]`` over plain arrays runs in
+        the C++ runtime (background thread + prefetch ring). Returns None when the chain does not match or
+        the runtime library is not built."""
+        from . import native_pipeline as npipe
+        if not npipe.available():
+            return None
+        chain = [d for d in self._chain() if d.kind not in ("options", "cache")]
+        depth = 2
+        if chain and chain[-1].kind == "prefetch":
+            depth = min(max(2, chain[-1].p["depth"]), 64)
+            chain = chain[:-1]
+        kinds = [d.kind for d in chain]
+        if len(kinds) < 2 or kinds[0] != "source" or kinds[-1] != "batch":
+            return None
+        mid = kinds[1:-1]
+        allowed = ["shard", "shuffle", "repeat"]
+        if any(k not in allowed for k in mid) or [k for k in allowed if k in mid] != mid:
+            return None
+        src = chain[0].p["src"]
+        if len(src.arrays) > 2:
+            return None
+        node = {d.kind: d for d in chain}
+        shuffle = node.get("shuffle")
+        repeat = node.get("repeat")
+        shard = node.get("shard")
+        seed = None
+        if shuffle is not None and shuffle.p["seed"] is not None:
+            seed = (int(shuffle.p["seed"]) * 1000003 + (shuffle._epoch if shuffle.p["reshuffle"] else 0)) & (2 ** 63 - 1)
+            shuffle._epoch += 1
+        rep = 1 if repeat is None else (-1 if repeat.p["count"] is None else int(repeat.p["count"]))
+        try:
+            return npipe.NativeBatchIterator(
+                src.arrays[0], src.arrays[1] if len(src.arrays) == 2 else None, node["batch"].p["batch"],
+                shuffle_buffer=0 if shuffle is None else shuffle.p["buffer"], seed=seed, repeat=rep,
+                drop_remainder=node["batch"].p["drop"], depth=depth,
+                shard_num=1 if shard is None else shard.p["num"], shard_index=0 if shard is None else shard.p["index"])
+        except (TypeError, OSError, RuntimeError):
+            return None
+
     # ---- iteration ----------------------------------------------------------------------------
     def __iter__(self):
+        if self.kind in ("batch", "prefetch", "options"):
+            it = self._native_iter()
+            if it is not None:
+                return it
         return self._iter()
 
     def _iter(self):

@@ -122,3 +122,42 @@ def test_mnist_sources_shapes():
     dsets, info = tf.data.mnist.load("mnist", with_info=True, as_supervised=True, n_train=256, n_test=64)
     img, lab = next(iter(dsets["train"]))
     assert img.shape == (28, 28, 1) and info.splits["train"] == 256
+
+
+def test_native_pipeline_matches_python_semantics():
+    from tfde_b200.data import native_pipeline as npipe
+    if not npipe.available():
+        pytest.skip("runtime library not built")
+    x = np.arange(103 * 3, dtype=np.float32).reshape(103, 3)
+    y = np.arange(103, dtype=np.int64)
+    ds = Dataset.from_tensor_slices((x, y)).shuffle(20, seed=5).repeat(2).batch(10).prefetch(4)
+    it = iter(ds)
+    assert type(it).__name__ == "NativeBatchIterator"
+    batches = list(it)
+    assert [len(b[1]) for b in batches] == [10] * 20 + [6]
+    labels = np.concatenate([np.asarray(b[1]) for b in batches])
+    feats = np.concatenate([np.asarray(b[0]) for b in batches])
+    assert sorted(labels[:103].tolist()) == list(range(103)) and sorted(labels[103:].tolist()) == list(range(103))
+    assert np.array_equal(feats[:, 0], labels * 3), "rows of every component stay aligned"
+    for pos, v in enumerate(labels[:103]):
+        assert v <= pos + 20, "windowed shuffle: element i cannot appear before position i - buffer"
+    assert labels[:103].tolist() != labels[103:].tolist(), "reshuffled each epoch"
+    # same seed -> same first-epoch order on a fresh dataset; shard + drop_remainder
+    ds2 = Dataset.from_tensor_slices((x, y)).shuffle(20, seed=5).repeat(2).batch(10).prefetch(4)
+    assert np.concatenate([np.asarray(b[1]) for b in ds2])[:103].tolist() == labels[:103].tolist()
+    ds3 = Dataset.from_tensor_slices((x, y)).shard(4, 1).batch(8, drop_remainder=True)
+    got = [np.asarray(b[1]).tolist() for b in ds3]
+    assert got == [list(range(1, 32, 4)), list(range(33, 64, 4)), list(range(65, 96, 4))]
+    # infinite repeat terminates cleanly when the consumer stops early
+    it4 = iter(Dataset.from_tensor_slices((x, y)).shuffle(1000).repeat().batch(16).prefetch(100))
+    for _ in range(30):
+        xb, yb = next(it4)
+        assert xb.shape == (16, 3)
+    it4.close()
+
+
+def test_python_fallback_when_native_disabled(monkeypatch):
+    monkeypatch.setenv("TFDE_NATIVE_PIPELINE", "0")
+    ds = _ds(10).shuffle(4, seed=1).batch(4)
+    assert type(iter(ds)).__name__ == "generator"
+    assert [len(b[0]) for b in ds] == [4, 4, 2]
