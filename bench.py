@@ -197,16 +197,17 @@ def run_ours(args):
     torch.cuda.synchronize()
     sampler.start()
     with torch.cuda.stream(stream):
+        step_graph = model.device_step_graph(st, gb) if model.use_cuda_graph else None
         for i in range(K):
             if flush is not None:
                 flush.fill_(i & 0xFF)
             starts[i].record(stream)
-            if st.graph is not None:
-                st.graph.replay()
+            if step_graph is not None:
+                step_graph.replay()
             else:
                 model._step_body(st.in_x, st.in_y, gb)
             ends[i].record(stream)
-    model.optimizer.iterations += K if st.graph is not None else 0
+    model.optimizer.iterations += K if step_graph is not None else 0
     torch.cuda.synchronize()
     barrier(world)
     clocks = sampler.stop()
@@ -237,7 +238,7 @@ def run_ours(args):
         "dtype": "fp32", "data": "synthetic", "impl": "ours",
         "config": {"model": "keras_mnist_cnn_conv32_pool_dense64_dense10" if args.model == "a" else "model_b_bn_cnn",
                    "global_batch": gb, "per_gpu_batch": B, "seq_len": None, "input": list(in_shape),
-                   "parallelism": f"dp{world}", "optimizer": args.optimizer, "cuda_graph": st.graph is not None,
+                   "parallelism": f"dp{world}", "optimizer": args.optimizer, "cuda_graph": model.graph_captured,
                    "l2": "flushed between timed steps (256 MiB write outside the event pairs)"
                          if not args.no_flush else "not flushed",
                    "allreduce": "fused p2p one/two-shot + optimizer (no NCCL on step path)" if world > 1 else "n/a"},

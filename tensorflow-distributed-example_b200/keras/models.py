@@ -46,12 +46,25 @@ def _fresh_seed() -> int:
     return int.from_bytes(os.urandom(4), "little")
 
 
+class _Slot:
+    """Pinned host staging for one in-flight step (inputs in, metrics tail out) + its captured graph."""
+
+    def __init__(self, x_shape, x_dtype, batch):
+        self.host_x = torch.empty(x_shape, dtype=x_dtype).pin_memory()
+        self.host_y = torch.empty((batch,), dtype=torch.int64).pin_memory()
+        self.host_tail = torch.zeros(4, dtype=torch.float32).pin_memory()
+        self.graph = None
+        self.event = None
+
+
 class _GraphState:
     def __init__(self):
         self.in_x = None
         self.in_y = None
         self.eager_steps = 0
-        self.graph = None
+        self.graph = None      # step only (device-resident inputs)
+        self.slots = None      # two _Slot: step + H2D/D2H staging
+        self.turn = 0
 
 
 class Sequential:
@@ -357,31 +370,63 @@ class Sequential:
                 xdtype = torch.float32
             st.in_x = torch.empty((b,) + tuple(x.shape[1:]), dtype=xdtype, device=self.device)
             st.in_y = torch.empty((b,), dtype=torch.int64, device=self.device)
+            st.slots = [_Slot(tuple(st.in_x.shape), xdtype, b) for _ in range(2)]
             self._graphs[key] = st
         if isinstance(x, np.ndarray):
             x = torch.from_numpy(x)
         if isinstance(y, np.ndarray):
             y = torch.from_numpy(y)
+        yy = y.reshape(-1)
         with torch.cuda.stream(self._stream):
             ops.native.Workspace.current(self.device)
-            st.in_x.copy_(x if x.dtype == st.in_x.dtype else x.to(st.in_x.dtype), non_blocking=True)
-            yy = y.reshape(-1)
-            st.in_y.copy_(yy if yy.dtype == torch.int64 else yy.to(torch.int64), non_blocking=True)
-            if st.graph is not None:
-                st.graph.replay()
+            graph_mode = self.use_cuda_graph and st.eager_steps >= self.graph_warmup_steps
+            if graph_mode and not x.is_cuda:
+                # Steady state, host inputs: ONE launch per step. The captured graph starts with the H2D
+                # copies out of a pinned staging slot and ends with a D2H copy of the 4-float metrics tail
+                # into pinned memory; two slots alternate so the host can fill slot k+1 while step k runs.
+                slot = st.slots[st.turn & 1]
+                st.turn += 1
+                if slot.event is not None:
+                    slot.event.synchronize()       # the step that last used this slot has finished
+                slot.host_x.copy_(x)
+                slot.host_y.copy_(yy)
+                if slot.graph is None:
+                    it0 = self.optimizer.iterations
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=self._stream):
+                        st.in_x.copy_(slot.host_x, non_blocking=True)
+                        st.in_y.copy_(slot.host_y, non_blocking=True)
+                        self._step_body(st.in_x, st.in_y, gb)
+                        slot.host_tail.copy_(self.arena.tail, non_blocking=True)
+                    self.optimizer.iterations = it0   # capture did not execute anything
+                    slot.graph = g
+                    slot.event = torch.cuda.Event()
+                slot.graph.replay()
+                slot.event.record(self._stream)
+                self._host_tail = slot.host_tail
                 self.optimizer.iterations += 1
-            elif not self.use_cuda_graph or st.eager_steps < self.graph_warmup_steps:
+                return
+            st.in_x.copy_(x if x.dtype == st.in_x.dtype else x.to(st.in_x.dtype), non_blocking=True)
+            st.in_y.copy_(yy if yy.dtype == torch.int64 else yy.to(torch.int64), non_blocking=True)
+            self._host_tail = None
+            if graph_mode:
+                self.device_step_graph(st, gb).replay()
+                self.optimizer.iterations += 1
+            else:
                 self._step_body(st.in_x, st.in_y, gb)
                 st.eager_steps += 1
-            else:
-                it0 = self.optimizer.iterations
-                g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g, stream=self._stream):
-                    self._step_body(st.in_x, st.in_y, gb)
-                self.optimizer.iterations = it0   # capture did not execute anything
-                st.graph = g
-                g.replay()
-                self.optimizer.iterations += 1
+
+    def device_step_graph(self, st, gb):
+        """CUDA graph of the step alone (inputs already in the static device buffers): used for device
+        inputs and by bench.py's device-timed region."""
+        if st.graph is None:
+            it0 = self.optimizer.iterations
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=self._stream):
+                self._step_body(st.in_x, st.in_y, gb)
+            self.optimizer.iterations = it0
+            st.graph = g
+        return st.graph
 
     def sync(self):
         if self.device.type == "cuda":
@@ -410,6 +455,8 @@ class Sequential:
     def last_step_loss(self) -> float:
         """Loss of the most recent step (global mean); forces a device->host read."""
         self.sync()
+        if getattr(self, "_host_tail", None) is not None:
+            return float(self._host_tail[0])     # already on the host: the graph's last node copied it
         return float(self.arena.tail[0].item())
 
     # ------------------------------------------------------------------------------------------
@@ -575,10 +622,20 @@ class Sequential:
         from ..ckpt.checkpoint import load_weights
         load_weights(self, path)
 
+    @property
+    def graph_captured(self) -> bool:
+        """True once a CUDA graph of the training step exists (either flavour)."""
+        for v in self._graphs.values():
+            if isinstance(v, _GraphState) and (v.graph is not None or any(sl.graph is not None for sl in v.slots or [])):
+                return True
+        return False
+
     def invalidate_graphs(self):
-        """Drop captured CUDA graphs (e.g. after set_weights changed nothing address-wise this is not
-        needed; it is needed only if buffers were re-allocated)."""
-        for k, v in list(self._graphs.items()):
+        """Drop captured CUDA graphs (needed only if buffers were re-allocated; weight updates through
+        set_weights/load_weights keep all addresses and need no re-capture)."""
+        for v in self._graphs.values():
             if isinstance(v, _GraphState):
                 v.graph = None
                 v.eager_steps = 0
+                for sl in v.slots or []:
+                    sl.graph = None

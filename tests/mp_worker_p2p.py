@@ -125,7 +125,7 @@ def check_model(strategy, graph):
     close = all(np.allclose(a, b, rtol=5e-3, atol=2e-4) for a, b in zip(m.get_weights(), mc.get_weights()))
     if not close:
         print(f"[rank {rank}] FAIL model weights differ from cpu reference", flush=True)
-    if graph and not any(getattr(v, "graph", None) is not None for v in m._graphs.values()):
+    if graph and not m.graph_captured:
         print(f"[rank {rank}] FAIL graph not captured", flush=True)
         ok = False
     return ok and same and close
