@@ -12,7 +12,9 @@
 //   dgrad    dx = dy . W^T       A = dy [M,N],        B = W   [K,N]   (Keras (in,out) layout as stored)
 //   wgrad    dW = x^T . dy       A = x^T [K,M],       B = dy^T [N,M]
 //
-// Structure (one 128 x BN output tile per CTA, 192 threads):
+// Structure (one (128*MT) x BN output tile per CTA, 192 threads; MT = 2 for large problems: two M=128
+// accumulators share every B tile, which cuts L2->SM operand traffic per FLOP by a third -- at 8192^3 the
+// MT=1 kernel measured 0.90 PFLOP/s and was bound by exactly that traffic):
 //   warp 0      TMA producer: one elected lane arms full[s] with expect_tx and issues two bulk tensor
 //               loads per k-block into a 4-stage ring (A: 128x64 bf16 = 16 KB, B: BNx64 bf16)
 //   warp 1      allocates BN TMEM columns; one elected lane issues 4 x tcgen05.mma (K=16 each) per
@@ -101,35 +103,38 @@ struct TcEpilogue {
   int M, N;
 };
 
-template <int BN>
+template <int BN, int MT>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const TcEpilogue ep, const int K) {
-  constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2;   // 16 KB
+  constexpr uint32_t A_SUB_BYTES = TC_BM * TC_BK * 2;   // 16 KB per 128-row sub-tile
+  constexpr uint32_t A_BYTES = A_SUB_BYTES * MT;
   constexpr uint32_t B_BYTES = BN * TC_BK * 2;
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr int STAGES = (MT == 2) ? 3 : TC_STAGES;
+  constexpr uint32_t TMEM_COLS = (BN * MT <= 32) ? 32 : (BN * MT <= 64 ? 64 : (BN * MT <= 128 ? 128 : (BN * MT <= 256 ? 256 : 512)));
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by the 128-byte swizzle atoms (base_offset field left at 0)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  __shared__ __align__(8) uint64_t full_bar[TC_STAGES];
-  __shared__ __align__(8) uint64_t empty_bar[TC_STAGES];
+  __shared__ __align__(8) uint64_t full_bar[STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[STAGES];
   __shared__ __align__(8) uint64_t tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * TC_BM, n0 = blockIdx.x * BN;
+  const int m0 = blockIdx.y * (TC_BM * MT), n0 = blockIdx.x * BN;
   const int num_k = (K + TC_BK - 1) / TC_BK;
 
   if (threadIdx.x == 0) {
 #pragma unroll
-    for (int s = 0; s < TC_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     mbar_init(&tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
   }
   if (warp == 1) {   // whole warp: allocate BN TMEM columns (power of two >= 32), publish the base address
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"((uint32_t)BN) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   tc_fence_before();
@@ -140,8 +145,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   if (warp == 0) {
     if (lane == 0) {
       for (int kb = 0; kb < num_k; ++kb) {
-        const int s = kb % TC_STAGES;
-        const uint32_t ph = (uint32_t)(kb / TC_STAGES) & 1u;
+        const int s = kb % STAGES;
+        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
         mbar_wait(&empty_bar[s], ph ^ 1u);            // slot free (fresh barrier: passes immediately)
         mbar_expect_tx(&full_bar[s], STAGE_BYTES);
         uint8_t* a_dst = smem + (size_t)s * STAGE_BYTES;
@@ -153,63 +158,59 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     if (lane == 0) {
       const uint32_t idesc = make_instr_desc(TC_BM, BN);
       for (int kb = 0; kb < num_k; ++kb) {
-        const int s = kb % TC_STAGES;
-        const uint32_t ph = (uint32_t)(kb / TC_STAGES) & 1u;
+        const int s = kb % STAGES;
+        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
         mbar_wait(&full_bar[s], ph);                  // TMA bytes have landed
         tc_fence_after();
         const uint32_t a_addr = smem_u32(smem + (size_t)s * STAGE_BYTES);
         const uint32_t b_addr = a_addr + A_BYTES;
 #pragma unroll
-        for (int k = 0; k < TC_BK / UMMA_K; ++k) {
-          // advancing K by 16 bf16 = 32 bytes inside the 128-byte swizzle row: bump the start address
-          const uint64_t da = make_smem_desc(a_addr + k * UMMA_K * 2);
-          const uint64_t db = make_smem_desc(b_addr + k * UMMA_K * 2);
-          umma_bf16(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+        for (int mt = 0; mt < MT; ++mt) {
+#pragma unroll
+          for (int k = 0; k < TC_BK / UMMA_K; ++k) {
+            // advancing K by 16 bf16 = 32 bytes inside the 128-byte swizzle row: bump the start address
+            const uint64_t da = make_smem_desc(a_addr + mt * A_SUB_BYTES + k * UMMA_K * 2);
+            const uint64_t db = make_smem_desc(b_addr + k * UMMA_K * 2);
+            umma_bf16(tmem_d + (uint32_t)(mt * BN), da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
         }
         umma_commit(&empty_bar[s]);                   // stage reusable once these MMAs have read it
       }
       umma_commit(&tmem_full_bar);                    // accumulator complete
     }
   } else {
-    // epilogue warps 2..5: TMEM lane quarter = warp % 4
+    // epilogue warps 2..5: TMEM lane quarter = warp % 4. Once tmem_full fires every MMA has finished
+    // reading shared memory, so the pipeline stages are free: each warp transposes its 32x32 chunk through
+    // a private padded tile there and stores full 128-byte (fp32) / 64-byte (bf16) row segments.
     mbar_wait(&tmem_full_bar, 0);
     tc_fence_after();
     const int q = warp & 3;
-    const int row = m0 + q * 32 + lane;
+    float* tile = reinterpret_cast<float*>(smem) + (size_t)(warp - 2) * (32 * 33);
 #pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
-      if (row < ep.M) {
+    for (int mt = 0; mt < MT; ++mt) {
+      const int row0 = m0 + mt * TC_BM + q * 32;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
         const int nbase = n0 + c0;
-        if (ep.c_f32 != nullptr) {
-          float* dst = ep.c_f32 + (size_t)row * ep.ldc + nbase;
-          const bool vec = (nbase + 32 <= ep.N) && ((ep.ldc & 3) == 0);
+        if (nbase >= ep.N) break;
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(mt * BN + c0), r);
+        __syncwarp();
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            float v[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              float x = __uint_as_float(r[j + u]);
-              if (ep.bias != nullptr && nbase + j + u < ep.N) x += __ldg(ep.bias + nbase + j + u);
-              if (ep.relu) x = fmaxf(x, 0.f);
-              v[u] = x;
-            }
-            if (vec) *reinterpret_cast<float4*>(dst + j) = make_float4(v[0], v[1], v[2], v[3]);
-            else {
-#pragma unroll
-              for (int u = 0; u < 4; ++u) if (nbase + j + u < ep.N) dst[j + u] = v[u];
-            }
-          }
-        }
-        if (ep.c_bf16 != nullptr) {
-          __nv_bfloat16* dst = ep.c_bf16 + (size_t)row * ep.ldc + nbase;
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float x = __uint_as_float(r[j]);
-            if (ep.bias != nullptr && nbase + j < ep.N) x += __ldg(ep.bias + nbase + j);
-            if (ep.relu) x = fmaxf(x, 0.f);
-            if (nbase + j < ep.N) dst[j] = __float2bfloat16(x);
+        for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = __uint_as_float(r[j]);   // row = lane, col = j
+        __syncwarp();
+        const int col = nbase + lane;
+        const bool col_ok = col < ep.N;
+        const float bv = (ep.bias != nullptr && col_ok) ? __ldg(ep.bias + col) : 0.f;
+#pragma unroll 4
+        for (int rr = 0; rr < 32; ++rr) {
+          const int row = row0 + rr;
+          if (row >= ep.M) break;
+          float x = tile[rr * 33 + lane] + bv;
+          if (ep.relu) x = fmaxf(x, 0.f);
+          if (col_ok) {
+            if (ep.c_f32 != nullptr) ep.c_f32[(size_t)row * ep.ldc + col] = x;
+            if (ep.c_bf16 != nullptr) ep.c_bf16[(size_t)row * ep.ldc + col] = __float2bfloat16(x);
           }
         }
       }
@@ -220,7 +221,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)BN) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
   }
 }
 
@@ -286,17 +287,18 @@ int make_map(CUtensorMap* map, const void* ptr, long rows, long cols, int box_ro
   return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
 }
 
-template <int BN>
+template <int BN, int MT>
 int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcEpilogue& ep, int M, int N, int K, cudaStream_t stream) {
-  constexpr size_t smem = (size_t)TC_STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + 1024;
+  constexpr int STAGES = (MT == 2) ? 3 : TC_STAGES;
+  constexpr size_t smem = (size_t)STAGES * (MT * TC_BM * TC_BK * 2 + BN * TC_BK * 2) + 1024;
   static bool configured = false;
   if (!configured) {
-    const cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     configured = true;
   }
-  dim3 grid((N + BN - 1) / BN, (M + TC_BM - 1) / TC_BM);
-  gemm_bf16_tcgen05_kernel<BN><<<grid, TC_THREADS, smem, stream>>>(ta, tb, ep, K);
+  dim3 grid((N + BN - 1) / BN, (M + TC_BM * MT - 1) / (TC_BM * MT));
+  gemm_bf16_tcgen05_kernel<BN, MT><<<grid, TC_THREADS, smem, stream>>>(ta, tb, ep, K);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
@@ -310,15 +312,19 @@ TFDE_API int tfde_gemm_bf16_tn(const void* A, const void* B, float* c_f32, void*
   if (M <= 0 || N <= 0 || K <= 0 || (K & 7) || !A || !B || (!c_f32 && !c_bf16)) return TFDE_ERR_INVALID;
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return TFDE_ERR_INVALID;
   const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+  // two stacked M=128 accumulators per CTA when the grid still fills the machine (>= 2 waves of 148 SMs)
+  const long tiles256 = (long)((M + 255) / 256) * ((N + BN - 1) / BN);
+  const int MT = (BN == 256 && tiles256 >= 2 * 148) ? 2 : 1;
   CUtensorMap ta, tb;
-  int rc = make_map(&ta, A, M, K, TC_BM);
+  int rc = make_map(&ta, A, M, K, TC_BM * MT);
   if (rc != 0) return rc;
   rc = make_map(&tb, B, N, K, BN);
   if (rc != 0) return rc;
   TcEpilogue ep{c_f32, (__nv_bfloat16*)c_bf16, ldc, bias, relu, M, N};
-  if (BN == 64) return launch_tc<64>(ta, tb, ep, M, N, K, stream);
-  if (BN == 128) return launch_tc<128>(ta, tb, ep, M, N, K, stream);
-  return launch_tc<256>(ta, tb, ep, M, N, K, stream);
+  if (BN == 64) return launch_tc<64, 1>(ta, tb, ep, M, N, K, stream);
+  if (BN == 128) return launch_tc<128, 1>(ta, tb, ep, M, N, K, stream);
+  if (MT == 2) return launch_tc<256, 2>(ta, tb, ep, M, N, K, stream);
+  return launch_tc<256, 1>(ta, tb, ep, M, N, K, stream);
 }
 
 TFDE_API int tfde_cast_bf16(const float* x, void* y, long n, cudaStream_t stream) {
