@@ -404,6 +404,7 @@ class Sequential:
                 slot.graph.replay()
                 slot.event.record(self._stream)
                 self._host_tail = slot.host_tail
+                self._prev_slot, self._last_slot = getattr(self, "_last_slot", None), slot
                 self.optimizer.iterations += 1
                 return
             st.in_x.copy_(x if x.dtype == st.in_x.dtype else x.to(st.in_x.dtype), non_blocking=True)
@@ -452,11 +453,16 @@ class Sequential:
                 self.arena.metrics.zero_()
         return out
 
-    def last_step_loss(self) -> float:
-        """Loss of the most recent step (global mean); forces a device->host read."""
-        self.sync()
+    def last_step_loss(self, lag: int = 0) -> float:
+        """Loss (global mean) of the most recent step, or -- ``lag=1`` -- of the step before it, which lets a
+        loop read EVERY step's loss one step late while the next step is already running on the GPU."""
         if getattr(self, "_host_tail", None) is not None:
-            return float(self._host_tail[0])     # already on the host: the graph's last node copied it
+            # already on the host: the graph's last node copied it into the slot's pinned tail
+            slot = self._last_slot if lag == 0 else self._prev_slot
+            if slot is not None:
+                slot.event.synchronize()         # waits for THAT step only; later steps keep running
+                return float(slot.host_tail[0])
+        self.sync()
         return float(self.arena.tail[0].item())
 
     # ------------------------------------------------------------------------------------------
