@@ -27,7 +27,7 @@ def run(args, METRIC, ClockSampler, max_over_ranks, barrier, dist_env, make_batc
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1 and not dist.is_initialized():
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("cpu:gloo,cuda:nccl", device_id=dev)
     torch.backends.cudnn.benchmark = True
     torch.manual_seed(1234)
     model = build_model_a(torch).to(dev).to(memory_format=torch.channels_last)

@@ -52,6 +52,8 @@ def parse_args():
     ap.add_argument("--model", default="a", choices=["a", "b"])
     ap.add_argument("--batch-per-gpu", type=int, default=64)
     ap.add_argument("--optimizer", default="sgd", choices=["sgd", "momentum", "adam"])
+    ap.add_argument("--dtype", default="fp32", choices=["fp32", "bf16"],
+                    help="bf16 = mixed_bfloat16 policy: large Dense layers on the tcgen05 GEMM (BASELINE.json config 3)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
     return ap.parse_args()
@@ -157,6 +159,8 @@ def run_ours(args):
         raise SystemExit("strategy did not initialise the process group")
     B = args.batch_per_gpu
     gb = B * world
+    if args.dtype == "bf16":
+        tf.keras.mixed_precision.set_global_policy("mixed_bfloat16")
     with strategy.scope():
         opt = {"sgd": lambda: tf.keras.optimizers.SGD(0.001),
                "momentum": lambda: tf.keras.optimizers.SGD(0.001, momentum=0.9),
@@ -241,7 +245,8 @@ def run_ours(args):
     out = {
         "metric": METRIC, "value": value, "unit": "images/sec", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "fp32", "data": "synthetic", "impl": "ours",
+        "dtype": "fp32" if args.dtype == "fp32" else "bf16 (mixed: fp32 master weights, tcgen05 dense GEMMs)",
+        "data": "synthetic", "impl": "ours",
         "config": {"model": "keras_mnist_cnn_conv32_pool_dense64_dense10" if args.model == "a" else "model_b_bn_cnn",
                    "global_batch": gb, "per_gpu_batch": B, "seq_len": None, "input": list(in_shape),
                    "parallelism": f"dp{world}", "optimizer": args.optimizer, "cuda_graph": model.graph_captured,

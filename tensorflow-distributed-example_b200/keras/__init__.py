@@ -19,3 +19,18 @@ class backend:
         """tf.keras.backend.set_learning_phase (mnist_keras_distributed.py:116). Training/inference is an
         explicit argument of every forward here, so this only records the value."""
         backend._learning_phase = value
+
+
+class mixed_precision:
+    """tf.keras.mixed_precision: 'mixed_bfloat16' routes large Dense layers to the tcgen05 bf16 GEMM
+    (fp32 master weights, fp32 accumulation); 'float32' (default) is the reference's precision."""
+
+    @staticmethod
+    def set_global_policy(name):
+        from ..ops import mixed
+        mixed.set_global_policy(name)
+
+    @staticmethod
+    def global_policy():
+        from ..ops import mixed
+        return mixed.global_policy()

@@ -320,16 +320,37 @@ class Dense(Layer):
         self.bias = self.add_weight("bias", (self.units,), zeros_init) if self.use_bias else None
         return out
 
+    def _mixed_bufs(self, m):
+        """bf16 staging buffers of the tensor-core path (static addresses, allocated once per batch size)."""
+        k, n = self.kernel.shape
+        bf = torch.bfloat16
+        return {"xb": self.buf("xb", (m, k), bf), "wt": self.buf("wt", (n, k), bf), "xt": self.buf("xt", (k, m), bf),
+                "dyt": self.buf("dyt", (n, m), bf), "dyb": self.buf("dyb", (m, n), bf), "wb": self.buf("wb", (k, n), bf)}
+
     def forward(self, x, training):
+        from ..ops import mixed
         b = x.shape[0]
         self._x = x
         y = self.buf("y", (b, self.units))
-        ops.dense_fwd(x, self.kernel.value, self.bias.value if self.bias else None, self.activation, out=y)
+        self._mixed = (mixed.global_policy() == "mixed_bfloat16" and self.activation in ("none", "relu")
+                       and mixed.supported(b, x.shape[1], self.units))
+        if self._mixed:
+            # bf16 operands, fp32 accumulation in TMEM (tcgen05); master weights stay fp32
+            mixed.dense_fwd(x, self.kernel.value, self.bias.value if self.bias else None, self.activation, out=y,
+                            bufs=self._mixed_bufs(b) if x.is_cuda else None)
+        else:
+            ops.dense_fwd(x, self.kernel.value, self.bias.value if self.bias else None, self.activation, out=y)
         self._y = y
         return y
 
     def backward(self, dy):
         dx = self.buf("dx", self._x.shape) if self.need_dx else None
+        if getattr(self, "_mixed", False):
+            from ..ops import mixed
+            mixed.dense_bwd(self._x, self.kernel.value, self._y, dy, self.activation, self.need_dx, self.use_bias,
+                            out_dx=dx, out_dw=self.kernel.grad, out_db=self.bias.grad if self.bias else None,
+                            bufs=self._mixed_bufs(dy.shape[0]) if dy.is_cuda else None)
+            return dx
         scratch = self.buf("dz", dy.shape) if self.activation == "softmax" else None
         ops.dense_bwd(self._x, self.kernel.value, self._y, dy, self.activation, self.need_dx, self.use_bias,
                       out_dx=dx, out_dw=self.kernel.grad, out_db=self.bias.grad if self.bias else None,

@@ -92,3 +92,18 @@ def test_fit_and_evaluate_on_gpu_learns():
 def test_graft_smoke():
     import __graft_entry__ as ge
     ge.smoke()
+
+
+def test_tiny_resnet_matches_cpu_reference():
+    """Residual blocks, BN with gamma, 7x7/s2 + 3x3/s2 'same' max-pool, GAP, Dense head on the GPU kernels."""
+    def builder():
+        m = tf.models.build_resnet((1, 2), width=8, classes=10, input_shape=(32, 32, 3), seed=13)
+        m.compile(optimizer=tf.keras.optimizers.SGD(0.05, momentum=0.9),
+                  loss=tf.keras.losses.SparseCategoricalCrossentropy(from_logits=True), metrics=["accuracy"])
+        return m
+    g = torch.Generator().manual_seed(2)
+    x = torch.rand(64, 32, 32, 3, generator=g)
+    y = torch.randint(0, 10, (64,), generator=g)
+    mc, lc = _train(builder, "cpu", 4, x, y, 16)
+    mg, lg = _train(builder, "cuda", 4, x, y, 16)
+    np.testing.assert_allclose(lg, lc, rtol=1e-2, atol=1e-3)
