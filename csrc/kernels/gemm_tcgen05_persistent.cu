@@ -1,0 +1,273 @@
+// Persistent variant of the tcgen05 bf16 GEMM (see gemm_tcgen05.cu for the operand layout and the PTX
+// helpers' rationale): one CTA per SM loops over output tiles, the TMEM accumulator is DOUBLE-BUFFERED
+// (2 x BN columns), so the epilogue of tile i (tcgen05.ld -> bias/ReLU -> coalesced stores) overlaps the
+// TMA/MMA main loop of tile i+1, and the per-CTA set-up (barrier init, TMEM allocation, tensor-map
+// prefetch) is paid once per SM instead of once per tile. This is the kernel for the many small-K /
+// output-bound GEMMs of a convolutional network (1x1 convolutions, K = 64..576), where the one-tile-per-CTA
+// kernel spends most of its time in set-up and drain.
+//
+//   C[M,N] = act( A[M,K] . B[N,K]^T + bias[N] ),  A/B bf16 K-major, C fp32 and/or bf16
+//
+// Pipelines: smem ring full[s]/empty[s] (TMA <-> MMA, STAGES deep), TMEM ring tmem_full[a]/tmem_empty[a]
+// (MMA <-> epilogue, 2 deep). Tile order is static: tile = blockIdx.x + i * gridDim.x, m-major.
+#include "common.cuh"
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <mutex>
+
+namespace {
+
+constexpr int P_BM = 128;
+constexpr int P_BK = 64;
+constexpr int P_THREADS = 192;
+constexpr int P_UMMA_K = 16;
+
+__device__ __forceinline__ uint32_t p_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void p_mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(p_smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void p_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(p_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void p_mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(p_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void p_mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(p_smem_u32(bar)), "r"(parity) : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void p_tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c_inner, int c_outer) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(p_smem_u32(dst)), "l"(map), "r"(p_smem_u32(bar)), "r"(c_inner), "r"(c_outer) : "memory");
+}
+__device__ __forceinline__ uint64_t p_smem_desc(uint32_t addr) {   // K-major, SWIZZLE_128B (see gemm_tcgen05.cu)
+  return (uint64_t)((addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+__device__ __forceinline__ void p_umma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void p_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(p_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void p_tmem_ld(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+struct PEpilogue {
+  float* c_f32; __nv_bfloat16* c_bf16; long ldc;
+  const float* bias; int relu;
+  int M, N;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(P_THREADS, 1)
+gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                                    const PEpilogue ep, const int K, const int tiles_m, const int tiles_n) {
+  constexpr uint32_t A_BYTES = P_BM * P_BK * 2;
+  constexpr uint32_t B_BYTES = BN * P_BK * 2;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr int STAGES = (BN == 256) ? 4 : 6;
+  constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;      // 128 / 256 / 512: powers of two
+  extern __shared__ __align__(1024) uint8_t p_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p_smem_raw) + 1023) & ~(uintptr_t)1023);
+  float* epi_tiles = reinterpret_cast<float*>(smem + (size_t)STAGES * STAGE_BYTES);   // 4 warps x 32x33 floats
+  __shared__ __align__(8) uint64_t full_bar[STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[STAGES];
+  __shared__ __align__(8) uint64_t tmem_full[2];
+  __shared__ __align__(8) uint64_t tmem_empty[2];
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_k = (K + P_BK - 1) / P_BK;
+  const int num_tiles = tiles_m * tiles_n;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) { p_mbar_init(&full_bar[s], 1); p_mbar_init(&empty_bar[s], 1); }
+    p_mbar_init(&tmem_full[0], 1); p_mbar_init(&tmem_full[1], 1);
+    p_mbar_init(&tmem_empty[0], 4); p_mbar_init(&tmem_empty[1], 4);    // one arrival per epilogue warp
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(p_smem_u32(&tmem_base_smem)), "r"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_d = tmem_base_smem;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;                                   // k-blocks issued so far (across tiles)
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile / tiles_n) * P_BM, n0 = (tile % tiles_n) * BN;
+        for (int kb = 0; kb < num_k; ++kb, ++it) {
+          const uint32_t s = it % STAGES, ph = (it / STAGES) & 1u;
+          p_mbar_wait(&empty_bar[s], ph ^ 1u);
+          p_mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+          uint8_t* a_dst = smem + (size_t)s * STAGE_BYTES;
+          p_tma_load_2d(a_dst, &tmA, &full_bar[s], kb * P_BK, m0);
+          p_tma_load_2d(a_dst + A_BYTES, &tmB, &full_bar[s], kb * P_BK, n0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(P_BM >> 4) << 24);
+      uint32_t it = 0, tl = 0;                           // tl: tiles done by this CTA
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
+        const uint32_t acc = tl & 1u, aph = (tl >> 1) & 1u;
+        p_mbar_wait(&tmem_empty[acc], aph ^ 1u);         // epilogue has drained this accumulator
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        for (int kb = 0; kb < num_k; ++kb, ++it) {
+          const uint32_t s = it % STAGES, ph = (it / STAGES) & 1u;
+          p_mbar_wait(&full_bar[s], ph);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t a_addr = p_smem_u32(smem + (size_t)s * STAGE_BYTES);
+          const uint32_t b_addr = a_addr + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < P_BK / P_UMMA_K; ++k)
+            p_umma(tmem_d + acc * BN, p_smem_desc(a_addr + k * P_UMMA_K * 2), p_smem_desc(b_addr + k * P_UMMA_K * 2),
+                   idesc, (kb | k) != 0 ? 1u : 0u);
+          p_commit(&empty_bar[s]);
+        }
+        p_commit(&tmem_full[acc]);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    float* tile_s = epi_tiles + (size_t)(warp - 2) * (32 * 33);
+    uint32_t tl = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
+      const uint32_t acc = tl & 1u, aph = (tl >> 1) & 1u;
+      const int m0 = (tile / tiles_n) * P_BM, n0 = (tile % tiles_n) * BN;
+      p_mbar_wait(&tmem_full[acc], aph);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const int row0 = m0 + q * 32;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        const int nbase = n0 + c0;
+        if (nbase >= ep.N) break;
+        uint32_t r[32];
+        p_tmem_ld(tmem_d + ((uint32_t)(q * 32) << 16) + acc * BN + (uint32_t)c0, r);
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) tile_s[lane * 33 + j] = __uint_as_float(r[j]);
+        __syncwarp();
+        const int col = nbase + lane;
+        const bool col_ok = col < ep.N;
+        const float bv = (ep.bias != nullptr && col_ok) ? __ldg(ep.bias + col) : 0.f;
+#pragma unroll 4
+        for (int rr = 0; rr < 32; ++rr) {
+          const int row = row0 + rr;
+          if (row >= ep.M) break;
+          float x = tile_s[rr * 33 + lane] + bv;
+          if (ep.relu) x = fmaxf(x, 0.f);
+          if (col_ok) {
+            if (ep.c_f32 != nullptr) ep.c_f32[(size_t)row * ep.ldc + col] = x;
+            if (ep.c_bf16 != nullptr) ep.c_bf16[(size_t)row * ep.ldc + col] = __float2bfloat16(x);
+          }
+        }
+      }
+      // this warp is done reading the accumulator: hand it back to the MMA warp
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) p_mbar_arrive(&tmem_empty[acc]);
+    }
+  }
+
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
+  }
+}
+
+typedef CUresult (*PEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                              const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                              CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+PEncodeFn p_encode = nullptr;
+std::mutex p_encode_mu;
+
+int p_make_map(CUtensorMap* map, const void* ptr, long rows, long cols, int box_rows) {
+  {
+    std::lock_guard<std::mutex> lock(p_encode_mu);
+    if (p_encode == nullptr) {
+      void* fn = nullptr;
+      cudaDriverEntryPointQueryResult q;
+      const cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+      if (e != cudaSuccess) return (int)e;
+      if (q != cudaDriverEntryPointSuccess || fn == nullptr) return (int)cudaErrorNotSupported;
+      p_encode = reinterpret_cast<PEncodeFn>(fn);
+    }
+  }
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)cols * 2};
+  cuuint32_t box[2] = {(cuuint32_t)P_BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  const CUresult r = p_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+}
+
+template <int BN>
+int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, int M, int N, int K, cudaStream_t stream) {
+  constexpr int STAGES = (BN == 256) ? 4 : 6;
+  constexpr size_t smem = (size_t)STAGES * (P_BM * P_BK * 2 + BN * P_BK * 2) + 4 * 32 * 33 * sizeof(float) + 1024;
+  static bool configured = false;
+  if (!configured) {
+    const cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_persistent_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    configured = true;
+  }
+  const int tiles_m = (M + P_BM - 1) / P_BM, tiles_n = (N + BN - 1) / BN;
+  const int grid = tiles_m * tiles_n < 148 ? tiles_m * tiles_n : 148;
+  gemm_bf16_tcgen05_persistent_kernel<BN><<<grid, P_THREADS, smem, stream>>>(ta, tb, ep, K, tiles_m, tiles_n);
+  TFDE_RETURN_LAUNCH_STATUS();
+}
+
+}  // namespace
+
+// Same contract as tfde_gemm_bf16_tn (K % 8 == 0, 16-byte aligned K-major bf16 operands); persistent
+// one-CTA-per-SM schedule with a double-buffered TMEM accumulator. First call per tile shape sets a
+// function attribute: make it outside of stream capture.
+TFDE_API int tfde_gemm_bf16_tn_persistent(const void* A, const void* B, float* c_f32, void* c_bf16, long ldc,
+                                          const float* bias, int relu, int M, int N, int K, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || (K & 7) || !A || !B || (!c_f32 && !c_bf16)) return TFDE_ERR_INVALID;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return TFDE_ERR_INVALID;
+  const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+  CUtensorMap ta, tb;
+  int rc = p_make_map(&ta, A, M, K, P_BM);
+  if (rc != 0) return rc;
+  rc = p_make_map(&tb, B, N, K, BN);
+  if (rc != 0) return rc;
+  PEpilogue ep{c_f32, (__nv_bfloat16*)c_bf16, ldc, bias, relu, M, N};
+  if (BN == 64) return p_launch<64>(ta, tb, ep, M, N, K, stream);
+  if (BN == 128) return p_launch<128>(ta, tb, ep, M, N, K, stream);
+  return p_launch<256>(ta, tb, ep, M, N, K, stream);
+}

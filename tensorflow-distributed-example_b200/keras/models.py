@@ -13,6 +13,8 @@ reduction, update, metric accumulation) is captured once in a CUDA graph and rep
 """
 from __future__ import annotations
 
+import contextlib
+import gc
 import logging
 import os
 import time
@@ -44,6 +46,22 @@ def _fresh_seed() -> int:
     if _global_seed is not None:
         return _global_seed
     return int.from_bytes(os.urandom(4), "little")
+
+
+@contextlib.contextmanager
+def _capture(graph, stream):
+    """torch.cuda.graph with the cyclic garbage collector paused. A collection that happens to run in
+    the middle of a capture can finalise CUDA graphs of dead models (CUDAGraph.reset frees device memory),
+    which CUDA forbids while a stream is capturing and which invalidates the capture in progress."""
+    gc.collect()
+    was_enabled = gc.isenabled()
+    gc.disable()
+    try:
+        with torch.cuda.graph(graph, stream=stream):
+            yield
+    finally:
+        if was_enabled:
+            gc.enable()
 
 
 class _Slot:
@@ -393,7 +411,7 @@ class Sequential:
                 if slot.graph is None:
                     it0 = self.optimizer.iterations
                     g = torch.cuda.CUDAGraph()
-                    with torch.cuda.graph(g, stream=self._stream):
+                    with _capture(g, self._stream):
                         st.in_x.copy_(slot.host_x, non_blocking=True)
                         st.in_y.copy_(slot.host_y, non_blocking=True)
                         self._step_body(st.in_x, st.in_y, gb)
@@ -423,7 +441,7 @@ class Sequential:
         if st.graph is None:
             it0 = self.optimizer.iterations
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g, stream=self._stream):
+            with _capture(g, self._stream):
                 self._step_body(st.in_x, st.in_y, gb)
             self.optimizer.iterations = it0
             st.graph = g

@@ -14,6 +14,7 @@ import torch
 
 from . import native
 from . import reference as ref
+from . import tensorcore
 
 c_p, c_i, c_l = native.c_p, native.c_i, native.c_l
 native.register_optional("tfde_cast_bf16_masked", [c_p, c_p, c_p, c_l, c_p])
@@ -78,7 +79,7 @@ def dense_fwd(x, w, bias=None, act="none", out=None, bufs=None):
     b = bufs if bufs is not None else {}
     xb = cast_bf16_masked(x, None, out=b.get("xb"))
     wt = native.cast_transpose_bf16(w, None, out=b.get("wt"))        # [N, K]
-    return native.gemm_bf16_tn(xb, wt, bias, relu, torch.float32, out=out)
+    return tensorcore.gemm_bf16_tn(xb, wt, bias, relu, torch.float32, out=out)
 
 
 def dense_bwd(x, w, y, dy, act="none", need_dx=True, has_bias=True, out_dx=None, out_dw=None, out_db=None,
@@ -101,11 +102,11 @@ def dense_bwd(x, w, y, dy, act="none", need_dx=True, has_bias=True, out_dx=None,
     N = w.shape[1]
     xt = native.cast_transpose_bf16(x, None, out=b.get("xt"))          # [K, M]
     dyt = native.cast_transpose_bf16(dy, mask, out=b.get("dyt"))       # [N, M]
-    dw = native.gemm_bf16_tn(xt, dyt, None, False, torch.float32, out=out_dw)   # [K, N]
+    dw = tensorcore.gemm_bf16_tn(xt, dyt, None, False, torch.float32, out=out_dw)   # [K, N]
     db = colsum_masked(dy, mask, out=out_db) if has_bias else None
     dx = None
     if need_dx:
         dyb = cast_bf16_masked(dy, mask, out=b.get("dyb"))             # [M, N]
         wb = cast_bf16_masked(w, None, out=b.get("wb"))                # [K, N]
-        dx = native.gemm_bf16_tn(dyb, wb, None, False, torch.float32, out=out_dx)   # [M, K]
+        dx = tensorcore.gemm_bf16_tn(dyb, wb, None, False, torch.float32, out=out_dx)   # [M, K]
     return dx, dw, db

@@ -1,0 +1,51 @@
+"""Front door of the tcgen05 bf16 GEMMs: picks between the two hand-written kernels.
+
+* ``gemm_tcgen05.cu``            one (128*MT) x BN tile per CTA; MT=2 stacks two accumulators that share
+                                 every B tile -- best for large square problems bound by L2->SM operand traffic.
+* ``gemm_tcgen05_persistent.cu`` one CTA per SM looping over tiles with a double-buffered TMEM accumulator
+                                 (epilogue overlaps the next tile's main loop) -- best for the many
+                                 small-K / output-bound GEMMs of a convolutional network.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+
+from . import native
+
+c_p, c_i, c_l = native.c_p, native.c_i, native.c_l
+native.register_optional("tfde_gemm_bf16_tn_persistent", [c_p, c_p, c_p, c_p, c_l, c_p, c_i, c_i, c_i, c_i, c_p])
+
+_FORCE = os.environ.get("TFDE_TC_KERNEL", "auto")   # auto | tile | persistent
+
+
+def pick(M: int, N: int, K: int) -> str:
+    if _FORCE in ("tile", "persistent"):
+        return _FORCE
+    bn = 64 if N <= 64 else (128 if N <= 128 else 256)
+    tiles256 = ((M + 255) // 256) * ((N + bn - 1) // bn)
+    if bn == 256 and tiles256 >= 2 * 148 and K >= 1024:
+        return "tile"          # 256x256 dual-accumulator tiles: a third less operand traffic per FLOP
+    return "persistent"
+
+
+def gemm_bf16_tn(a, b, bias=None, relu=False, out_dtype=torch.float32, out=None, kernel=None):
+    """C[M,N] = act(A[M,K] @ B[N,K]^T + bias), bf16 operands (K contiguous, K % 8 == 0), fp32 accumulate."""
+    L = native.load()
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
+        raise TypeError("gemm_bf16_tn expects bf16 operands")
+    if not (a.is_contiguous() and b.is_contiguous()):
+        raise ValueError("operands must be contiguous")
+    M, K = a.shape
+    N, K2 = b.shape
+    if K != K2:
+        raise ValueError(f"K mismatch: {K} vs {K2}")
+    c = out if out is not None else torch.empty((M, N), dtype=out_dtype, device=a.device)
+    f32 = c.data_ptr() if c.dtype == torch.float32 else None
+    b16 = c.data_ptr() if c.dtype == torch.bfloat16 else None
+    which = kernel or pick(M, N, K)
+    fn = L.tfde_gemm_bf16_tn_persistent if which == "persistent" else L.tfde_gemm_bf16_tn
+    native.check(fn(a.data_ptr(), b.data_ptr(), f32, b16, c.stride(0), native.ptr(bias), 1 if relu else 0, M, N, K,
+                    native.stream_ptr()), f"gemm_bf16_tn[{which}]")
+    return c

@@ -8,7 +8,7 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 
-from tfde_b200.ops import native
+from tfde_b200.ops import native, tensorcore
 
 
 def one(M, N, K, bias, relu, out_dtype, time_it=False):
@@ -16,7 +16,21 @@ def one(M, N, K, bias, relu, out_dtype, time_it=False):
     a = (torch.randn(M, K, generator=g) * 0.5).to(torch.bfloat16).cuda()
     b = (torch.randn(N, K, generator=g) * 0.5).to(torch.bfloat16).cuda()
     bv = torch.randn(N, generator=g).cuda() if bias else None
-    c = native.gemm_bf16_tn(a, b, bv, relu, out_dtype)
+    ok_all = True
+    for kern in ("tile", "persistent"):
+        ck = tensorcore.gemm_bf16_tn(a, b, bv, relu, out_dtype, kernel=kern)
+        torch.cuda.synchronize()
+        refk = a.float() @ b.float().t()
+        if bias:
+            refk = refk + bv
+        if relu:
+            refk = torch.relu(refk)
+        errk = (ck.float() - refk).abs().max().item()
+        tolk = (2e-3 if out_dtype == torch.float32 else 1.2e-2) * (refk.abs().max().item() + 1e-9)
+        if not errk <= tolk:
+            print(json.dumps({"kernel": kern, "M": M, "N": N, "K": K, "FAILED_err": errk}), flush=True)
+            ok_all = False
+    c = tensorcore.gemm_bf16_tn(a, b, bv, relu, out_dtype)
     torch.cuda.synchronize()
     ref = a.float() @ b.float().t()
     if bias:
@@ -26,11 +40,12 @@ def one(M, N, K, bias, relu, out_dtype, time_it=False):
     err = (c.float() - ref).abs().max().item()
     scale = ref.abs().max().item() + 1e-9
     tol = 2e-3 if out_dtype == torch.float32 else 1.2e-2
-    ok = err <= tol * scale
+    ok = err <= tol * scale and ok_all
     res = {"M": M, "N": N, "K": K, "bias": bias, "relu": relu, "out": str(out_dtype).split(".")[-1],
            "max_abs_err": err, "scale": scale, "ok": bool(ok)}
     if time_it:
-        for fn, key in ((lambda: native.gemm_bf16_tn(a, b, bv, relu, out_dtype, out=c), "tcgen05_tflops"),
+        for fn, key in ((lambda: tensorcore.gemm_bf16_tn(a, b, bv, relu, out_dtype, out=c, kernel="tile"), "tile_tflops"),
+                        (lambda: tensorcore.gemm_bf16_tn(a, b, bv, relu, out_dtype, out=c, kernel="persistent"), "persistent_tflops"),
                         (lambda: torch.matmul(a, b.t()), "cublas_tflops")):
             for _ in range(3):
                 fn()
@@ -59,6 +74,10 @@ def main():
     ok &= one(8192, 5408, 64, False, False, torch.float32, True)  # its dgrad
     ok &= one(5408, 64, 8192, False, False, torch.float32, True)  # its wgrad
     ok &= one(333, 200, 1176, False, False, torch.bfloat16)
+    ok &= one(100352, 64, 64, False, True, torch.float32, True)     # ResNet 1x1 conv, 56x56x64, batch 32
+    ok &= one(100352, 64, 576, True, False, torch.float32, True)    # ResNet 3x3 conv as im2col GEMM
+    ok &= one(6272, 512, 2304, False, False, torch.float32, True)   # stage-4 3x3
+    ok &= one(1568, 2048, 512, False, False, torch.float32, True)   # stage-5 1x1 expand
     ok &= one(4096, 4096, 4096, False, False, torch.bfloat16, True)
     ok &= one(8192, 8192, 8192, False, False, torch.bfloat16, True)
     print("TCGEN05", "PASSED" if ok else "FAILED", flush=True)

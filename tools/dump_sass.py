@@ -1,0 +1,56 @@
+"""Writes profiles/sass/<kernel>.sass for the kernels of libtfde_kernels.so and a summary of the SASS
+mnemonics that prove the Blackwell-native paths (UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG = TMA,
+UTCBAR = tcgen05.commit, SYNCS = mbarrier, peer/system-scope memory ops in the all-reduce)."""
+import collections
+import os
+import re
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "tensorflow-distributed-example_b200", "_lib", "libtfde_kernels.so")
+OUT = os.path.join(ROOT, "profiles", "sass")
+KEEP = ("gemm_bf16_tcgen05_kernel", "allreduce_fused_kernel", "dense_skinny_fwd_kernel", "head_fwd_bwd_kernel",
+        "conv3x3c1_relu_pool", "gemm_fp32_kernel")
+MNEMONICS = ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMAPF", "SYNCS", "LDGSTS", "UCGABAR", "HMMA", "FFMA", "LDG", "STG",
+             "ATOMG", "REDG", "MEMBAR", "CCTL")
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    txt = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True, check=True).stdout
+    parts = re.split(r"\n\s*Function : ", txt)
+    rows = []
+    for part in parts[1:]:
+        name, _, body = part.partition("\n")
+        if not any(k in name for k in KEEP):
+            continue
+        dem = subprocess.run(["cu++filt", name.strip()], capture_output=True, text=True).stdout.strip() or name.strip()
+        clean = dem.replace("(anonymous namespace)::", "").replace("<unnamed>::", "")
+        clean = re.sub(r"^void\s+", "", clean)
+        short = re.sub(r"[^A-Za-z0-9_]+", "_", clean.split("(")[0]).strip("_")[:90]
+        counts = collections.Counter()
+        for line in body.splitlines():
+            m = re.search(r"/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
+            if m:
+                op = m.group(1)
+                for mn in MNEMONICS:
+                    if op.startswith(mn):
+                        counts[mn] += 1
+                if ".SYS" in op or ".STRONG.SYS" in op:
+                    counts["sys-scope"] += 1
+        path = os.path.join(OUT, short + ".sass")
+        if any(k in name for k in KEEP[:5]):
+            with open(path, "w") as f:
+                f.write("Function : " + part)
+        rows.append((short, counts))
+    with open(os.path.join(ROOT, "profiles", "sass_summary.md"), "w") as f:
+        f.write("# SASS mnemonic counts per kernel (cuobjdump -sass, sm_100a)\n\n")
+        f.write("| kernel | " + " | ".join(MNEMONICS) + " | sys-scope |\n|---|" + "---|" * (len(MNEMONICS) + 1) + "\n")
+        for short, c in sorted(rows):
+            f.write(f"| {short} | " + " | ".join(str(c.get(m, 0)) for m in MNEMONICS) + f" | {c.get('sys-scope', 0)} |\n")
+    print(f"wrote {len(rows)} kernels to profiles/sass_summary.md")
+
+
+if __name__ == "__main__":
+    main()
