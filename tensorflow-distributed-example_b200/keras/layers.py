@@ -209,13 +209,26 @@ class Conv2D(Layer):
         b = x.shape[0]
         self._x = x
         y = self.buf("y", (b,) + self.out_shape)
-        ops.conv2d_fwd(x, self.kernel.value, self.bias.value if self.bias else None, self.strides,
-                       self.pads, self.activation == "relu", out=y)
+        from ..ops import mixed, mixed_conv
+        self._mixed = (mixed.global_policy() == "mixed_bfloat16"
+                       and mixed_conv.supported(x.shape, self.kernel.shape, self.out_shape[0], self.out_shape[1]))
+        if self._mixed:   # tensor-core path: gathered bf16 operands, fp32 accumulation in TMEM
+            mixed_conv.conv2d_fwd(x, self.kernel.value, self.bias.value if self.bias else None, self.strides,
+                                  self.pads, self.activation == "relu", out=y)
+        else:
+            ops.conv2d_fwd(x, self.kernel.value, self.bias.value if self.bias else None, self.strides,
+                           self.pads, self.activation == "relu", out=y)
         self._y = y
         return y
 
     def backward(self, dy):
         dx = self.buf("dx", self._x.shape) if self.need_dx else None
+        if getattr(self, "_mixed", False):
+            from ..ops import mixed_conv
+            mixed_conv.conv2d_bwd(self._x, self.kernel.value, self._y, dy, self.strides, self.pads,
+                                  self.activation == "relu", self.need_dx, self.use_bias, out_dx=dx,
+                                  out_dw=self.kernel.grad, out_db=self.bias.grad if self.bias else None)
+            return dx
         ops.conv2d_bwd(self._x, self.kernel.value, self._y, dy, self.strides, self.pads,
                        self.activation == "relu", self.need_dx, self.use_bias, out_dx=dx,
                        out_dw=self.kernel.grad, out_db=self.bias.grad if self.bias else None)

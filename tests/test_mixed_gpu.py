@@ -84,3 +84,32 @@ def test_model_a_trains_under_mixed_bfloat16():
         assert res[DEV][-1] < res[DEV][0]
     finally:
         tf.keras.mixed_precision.set_global_policy("float32")
+
+
+CONVS = [  # B,H,W,C, k, stride, padding, Cout, bias, relu
+    (8, 16, 16, 64, 1, 1, "valid", 64, True, True),
+    (8, 16, 16, 64, 3, 1, "same", 64, True, False),
+    (8, 16, 16, 64, 1, 2, "valid", 128, True, False),
+    (8, 32, 32, 3, 7, 2, "same", 64, True, False),
+    (8, 14, 14, 32, 3, 2, "same", 72, False, True),
+]
+
+
+@pytest.mark.parametrize("B,H,W,C,k,s,pad,Co,bias,relu", CONVS)
+def test_mixed_conv_fwd_bwd(B, H, W, C, k, s, pad, Co, bias, relu):
+    from tfde_b200 import ops
+    from tfde_b200.ops import mixed_conv
+    x, w = _rand(B, H, W, C, seed=1), _rand(k, k, C, Co, seed=2) * 0.1
+    b = _rand(Co, seed=3) if bias else None
+    ho, wo, pads = ops.conv_geometry(H, W, k, k, (s, s), pad)
+    assert mixed_conv.supported(x.shape, w.shape, ho, wo)
+    dy = _rand(B, ho, wo, Co, seed=4)
+    y_ref = mixed_conv.conv2d_fwd(x, w, b, (s, s), pads, relu)
+    dx_ref, dw_ref, db_ref = mixed_conv.conv2d_bwd(x, w, y_ref, dy, (s, s), pads, relu, True, bias)
+    y = mixed_conv.conv2d_fwd(x.to(DEV), w.to(DEV), b.to(DEV) if bias else None, (s, s), pads, relu)
+    _close(y, y_ref, 3e-3, "mixed conv fwd")
+    dx, dw, db = mixed_conv.conv2d_bwd(x.to(DEV), w.to(DEV), y, dy.to(DEV), (s, s), pads, relu, True, bias)
+    _close(dx, dx_ref, 4e-3, "mixed conv dx")
+    _close(dw, dw_ref, 4e-3, "mixed conv dw")
+    if bias:
+        _close(db, db_ref, 1e-4, "mixed conv db")
