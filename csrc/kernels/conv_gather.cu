@@ -236,3 +236,48 @@ TFDE_API int tfde_cast_transpose_pad_bf16(const float* x, const float* mask, voi
   cast_transpose_pad_bf16_kernel<<<grid, block, 0, stream>>>(x, mask, (__nv_bfloat16*)y, R, C, ldy);
   TFDE_RETURN_LAUNCH_STATUS();
 }
+
+// ---------------------------------------------------------------------------------------------
+// bf16 matrix transpose y[C, R] (ld = ldy) = x[R, C] (ld = ldx): 64x64 tiles through shared memory, 4-byte
+// accesses on both sides. Used to turn the (fast, vectorised) im2col operand into the K-major operand of
+// the filter-gradient GEMM instead of gathering it a second time in transposed order.
+// ---------------------------------------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256)
+transpose_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long R, int C, long ldx,
+                      long ldy) {
+  __shared__ __nv_bfloat16 tile[64][66];
+  const long r0 = (long)blockIdx.x * 64;
+  const int c0 = blockIdx.y * 64;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;       // 32 x 8
+  for (int i = ty; i < 64; i += 8) {                            // row i of the tile, columns 2*tx, 2*tx+1
+    const long r = r0 + i;
+    const int c = c0 + 2 * tx;
+    __nv_bfloat162 v = __floats2bfloat162_rn(0.f, 0.f);
+    if (r < R) {
+      if (c + 1 < C) v = *reinterpret_cast<const __nv_bfloat162*>(x + r * ldx + c);
+      else if (c < C) v.x = x[r * ldx + c];
+    }
+    tile[i][2 * tx] = v.x; tile[i][2 * tx + 1] = v.y;
+  }
+  __syncthreads();
+  for (int i = ty; i < 64; i += 8) {                            // output row c0+i, columns r0 + 2*tx, +1
+    const int c = c0 + i;
+    const long r = r0 + 2 * tx;
+    if (c < C && r < ldy) {
+      __nv_bfloat162 v;
+      v.x = tile[2 * tx][i]; v.y = tile[2 * tx + 1][i];
+      if (r + 1 < ldy) *reinterpret_cast<__nv_bfloat162*>(y + (long)c * ldy + r) = v;
+      else y[(long)c * ldy + r] = v.x;
+    }
+  }
+}
+}  // namespace
+
+// y[C, ldy] = transpose(x[R, ldx]); rows of x beyond R read as zero (ldy may exceed R: zero padding).
+TFDE_API int tfde_transpose_bf16(const void* x, void* y, long R, int C, long ldx, long ldy, cudaStream_t stream) {
+  if ((ldx & 1) || (ldy & 1) || ldy < R) return TFDE_ERR_INVALID;
+  dim3 grid((unsigned)((ldy + 63) / 64), (C + 63) / 64);
+  transpose_bf16_kernel<<<grid, 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, R, C, ldx, ldy);
+  TFDE_RETURN_LAUNCH_STATUS();
+}

@@ -28,16 +28,19 @@ __global__ void cast_bf16_masked_kernel(const float* __restrict__ x, const float
   }
 }
 
-// out[c] = sum_r x[r,c] * (mask[r,c] > 0): block = 32 columns x 8 row lanes, fixed-order tree.
+// out[c] = sum_r x[r,c] * (mask[r,c] > 0). Grid = (column tiles of 32, row blocks); every block reduces its
+// row range (32 columns x 8 row lanes), writes a partial, and the last block of a column tile adds the
+// partials in row-block order (deterministic, same ticket scheme as the batch-norm statistics).
 __global__ void __launch_bounds__(256)
 colsum_masked_kernel(const float* __restrict__ x, const float* __restrict__ mask, float* __restrict__ out,
-                     long R, int C) {
+                     long R, int C, float* __restrict__ partials, unsigned* __restrict__ counters) {
   __shared__ float s[8][33];
+  __shared__ int s_last;
   const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + cx;
   float a = 0.f;
   if (c < C) {
-    for (long r = ry; r < R; r += 8) {
+    for (long r = (long)blockIdx.y * 8 + ry; r < R; r += (long)gridDim.y * 8) {
       float v = __ldg(x + r * C + c);
       if (mask != nullptr && !(__ldg(mask + r * C + c) > 0.f)) v = 0.f;
       a += v;
@@ -45,12 +48,30 @@ colsum_masked_kernel(const float* __restrict__ x, const float* __restrict__ mask
   }
   s[ry][cx] = a;
   __syncthreads();
-  if (ry == 0 && c < C) {
-    float t = 0.f;
+  float t = 0.f;
+  if (ry == 0) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) t += s[i][cx];
-    out[c] = t;
   }
+  if (gridDim.y == 1) {
+    if (ry == 0 && c < C) out[c] = t;
+    return;
+  }
+  float* part = partials + ((size_t)blockIdx.x * gridDim.y + blockIdx.y) * 32;
+  if (ry == 0) __stcg(part + cx, t);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(counters + blockIdx.x, 1u) == gridDim.y - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (ry == 0 && c < C) {
+    float tot = 0.f;
+    for (unsigned rb = 0; rb < gridDim.y; ++rb)
+      tot += __ldcg(partials + ((size_t)blockIdx.x * gridDim.y + rb) * 32 + cx);
+    out[c] = tot;
+  }
+  if (threadIdx.x == 0) counters[blockIdx.x] = 0u;
 }
 
 }  // namespace
@@ -63,7 +84,16 @@ TFDE_API int tfde_cast_bf16_masked(const float* x, const float* mask, void* y, l
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
-TFDE_API int tfde_colsum_masked(const float* x, const float* mask, float* out, long R, int C, cudaStream_t stream) {
-  colsum_masked_kernel<<<(C + 31) / 32, 256, 0, stream>>>(x, mask, out, R, C);
+// partials: >= ceil(C/32) * row_blocks * 32 floats (row_blocks <= 128); counters: ceil(C/32) zeroed tickets.
+TFDE_API int tfde_colsum_masked(const float* x, const float* mask, float* out, long R, int C, float* partials,
+                                unsigned* counters, cudaStream_t stream) {
+  const int ct = (C + 31) / 32;
+  if (ct > TFDE_MAX_COUNTERS) return TFDE_ERR_INVALID;
+  long rb = (R + 8 * 16 - 1) / (8 * 16);                 // >= 16 rows per thread
+  const long cap = (148L * 4 + ct - 1) / ct;
+  if (rb > cap) rb = cap;
+  if (rb > 128) rb = 128;
+  if (rb < 1 || partials == nullptr || counters == nullptr) rb = 1;
+  colsum_masked_kernel<<<dim3(ct, (unsigned)rb), 256, 0, stream>>>(x, mask, out, R, C, partials, counters);
   TFDE_RETURN_LAUNCH_STATUS();
 }

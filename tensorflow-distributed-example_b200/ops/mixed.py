@@ -18,7 +18,7 @@ from . import tensorcore
 
 c_p, c_i, c_l = native.c_p, native.c_i, native.c_l
 native.register_optional("tfde_cast_bf16_masked", [c_p, c_p, c_p, c_l, c_p])
-native.register_optional("tfde_colsum_masked", [c_p, c_p, c_p, c_l, c_i, c_p])
+native.register_optional("tfde_colsum_masked", [c_p, c_p, c_p, c_l, c_i, c_p, c_p, c_p])
 
 _policy = "float32"
 
@@ -57,8 +57,9 @@ def colsum_masked(x, mask=None, out=None):
     L = native.load()
     R, C = x.shape
     o = out if out is not None else torch.empty((C,), dtype=torch.float32, device=x.device)
-    native.check(L.tfde_colsum_masked(x.data_ptr(), native.ptr(mask), o.data_ptr(), R, C, native.stream_ptr()),
-                 "colsum_masked")
+    wsp = native.Workspace.current(x.device)
+    native.check(L.tfde_colsum_masked(x.data_ptr(), native.ptr(mask), o.data_ptr(), R, C, wsp.small.data_ptr(),
+                                      wsp.counters.data_ptr(), native.stream_ptr()), "colsum_masked")
     return o
 
 

@@ -23,6 +23,7 @@ native.register_optional("tfde_im2colT_bf16", [c_p, c_p] + _G + [c_l, c_p])
 native.register_optional("tfde_dgrad_gather_bf16", [c_p, c_p, c_p] + _G + [c_i, c_p])
 native.register_optional("tfde_wrot_bf16", [c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_p])
 native.register_optional("tfde_cast_transpose_pad_bf16", [c_p, c_p, c_p, c_l, c_i, c_l, c_p])
+native.register_optional("tfde_transpose_bf16", [c_p, c_p, c_l, c_i, c_l, c_l, c_p])
 
 _pool = {}
 
@@ -110,8 +111,16 @@ def conv2d_bwd(x, w, y, dy, stride=(1, 1), pads=(0, 0, 0, 0), relu=False, need_d
     dy2 = dy.reshape(M, cout)
     mask2 = mask.reshape(M, cout) if mask is not None else None
     # wgrad: dW[kc, cout] = im2col^T[kc, M] . dy^T[cout, M]^T
+    # K-major (M contiguous) im2col operand: gather once in the fast row-major order, then a streaming
+    # bf16 transpose (measured ~4x faster than gathering in transposed order)
+    kp = _r8(kc)
+    if kh == 1 and kw == 1 and stride == (1, 1) and kp == kc:
+        a = cast_bf16_masked(x.reshape(M, c), None, out=_scratch(dev, "C", M * kp).view(M, kp))
+    else:
+        a = _scratch(dev, "C", M * kp).view(M, kp)
+        native.check(L.tfde_im2col_bf16(x.data_ptr(), a.data_ptr(), *g, kp, native.stream_ptr()), "im2col_bf16")
     at = _scratch(dev, "A", kc * M).view(kc, M)
-    native.check(L.tfde_im2colT_bf16(x.data_ptr(), at.data_ptr(), *g, M, native.stream_ptr()), "im2colT_bf16")
+    native.check(L.tfde_transpose_bf16(a.data_ptr(), at.data_ptr(), M, kc, kp, M, native.stream_ptr()), "transpose_bf16")
     dyt = _scratch(dev, "B", cout * M).view(cout, M)
     native.check(L.tfde_cast_transpose_pad_bf16(dy2.data_ptr(), native.ptr(mask2), dyt.data_ptr(), M, cout, M,
                                                 native.stream_ptr()), "cast_transpose_pad_bf16")
