@@ -82,7 +82,8 @@ struct PEpilogue {
 template <int BN>
 __global__ void __launch_bounds__(P_THREADS, 1)
 gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                                    const PEpilogue ep, const int K, const int tiles_m, const int tiles_n) {
+                                    const PEpilogue ep_in, const int K, const int tiles_m, const int tiles_n,
+                                    const int splits, float* __restrict__ ws) {
   constexpr uint32_t A_BYTES = P_BM * P_BK * 2;
   constexpr uint32_t B_BYTES = BN * P_BK * 2;
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
@@ -99,7 +100,10 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_k = (K + P_BK - 1) / P_BK;
-  const int num_tiles = tiles_m * tiles_n;
+  // work item = (output tile, k split); split z covers k-blocks [z*kb_per, min(num_k, (z+1)*kb_per)).
+  // With splits > 1 every item stores an fp32 partial tile into ws[z]; a second kernel adds them in z order.
+  const int kb_per = (num_k + splits - 1) / splits;
+  const int num_tiles = tiles_m * tiles_n * splits;
 
   if (threadIdx.x == 0) {
 #pragma unroll
@@ -122,9 +126,11 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
   if (warp == 0) {
     if (lane == 0) {
       uint32_t it = 0;                                   // k-blocks issued so far (across tiles)
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int item = blockIdx.x; item < num_tiles; item += gridDim.x) {
+        const int tile = item / splits, z = item % splits;
         const int m0 = (tile / tiles_n) * P_BM, n0 = (tile % tiles_n) * BN;
-        for (int kb = 0; kb < num_k; ++kb, ++it) {
+        const int kb_end = min(num_k, (z + 1) * kb_per);
+        for (int kb = z * kb_per; kb < kb_end; ++kb, ++it) {
           const uint32_t s = it % STAGES, ph = (it / STAGES) & 1u;
           p_mbar_wait(&empty_bar[s], ph ^ 1u);
           p_mbar_expect_tx(&full_bar[s], STAGE_BYTES);
@@ -138,11 +144,13 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
     if (lane == 0) {
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(P_BM >> 4) << 24);
       uint32_t it = 0, tl = 0;                           // tl: tiles done by this CTA
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
+      for (int item = blockIdx.x; item < num_tiles; item += gridDim.x, ++tl) {
+        const int z = item % splits;
+        const int kb_begin = z * kb_per, kb_end = min(num_k, (z + 1) * kb_per);
         const uint32_t acc = tl & 1u, aph = (tl >> 1) & 1u;
         p_mbar_wait(&tmem_empty[acc], aph ^ 1u);         // epilogue has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        for (int kb = 0; kb < num_k; ++kb, ++it) {
+        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
           const uint32_t s = it % STAGES, ph = (it / STAGES) & 1u;
           p_mbar_wait(&full_bar[s], ph);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -151,7 +159,7 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
 #pragma unroll
           for (int k = 0; k < P_BK / P_UMMA_K; ++k)
             p_umma(tmem_d + acc * BN, p_smem_desc(a_addr + k * P_UMMA_K * 2), p_smem_desc(b_addr + k * P_UMMA_K * 2),
-                   idesc, (kb | k) != 0 ? 1u : 0u);
+                   idesc, (kb != kb_begin || k != 0) ? 1u : 0u);
           p_commit(&empty_bar[s]);
         }
         p_commit(&tmem_full[acc]);
@@ -160,9 +168,14 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
   } else {
     const int q = warp & 3;
     uint32_t tl = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
+    for (int item = blockIdx.x; item < num_tiles; item += gridDim.x, ++tl) {
+      const int tile = item / splits, z = item % splits;
       const uint32_t acc = tl & 1u, aph = (tl >> 1) & 1u;
       const int m0 = (tile / tiles_n) * P_BM, n0 = (tile % tiles_n) * BN;
+      PEpilogue ep = ep_in;
+      if (splits > 1) {   // raw fp32 partial into ws[z][M][N]; bias / activation / cast happen in the reduce kernel
+        ep.c_f32 = ws + (size_t)z * ep_in.M * ep_in.N; ep.c_bf16 = nullptr; ep.ldc = ep_in.N; ep.bias = nullptr; ep.relu = 0;
+      }
       p_mbar_wait(&tmem_full[acc], aph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const int row0 = m0 + q * 32;
@@ -229,6 +242,29 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
   }
 }
 
+// out[i] = act(sum_z ws[z][i] + bias[col]) in z order; fp32 and/or bf16 output with row stride ldc.
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __restrict__ c_f32,
+                                     __nv_bfloat16* __restrict__ c_bf16, long ldc, const float* __restrict__ bias,
+                                     int relu, int M, int N, int splits) {
+  const long total = (long)M * N;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    float s = 0.f;
+    for (int z0 = 0; z0 < splits; z0 += 4) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = (z0 + u < splits) ? __ldcg(ws + (size_t)(z0 + u) * total + i) : 0.f;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) s += v[u];
+    }
+    const int col = (int)(i % N);
+    const long row = i / N;
+    if (bias != nullptr) s += __ldg(bias + col);
+    if (relu) s = fmaxf(s, 0.f);
+    if (c_f32 != nullptr) c_f32[row * ldc + col] = s;
+    if (c_bf16 != nullptr) c_bf16[row * ldc + col] = __float2bfloat16(s);
+  }
+}
+
 typedef CUresult (*PEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -258,7 +294,8 @@ int p_make_map(CUtensorMap* map, const void* ptr, long rows, long cols, int box_
 }
 
 template <int BN>
-int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, int M, int N, int K, cudaStream_t stream) {
+int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, int M, int N, int K, float* ws,
+             size_t ws_bytes, cudaStream_t stream) {
   constexpr int STAGES = (BN == 256) ? 4 : 6;
   constexpr size_t smem = (size_t)STAGES * (P_BM * P_BK * 2 + BN * P_BK * 2) + 4 * 32 * 33 * sizeof(float) + 1024;
   static bool configured = false;
@@ -268,18 +305,42 @@ int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, 
     configured = true;
   }
   const int tiles_m = (M + P_BM - 1) / P_BM, tiles_n = (N + BN - 1) / BN;
-  const int grid = tiles_m * tiles_n < 148 ? tiles_m * tiles_n : 148;
-  gemm_bf16_tcgen05_persistent_kernel<BN><<<grid, P_THREADS, smem, stream>>>(ta, tb, ep, K, tiles_m, tiles_n);
+  const int tiles = tiles_m * tiles_n;
+  const int num_k = (K + P_BK - 1) / P_BK;
+  // split K when the output has too few tiles to fill the machine and the reduction is long (the filter-
+  // gradient GEMMs of a convolution: output [KH*KW*Cin, Cout], reduction over B*Ho*Wo)
+  int splits = 1;
+  if (ws != nullptr && tiles < 148 && num_k >= 8) {
+    splits = (148 + tiles - 1) / tiles;
+    if (splits > num_k / 4) splits = num_k / 4;
+    if (splits > 64) splits = 64;
+    const size_t per = (size_t)M * N * sizeof(float);
+    if (per * (size_t)splits > ws_bytes) splits = (int)(ws_bytes / per);
+    if (splits < 1) splits = 1;
+    const int kb_per = (num_k + splits - 1) / splits;
+    splits = (num_k + kb_per - 1) / kb_per;          // no empty split
+  }
+  const int items = tiles * splits;
+  const int grid = items < 148 ? items : 148;
+  gemm_bf16_tcgen05_persistent_kernel<BN><<<grid, P_THREADS, smem, stream>>>(ta, tb, ep, K, tiles_m, tiles_n, splits, ws);
+  if (splits > 1) {
+    long blocks = ((long)M * N + 255) / 256;
+    if (blocks > 148L * 8) blocks = 148L * 8;
+    splitk_reduce_kernel<<<(int)blocks, 256, 0, stream>>>(ws, ep.c_f32, ep.c_bf16, ep.ldc, ep.bias, ep.relu, M, N, splits);
+  }
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
 }  // namespace
 
+// `ws` (optional, ws_bytes): fp32 scratch for deterministic split-K (partials summed in split order by a
+// second kernel); pass NULL to disable splitting.
 // Same contract as tfde_gemm_bf16_tn (K % 8 == 0, 16-byte aligned K-major bf16 operands); persistent
 // one-CTA-per-SM schedule with a double-buffered TMEM accumulator. First call per tile shape sets a
 // function attribute: make it outside of stream capture.
 TFDE_API int tfde_gemm_bf16_tn_persistent(const void* A, const void* B, float* c_f32, void* c_bf16, long ldc,
-                                          const float* bias, int relu, int M, int N, int K, cudaStream_t stream) {
+                                          const float* bias, int relu, int M, int N, int K, float* ws,
+                                          size_t ws_bytes, cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0 || (K & 7) || !A || !B || (!c_f32 && !c_bf16)) return TFDE_ERR_INVALID;
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return TFDE_ERR_INVALID;
   const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
@@ -289,7 +350,7 @@ TFDE_API int tfde_gemm_bf16_tn_persistent(const void* A, const void* B, float* c
   rc = p_make_map(&tb, B, N, K, BN);
   if (rc != 0) return rc;
   PEpilogue ep{c_f32, (__nv_bfloat16*)c_bf16, ldc, bias, relu, M, N};
-  if (BN == 64) return p_launch<64>(ta, tb, ep, M, N, K, stream);
-  if (BN == 128) return p_launch<128>(ta, tb, ep, M, N, K, stream);
-  return p_launch<256>(ta, tb, ep, M, N, K, stream);
+  if (BN == 64) return p_launch<64>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  if (BN == 128) return p_launch<128>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  return p_launch<256>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
 }

@@ -15,7 +15,8 @@ import torch
 from . import native
 
 c_p, c_i, c_l = native.c_p, native.c_i, native.c_l
-native.register_optional("tfde_gemm_bf16_tn_persistent", [c_p, c_p, c_p, c_p, c_l, c_p, c_i, c_i, c_i, c_i, c_p])
+native.register_optional("tfde_gemm_bf16_tn_persistent",
+                         [c_p, c_p, c_p, c_p, c_l, c_p, c_i, c_i, c_i, c_i, c_p, native.c_z, c_p])
 
 _FORCE = os.environ.get("TFDE_TC_KERNEL", "auto")   # auto | tile | persistent
 
@@ -45,7 +46,12 @@ def gemm_bf16_tn(a, b, bias=None, relu=False, out_dtype=torch.float32, out=None,
     f32 = c.data_ptr() if c.dtype == torch.float32 else None
     b16 = c.data_ptr() if c.dtype == torch.bfloat16 else None
     which = kernel or pick(M, N, K)
-    fn = L.tfde_gemm_bf16_tn_persistent if which == "persistent" else L.tfde_gemm_bf16_tn
-    native.check(fn(a.data_ptr(), b.data_ptr(), f32, b16, c.stride(0), native.ptr(bias), 1 if relu else 0, M, N, K,
-                    native.stream_ptr()), f"gemm_bf16_tn[{which}]")
+    if which == "persistent":
+        wsp = native.Workspace.current(a.device)
+        native.check(L.tfde_gemm_bf16_tn_persistent(a.data_ptr(), b.data_ptr(), f32, b16, c.stride(0), native.ptr(bias),
+                                                    1 if relu else 0, M, N, K, wsp.ws.data_ptr(), wsp.ws_bytes,
+                                                    native.stream_ptr()), "gemm_bf16_tn[persistent]")
+    else:
+        native.check(L.tfde_gemm_bf16_tn(a.data_ptr(), b.data_ptr(), f32, b16, c.stride(0), native.ptr(bias),
+                                         1 if relu else 0, M, N, K, native.stream_ptr()), "gemm_bf16_tn[tile]")
     return c

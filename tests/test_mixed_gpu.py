@@ -25,7 +25,8 @@ def _close(a, b, rtol, what):
 
 @pytest.mark.parametrize("M,N,K,bias,relu,dt", [(128, 64, 64, False, False, torch.float32), (100, 40, 72, True, True, torch.float32),
                                                 (1024, 64, 5408, True, True, torch.float32), (333, 200, 1176, False, False, torch.bfloat16),
-                                                (512, 512, 256, True, False, torch.bfloat16), (2048, 2048, 512, False, True, torch.float32)])
+                                                (512, 512, 256, True, False, torch.bfloat16), (2048, 2048, 512, False, True, torch.float32),
+                                                (576, 64, 12544, True, True, torch.float32), (200, 40, 4096, False, False, torch.bfloat16)])
 def test_tcgen05_gemm(M, N, K, bias, relu, dt):
     a = (_rand(M, K, seed=1) * 0.5).to(torch.bfloat16).to(DEV)
     b = (_rand(N, K, seed=2) * 0.5).to(torch.bfloat16).to(DEV)

@@ -78,6 +78,9 @@ def main():
     ok &= one(100352, 64, 576, True, False, torch.float32, True)    # ResNet 3x3 conv as im2col GEMM
     ok &= one(6272, 512, 2304, False, False, torch.float32, True)   # stage-4 3x3
     ok &= one(1568, 2048, 512, False, False, torch.float32, True)   # stage-5 1x1 expand
+    ok &= one(576, 64, 100352, False, False, torch.float32, True)   # wgrad of a 3x3x64 conv: split-K
+    ok &= one(4608, 512, 1568, False, False, torch.float32, True)   # wgrad of the stage-5 3x3 conv
+    ok &= one(152, 64, 401408, False, False, torch.float32, True)   # wgrad of conv1 (7x7x3 padded to 152)
     ok &= one(4096, 4096, 4096, False, False, torch.bfloat16, True)
     ok &= one(8192, 8192, 8192, False, False, torch.bfloat16, True)
     print("TCGEN05", "PASSED" if ok else "FAILED", flush=True)
