@@ -37,8 +37,36 @@ def main():
         sync = m.sync
         loss = m.last_step_loss
     else:
-        import torchvision  # noqa: F401
-        raise SystemExit("torchvision baseline not wired")
+        # stand-in baseline: torchvision ResNet-50, channels_last, cuDNN autotune, (bf16 autocast), DDP/NCCL
+        import torch.distributed as dist
+        import torchvision
+        local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(local)
+        dev = torch.device("cuda", local)
+        if world > 1 and not dist.is_initialized():
+            dist.init_process_group("cpu:gloo,cuda:nccl", device_id=dev)
+        torch.backends.cudnn.benchmark = True
+        net = torchvision.models.resnet50(num_classes=1000).to(dev).to(memory_format=torch.channels_last)
+        ddp = torch.nn.parallel.DistributedDataParallel(net, device_ids=[local]) if world > 1 else net
+        opt = torch.optim.SGD(ddp.parameters(), lr=0.1, momentum=0.9)
+        xd = x.permute(0, 3, 1, 2).contiguous().to(dev).contiguous(memory_format=torch.channels_last)
+        yd = y.to(dev)
+        last = [None]
+
+        def step():
+            opt.zero_grad(set_to_none=True)
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=a.dtype == "bf16"):
+                l = torch.nn.functional.cross_entropy(ddp(xd), yd)
+            l.backward()
+            opt.step()
+            last[0] = l
+
+        class _M:
+            _stream = torch.cuda.current_stream()
+            graph_captured = False
+        m = _M()
+        sync = torch.cuda.synchronize
+        loss = lambda: float(last[0].item())
     for _ in range(a.warmup):
         step()
     sync()
