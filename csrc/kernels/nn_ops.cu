@@ -64,20 +64,40 @@ bn_stats_kernel(const float* __restrict__ x, long M, int C, float* __restrict__ 
 
 // y = ((x - mean) * invstd) * gamma + beta, optional ReLU. `stat_is_var`: second stat is a variance
 // (inference with moving statistics) instead of an inverse standard deviation.
+__device__ __forceinline__ float bn_apply_one(float xv, float mu, float inv, const float* gamma, const float* beta,
+                                              int c, int relu) {
+  float v = (xv - mu) * inv;
+  if (gamma) v *= __ldg(gamma + c);
+  if (beta) v += __ldg(beta + c);
+  return relu ? fmaxf(v, 0.f) : v;
+}
 __global__ void bn_apply_kernel(const float* __restrict__ x, float* __restrict__ y, long total,
                                 int C, const float* __restrict__ mean,
                                 const float* __restrict__ stat, int stat_is_var, float eps,
                                 const float* __restrict__ gamma, const float* __restrict__ beta,
                                 int relu) {
+  if ((C & 3) == 0) {   // 16-byte path: 4 consecutive channels per thread
+    const long n4 = total >> 2;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
+      const int c = (int)((i << 2) % C);
+      const float4 xv = __ldg(reinterpret_cast<const float4*>(x) + i);
+      const float4 mu = __ldg(reinterpret_cast<const float4*>(mean + c));
+      float4 st = __ldg(reinterpret_cast<const float4*>(stat + c));
+      if (stat_is_var) { st.x = rsqrtf(st.x + eps); st.y = rsqrtf(st.y + eps); st.z = rsqrtf(st.z + eps); st.w = rsqrtf(st.w + eps); }
+      float4 o;
+      o.x = bn_apply_one(xv.x, mu.x, st.x, gamma, beta, c, relu);
+      o.y = bn_apply_one(xv.y, mu.y, st.y, gamma, beta, c + 1, relu);
+      o.z = bn_apply_one(xv.z, mu.z, st.z, gamma, beta, c + 2, relu);
+      o.w = bn_apply_one(xv.w, mu.w, st.w, gamma, beta, c + 3, relu);
+      reinterpret_cast<float4*>(y)[i] = o;
+    }
+    return;
+  }
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long)gridDim.x * blockDim.x) {
     const int c = (int)(i % C);
     const float inv = stat_is_var ? rsqrtf(__ldg(stat + c) + eps) : __ldg(stat + c);
-    float v = (__ldg(x + i) - __ldg(mean + c)) * inv;
-    if (gamma) v *= __ldg(gamma + c);
-    if (beta) v += __ldg(beta + c);
-    if (relu) v = fmaxf(v, 0.f);
-    y[i] = v;
+    y[i] = bn_apply_one(__ldg(x + i), __ldg(mean + c), inv, gamma, beta, c, relu);
   }
 }
 
@@ -128,6 +148,12 @@ bn_bwd_reduce_kernel(const float* __restrict__ x, const float* __restrict__ y,
 }
 
 // Backward phase 2: dx = gamma*invstd/M * (M*dy' - dbeta - xhat*dgamma)
+__device__ __forceinline__ float bn_bwd_one(float xv, float yv, float g, float mu, float inv, float gm, float dbt,
+                                            float dgm, float fM, float invM, int relu) {
+  if (relu && !(yv > 0.f)) g = 0.f;
+  const float xhat = (xv - mu) * inv;
+  return gm * inv * invM * (fM * g - dbt - xhat * dgm);
+}
 __global__ void bn_bwd_apply_kernel(const float* __restrict__ x, const float* __restrict__ y,
                                     const float* __restrict__ dy, float* __restrict__ dx,
                                     long total, long M, int C, const float* __restrict__ mean,
@@ -135,16 +161,34 @@ __global__ void bn_bwd_apply_kernel(const float* __restrict__ x, const float* __
                                     const float* __restrict__ gamma,
                                     const float* __restrict__ dbeta,
                                     const float* __restrict__ dgamma_full, int relu) {
-  const float invM = 1.f / (float)M;
+  const float invM = 1.f / (float)M, fM = (float)M;
+  if ((C & 3) == 0) {
+    const long n4 = total >> 2;
+    const float4 one4 = make_float4(1.f, 1.f, 1.f, 1.f);
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
+      const int c = (int)((i << 2) % C);
+      const float4 xv = __ldg(reinterpret_cast<const float4*>(x) + i);
+      const float4 yv = relu ? __ldg(reinterpret_cast<const float4*>(y) + i) : one4;
+      const float4 g = __ldg(reinterpret_cast<const float4*>(dy) + i);
+      const float4 mu = __ldg(reinterpret_cast<const float4*>(mean + c));
+      const float4 iv = __ldg(reinterpret_cast<const float4*>(invstd + c));
+      const float4 gm = gamma ? __ldg(reinterpret_cast<const float4*>(gamma + c)) : one4;
+      const float4 db = __ldg(reinterpret_cast<const float4*>(dbeta + c));
+      const float4 dg = __ldg(reinterpret_cast<const float4*>(dgamma_full + c));
+      float4 o;
+      o.x = bn_bwd_one(xv.x, yv.x, g.x, mu.x, iv.x, gm.x, db.x, dg.x, fM, invM, relu);
+      o.y = bn_bwd_one(xv.y, yv.y, g.y, mu.y, iv.y, gm.y, db.y, dg.y, fM, invM, relu);
+      o.z = bn_bwd_one(xv.z, yv.z, g.z, mu.z, iv.z, gm.z, db.z, dg.z, fM, invM, relu);
+      o.w = bn_bwd_one(xv.w, yv.w, g.w, mu.w, iv.w, gm.w, db.w, dg.w, fM, invM, relu);
+      reinterpret_cast<float4*>(dx)[i] = o;
+    }
+    return;
+  }
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long)gridDim.x * blockDim.x) {
     const int c = (int)(i % C);
-    float g = __ldg(dy + i);
-    if (relu && !(__ldg(y + i) > 0.f)) g = 0.f;
-    const float inv = __ldg(invstd + c);
-    const float xhat = (__ldg(x + i) - __ldg(mean + c)) * inv;
-    const float gm = gamma ? __ldg(gamma + c) : 1.f;
-    dx[i] = gm * inv * invM * ((float)M * g - __ldg(dbeta + c) - xhat * __ldg(dgamma_full + c));
+    dx[i] = bn_bwd_one(__ldg(x + i), relu ? __ldg(y + i) : 1.f, __ldg(dy + i), __ldg(mean + c), __ldg(invstd + c),
+                       gamma ? __ldg(gamma + c) : 1.f, __ldg(dbeta + c), __ldg(dgamma_full + c), fM, invM, relu);
   }
 }
 
@@ -208,17 +252,37 @@ __global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* 
 // Elementwise
 // ------------------------------------------------------------------------------------------
 __global__ void relu_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long n) {
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+  const long n4 = n >> 2;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
+    float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
+    v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
+    reinterpret_cast<float4*>(y)[i] = v;
+  }
+  for (long i = (n4 << 2) + (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
     y[i] = fmaxf(__ldg(x + i), 0.f);
 }
 __global__ void relu_bwd_kernel(const float* __restrict__ y, const float* __restrict__ dy,
                                 float* __restrict__ dx, long n) {
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+  const long n4 = n >> 2;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
+    const float4 m = __ldg(reinterpret_cast<const float4*>(y) + i);
+    float4 g = __ldg(reinterpret_cast<const float4*>(dy) + i);
+    if (!(m.x > 0.f)) g.x = 0.f; if (!(m.y > 0.f)) g.y = 0.f; if (!(m.z > 0.f)) g.z = 0.f; if (!(m.w > 0.f)) g.w = 0.f;
+    reinterpret_cast<float4*>(dx)[i] = g;
+  }
+  for (long i = (n4 << 2) + (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
     dx[i] = (__ldg(y + i) > 0.f) ? __ldg(dy + i) : 0.f;
 }
 __global__ void add_kernel(const float* __restrict__ a, const float* __restrict__ b,
                            float* __restrict__ y, long n, int relu) {
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+  const long n4 = n >> 2;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
+    const float4 u = __ldg(reinterpret_cast<const float4*>(a) + i), w = __ldg(reinterpret_cast<const float4*>(b) + i);
+    float4 v = make_float4(u.x + w.x, u.y + w.y, u.z + w.z, u.w + w.w);
+    if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+    reinterpret_cast<float4*>(y)[i] = v;
+  }
+  for (long i = (n4 << 2) + (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
     float v = __ldg(a + i) + __ldg(b + i);
     y[i] = relu ? fmaxf(v, 0.f) : v;
   }

@@ -139,6 +139,60 @@ int tfde_allreduce_fused(const void* desc, tfde_stream_t stream);
 /* dst(local) <- src(peer mapped): initial broadcast from the chief. ref: distributed_with_keras.py:58. */
 int tfde_p2p_copy(float* dst, const float* src, long n, tfde_stream_t stream);
 
+/* ---- small-batch latency kernels (csrc/kernels/small_batch.cu) -------------------------------------- */
+/* Dense forward for small M*N and long K (cluster / DSMEM split-K). ref: Dense(64) over the 5408-wide
+ * flattened activation at per-replica batch 64, distributed_with_keras.py:13,37. */
+int tfde_dense_skinny_supported(int M, int K, int N);
+size_t tfde_dense_skinny_ws_floats(int M, int K, int N);
+int tfde_dense_skinny_fwd(const float* x, const float* w, const float* bias, float* y, int M, int K, int N,
+                          int relu, float* ws, unsigned* counters, tfde_stream_t stream);
+/* Classifier head in one launch: Dense(N<=32) + sparse categorical cross-entropy (+accuracy) + backward of
+ * that Dense. ref: Dense(10) + SCCE, distributed_with_keras.py:38,41; Dense(10, softmax) + SCCE on
+ * probabilities, mnist_keras_distributed.py:108,114. */
+int tfde_head_supported(int K, int N);
+size_t tfde_head_ws_floats(int M, int K, int N);
+int tfde_head_fwd_bwd(const float* h, const float* w, const float* bias, const void* labels, int label_is_i64,
+                      float* out, float* dh, float* dw, float* db, float* out4, int M, int K, int N,
+                      int relu_mask, int from_probs, float scale, float* partials, unsigned* counter,
+                      tfde_stream_t stream);
+
+/* ---- bf16 tensor-core GEMMs: tcgen05.mma + TMEM + TMA (gemm_tcgen05.cu, gemm_tcgen05_persistent.cu) -- */
+/* C[M,N] = act(A[M,K] . B[N,K]^T + bias); A, B bf16 with K contiguous (K % 8 == 0, 16-byte aligned);
+ * exactly one of c_f32 / c_bf16 may be NULL. The first call per tile shape raises the kernel's dynamic
+ * shared-memory limit and must happen outside stream capture. ref: the cuBLAS GEMMs behind Dense / Conv2D
+ * in TensorFlow (distributed_with_keras.py:34-38), BASELINE.json configs 3 and 4. */
+int tfde_gemm_bf16_tn(const void* A, const void* B, float* c_f32, void* c_bf16, long ldc, const float* bias,
+                      int relu, int M, int N, int K, tfde_stream_t stream);
+/* persistent one-CTA-per-SM schedule, double-buffered TMEM accumulator, optional deterministic split-K
+ * through the fp32 scratch `ws` (NULL disables splitting). */
+int tfde_gemm_bf16_tn_persistent(const void* A, const void* B, float* c_f32, void* c_bf16, long ldc,
+                                 const float* bias, int relu, int M, int N, int K, float* ws, size_t ws_bytes,
+                                 tfde_stream_t stream);
+int tfde_cast_bf16(const float* x, void* y, long n, tfde_stream_t stream);
+int tfde_cast_transpose_bf16(const float* x, const float* mask, void* y, int R, int C, tfde_stream_t stream);
+
+/* ---- mixed-precision glue (mixed_ops.cu) and convolution operand builders (conv_gather.cu) ------------ */
+int tfde_cast_bf16_masked(const float* x, const float* mask, void* y, long n, tfde_stream_t stream);
+int tfde_colsum_masked(const float* x, const float* mask, float* out, long R, int C, float* partials,
+                       unsigned* counters, tfde_stream_t stream);
+/* geometry arguments: B,H,W,C,KH,KW,Ho,Wo,sh,sw,pt,pl,Cout; ld* in elements, multiples of 8.
+ * ref: Conv2D forward / filter gradient / data gradient (cuDNN in TF), mnist_keras_distributed.py:83-98. */
+int tfde_im2col_bf16(const float* x, void* out, int B, int H, int W, int C, int KH, int KW, int Ho, int Wo,
+                     int sh, int sw, int pt, int pl, int Cout, int ldo, tfde_stream_t stream);
+int tfde_im2colT_bf16(const float* x, void* out, int B, int H, int W, int C, int KH, int KW, int Ho, int Wo,
+                      int sh, int sw, int pt, int pl, int Cout, long ldo, tfde_stream_t stream);
+int tfde_dgrad_gather_bf16(const float* dy, const float* mask, void* out, int B, int H, int W, int C, int KH,
+                           int KW, int Ho, int Wo, int sh, int sw, int pt, int pl, int Cout, int ldo,
+                           tfde_stream_t stream);
+int tfde_wrot_bf16(const float* w, void* out, int KH, int KW, int Cin, int Cout, int ldo, tfde_stream_t stream);
+int tfde_cast_transpose_pad_bf16(const float* x, const float* mask, void* y, long R, int C, long ldy,
+                                 tfde_stream_t stream);
+int tfde_transpose_bf16(const void* x, void* y, long R, int C, long ldx, long ldy, tfde_stream_t stream);
+
+/* ---- diagnostics (debug_util.cu) ---------------------------------------------------------------------- */
+int tfde_capture_status(tfde_stream_t stream); /* 0 none, 1 capturing, 2 capture invalidated */
+int tfde_clear_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif
