@@ -59,6 +59,8 @@ struct ARParams {
   unsigned* done_counter;          // local ticket for the hparams advance
   int* status;                     // local [4]: code, epoch, peer, block
   unsigned long long timeout_ns;
+  long pp_lo, pp_hi;               // arena range a producer kernel may have pushed already (GEMM epilogue)
+  const uint32_t* pp_done;         // == this epoch when it did; nullptr when the feature is off
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -247,6 +249,9 @@ allreduce_fused_kernel(const ARParams p) {
 
   const long slot = p.slot_floats;
   const float* base = p.recv[R] + (size_t)parity * W * slot;   // my receive slots of this parity
+  // [pp_lo, pp_hi) was already pushed by the epilogue of the GEMM that produced it (if it ran this step)
+  const bool prepushed = p.pp_done != nullptr && *p.pp_done == e;
+  const long pp_lo = prepushed ? p.pp_lo : 0, pp_hi = prepushed ? p.pp_hi : 0;
   if (p.mode == 0) {
     // ------------------------------- one-shot -------------------------------------------
     long chunk = (p.n_total + nb - 1) / nb; chunk = (chunk + 3) & ~3L;
@@ -257,9 +262,13 @@ allreduce_fused_kernel(const ARParams p) {
     for (long i0 = t; i0 < cnt4; i0 += (long)PUSH_U * blockDim.x) {
       float4 v[PUSH_U];
 #pragma unroll
+      bool need[PUSH_U];
+#pragma unroll
       for (int u = 0; u < PUSH_U; ++u) {
         const long i = i0 + (long)u * blockDim.x;
-        if (i < cnt4) v[u] = __ldg(g4 + i);
+        const long gi = lo + (i << 2);
+        need[u] = i < cnt4 && !(gi >= pp_lo && gi < pp_hi);
+        if (need[u]) v[u] = __ldg(g4 + i);
       }
       for (int k = 1; k < W; ++k) {
         const int peer = (R + k) % W;
@@ -267,7 +276,7 @@ allreduce_fused_kernel(const ARParams p) {
 #pragma unroll
         for (int u = 0; u < PUSH_U; ++u) {
           const long i = i0 + (long)u * blockDim.x;
-          if (i < cnt4) slot_store4(dst, lo4 + i, v[u], p.wire_bf16);
+          if (need[u]) slot_store4(dst, lo4 + i, v[u], p.wire_bf16);
         }
       }
     }
@@ -295,14 +304,18 @@ allreduce_fused_kernel(const ARParams p) {
       for (long i0 = t; i0 < cnt4; i0 += (long)PUSH_U * blockDim.x) {
         float4 v[PUSH_U];
 #pragma unroll
+        bool need[PUSH_U];
+#pragma unroll
         for (int u = 0; u < PUSH_U; ++u) {
           const long i = i0 + (long)u * blockDim.x;
-          if (i < cnt4) v[u] = __ldg(g4 + i);
+          const long gi = gbeg + (i << 2);
+          need[u] = i < cnt4 && !(gi >= pp_lo && gi < pp_hi);
+          if (need[u]) v[u] = __ldg(g4 + i);
         }
 #pragma unroll
         for (int u = 0; u < PUSH_U; ++u) {
           const long i = i0 + (long)u * blockDim.x;
-          if (i < cnt4) slot_store4(dst, lo4 + i, v[u], p.wire_bf16);
+          if (need[u]) slot_store4(dst, lo4 + i, v[u], p.wire_bf16);
         }
       }
     }
@@ -397,6 +410,7 @@ struct TfdeARDesc {
   void* recv[MAX_RANKS]; void* wpeer[MAX_RANKS]; void* wbf_peer[MAX_RANKS]; void* flags[MAX_RANKS];
   void* epoch; float* metrics; void* hp; void* done_counter; void* status;
   unsigned long long timeout_ns;
+  long pp_lo, pp_hi; const void* pp_done;     // pre-pushed range (see ARParams)
 };
 
 TFDE_API size_t tfde_ar_desc_bytes() { return sizeof(TfdeARDesc); }
@@ -417,6 +431,8 @@ TFDE_API int tfde_allreduce_fused(const TfdeARDesc* d, cudaStream_t stream) {
   p.epoch = (uint32_t*)d->epoch; p.metrics = d->metrics; p.n_extra = d->n_extra;
   p.hp = (TfdeHParams*)d->hp; p.done_counter = (unsigned*)d->done_counter; p.status = (int*)d->status;
   p.timeout_ns = d->timeout_ns ? d->timeout_ns : 20000000000ULL;
+  p.pp_lo = d->pp_lo; p.pp_hi = d->pp_hi; p.pp_done = (const uint32_t*)d->pp_done;
+  if (d->wire_bf16 || (p.pp_lo & 3) || (p.pp_hi & 3)) p.pp_done = nullptr;   // pushes are fp32, 16-byte groups
   allreduce_fused_kernel<<<d->blocks, AR_THREADS, 0, stream>>>(p);
   TFDE_RETURN_LAUNCH_STATUS();
 }

@@ -31,7 +31,21 @@ struct ConvGeom {
   int Cout;
 };
 
+// Optional "push" epilogue: the filter-gradient tile is ALSO stored straight into the peers' all-reduce
+// receive slots over NVLink (GEMM -> reduce-scatter in one kernel): the transfer of the 1.38 MB dense
+// gradient overlaps the math tile by tile and the all-reduce kernel that follows skips its push phase
+// for this range. Layout contract = allreduce_p2p.cu (slot[rank] of parity (epoch+1)&1 in every peer).
+struct TfdePush {
+  int enabled, world, rank, mode;      // mode 0 one-shot (every peer gets everything), 1 two-shot (owner only)
+  long slot_floats;                    // floats per receive slot
+  long arena_off;                      // index of C[0] inside the flat gradient arena
+  float* recv[8];                      // peer-mapped receive buffers [2][world][slot_floats]
+  const uint32_t* epoch;               // all-reduce epoch counter of block 0 (device memory)
+  uint32_t* done_flag;                 // set to the epoch this push belongs to
+};
+
 struct GemmParams {
+  TfdePush push;
   const float* A; const float* Amask; int lda;
   const float* B; const float* Bmask; int ldb;
   float* C; int ldc;
@@ -331,7 +345,13 @@ __global__ void __launch_bounds__(NTHREADS) gemm_fp32_kernel(const GemmParams p)
     if (t == 0) p.counters[tile] = 0u;  // self-cleaning for the next launch
   }
 
-  // Epilogue: bias, ReLU, ones-row routing.
+  // Epilogue: bias, ReLU, ones-row routing (+ optional push of the tile into the peers' receive slots).
+  int parity = 0;
+  if (p.push.enabled) {
+    const uint32_t e = __ldg(p.push.epoch) + 1u;
+    parity = (int)(e & 1u);
+    if (t == 0 && blockIdx.x == 0 && blockIdx.y == 0) *p.push.done_flag = e;
+  }
 #pragma unroll
   for (int i = 0; i < TM; ++i) {
     const int m = m0 + ty * TM + i;
@@ -348,6 +368,17 @@ __global__ void __launch_bounds__(NTHREADS) gemm_fp32_kernel(const GemmParams p)
       if (p.bias != nullptr) v += __ldg(p.bias + n);
       if (p.relu) v = fmaxf(v, 0.f);
       p.C[(size_t)m * p.ldc + n] = v;
+      if (p.push.enabled) {
+        const long gi = p.push.arena_off + (long)m * p.ldc + n;      // index in the gradient arena
+        const size_t slot_base = ((size_t)parity * p.push.world + p.push.rank) * p.push.slot_floats;
+        if (p.push.mode == 0) {
+          for (int r = 0; r < p.push.world; ++r)
+            if (r != p.push.rank) __stcg(p.push.recv[r] + slot_base + gi, v);
+        } else {
+          const int owner = (int)(gi / p.push.slot_floats);
+          if (owner != p.push.rank) __stcg(p.push.recv[owner] + slot_base + (gi - (long)owner * p.push.slot_floats), v);
+        }
+      }
     }
   }
 }
@@ -437,6 +468,25 @@ TFDE_API int tfde_dense_wgrad(const float* x, const float* dy, const float* ymas
   p.splits = (ws && counters) ? choose_splits(p.M, N, M, ws_bytes, kMaxCounters) : 1;
   return dispatch(A_DENSE_T, B_DENSE, p, stream);
 }
+
+// tfde_dense_wgrad whose epilogue additionally pushes dw into the peers' all-reduce receive slots
+// (`push` is a TfdePush; see allreduce_p2p.cu for the slot layout). GEMM -> reduce-scatter in one kernel.
+TFDE_API int tfde_dense_wgrad_push(const float* x, const float* dy, const float* ymask, float* dw,
+                                   float* db, int M, int K, int N, float* ws, size_t ws_bytes,
+                                   unsigned* counters, const TfdePush* push, cudaStream_t stream) {
+  GemmParams p{};
+  if (push != nullptr) p.push = *push;
+  if (p.push.enabled && (p.push.world < 2 || p.push.world > 8)) return TFDE_ERR_INVALID;
+  p.A = x; p.lda = K;
+  p.B = dy; p.Bmask = ymask; p.ldb = N;
+  p.C = dw; p.ldc = N; p.C2 = db;
+  p.M = db ? K + 1 : K; p.N = N; p.K = M;
+  p.ones_row = db ? K : -1;
+  p.ws = ws; p.counters = counters;
+  p.splits = (ws && counters) ? choose_splits(p.M, N, M, ws_bytes, kMaxCounters) : 1;
+  return dispatch(A_DENSE_T, B_DENSE, p, stream);
+}
+TFDE_API size_t tfde_push_desc_bytes() { return sizeof(TfdePush); }
 
 // dx[M,K] = (dy[M,N] * (ymask > 0)) . w[K,N]^T
 TFDE_API int tfde_dense_dgrad(const float* dy, const float* ymask, const float* w, float* dx,

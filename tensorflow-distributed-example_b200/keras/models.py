@@ -242,7 +242,14 @@ class Sequential:
         self.optimizer.bind(self.device, seed=self.seed, step=self.optimizer.iterations)
         self.optimizer._bound_to = self
         if self.strategy.num_replicas_in_sync > 1:
-            self.strategy.comm().prepare(self.arena, self.optimizer)
+            ch = self.strategy.comm().prepare(self.arena, self.optimizer)
+            if hasattr(ch, "enable_fused_push"):
+                # the largest Dense kernel gradient is pushed to the peers by its own wgrad GEMM
+                dense = [l for l in self.exec_plan if isinstance(l, L.Dense) and l.kernel.size % 4 == 0]
+                if dense:
+                    big = max(dense, key=lambda l: l.kernel.size)
+                    if big.kernel.size * 4 >= (256 << 10):
+                        ch.enable_fused_push(big.kernel.grad, big.kernel.offset)
         else:
             self.optimizer.ensure_slots(self.arena)
 

@@ -140,6 +140,11 @@ def launch_count() -> int:
     return _launches
 
 
+def register_wgrad_push(grad_ptr: int, desc) -> None:
+    from . import push as _push
+    _push.register(grad_ptr, desc)
+
+
 def stream_ptr() -> int:
     return torch.cuda.current_stream().cuda_stream
 
@@ -271,8 +276,17 @@ def dense_bwd(x, w, y, dy, act="none", need_dx=True, has_bias=True, out_dx=None,
     db = None
     if has_bias:
         db = out_db if out_db is not None else torch.empty((N,), dtype=torch.float32, device=dev)
-    check(L.tfde_dense_wgrad(x.data_ptr(), dy.data_ptr(), ptr(mask), dw.data_ptr(), ptr(db), M, K, N,
-                             *_gemm_tail(wsp)), "dense_wgrad")
+    from . import push as _push
+    pd = _push.lookup(dw.data_ptr())
+    if pd is not None:
+        # GEMM -> reduce-scatter in one kernel: tiles also go straight into the peers' receive slots
+        check(L.tfde_dense_wgrad_push(x.data_ptr(), dy.data_ptr(), ptr(mask), dw.data_ptr(), ptr(db), M, K, N,
+                                      wsp.ws.data_ptr(), wsp.ws_bytes, wsp.counters.data_ptr(), ctypes.byref(pd),
+                                      stream_ptr()), "dense_wgrad_push")
+        _push.stats["pushed_launches"] += 1
+    else:
+        check(L.tfde_dense_wgrad(x.data_ptr(), dy.data_ptr(), ptr(mask), dw.data_ptr(), ptr(db), M, K, N,
+                                 *_gemm_tail(wsp)), "dense_wgrad")
     dx = None
     if need_dx:
         dx = out_dx if out_dx is not None else torch.empty((M, K), dtype=torch.float32, device=dev)

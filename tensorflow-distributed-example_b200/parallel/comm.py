@@ -132,6 +132,17 @@ class _ARDesc(ctypes.Structure):
         ("epoch", ctypes.c_void_p), ("metrics", ctypes.c_void_p), ("hp", ctypes.c_void_p),
         ("done_counter", ctypes.c_void_p), ("status", ctypes.c_void_p),
         ("timeout_ns", ctypes.c_ulonglong),
+        ("pp_lo", ctypes.c_long), ("pp_hi", ctypes.c_long), ("pp_done", ctypes.c_void_p),
+    ]
+
+
+class _PushDesc(ctypes.Structure):
+    """TfdePush of csrc/kernels/gemm_fp32.cu: lets a filter-gradient GEMM store its tiles straight into the
+    peers' receive slots (GEMM -> reduce-scatter in one kernel)."""
+    _fields_ = [
+        ("enabled", ctypes.c_int), ("world", ctypes.c_int), ("rank", ctypes.c_int), ("mode", ctypes.c_int),
+        ("slot_floats", ctypes.c_long), ("arena_off", ctypes.c_long),
+        ("recv", ctypes.c_void_p * MAX_RANKS), ("epoch", ctypes.c_void_p), ("done_flag", ctypes.c_void_p),
     ]
 
 
@@ -147,6 +158,9 @@ for _n, _a, _r in [
     ("tfde_ar_flag_bytes", [ctypes.c_int], ctypes.c_size_t),
     ("tfde_allreduce_fused", [ctypes.POINTER(_ARDesc), ctypes.c_void_p], ctypes.c_int),
     ("tfde_p2p_copy", [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p], ctypes.c_int),
+    ("tfde_dense_wgrad_push", [ctypes.c_void_p] * 5 + [ctypes.c_int] * 3 + [ctypes.c_void_p, ctypes.c_size_t,
+                               ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p], ctypes.c_int),
+    ("tfde_push_desc_bytes", [], ctypes.c_size_t),
 ]:
     native.register_optional(_n, _a, _r)
 
@@ -315,6 +329,8 @@ class P2PComm(CommBase):
                 pass
         self._buffers = []
         self._channels = {}
+        from ..ops import push as _push
+        _push.clear()      # descriptors point into the buffers just freed
 
 
 class _Channel:
@@ -375,6 +391,28 @@ class _Channel:
             dist.barrier(group=comm.strategy.group)
         log.info("p2p channel: n_total=%d mode=%s slot=%d blocks=%d wire_bf16=%s", n_total,
                  "one_shot" if self.mode == ONE_SHOT else "two_shot", self.slot, self.blocks, comm.wire_bf16)
+
+    def enable_fused_push(self, grad_view: torch.Tensor, arena_offset: int):
+        """Registers one gradient tensor (the largest dense kernel) whose wgrad GEMM pushes its tiles into
+        the peers' receive slots itself; the all-reduce kernel then skips that range when the GEMM says it
+        ran this step (pp_done == epoch)."""
+        if self.comm.world < 2 or self.comm.wire_bf16 or os.environ.get("TFDE_FUSED_PUSH", "1") != "1":
+            return False
+        n = grad_view.numel()
+        if n % 4 or arena_offset % 4 or ctypes.sizeof(_PushDesc) != native.load().tfde_push_desc_bytes():
+            return False
+        self.pp_done = torch.zeros(1, dtype=torch.int32, device=self.comm.device)
+        pd = _PushDesc()
+        pd.enabled, pd.world, pd.rank, pd.mode = 1, self.comm.world, self.comm.rank, self.mode
+        pd.slot_floats, pd.arena_off = self.slot, arena_offset
+        for r in range(self.comm.world):
+            pd.recv[r] = self.recv.peer_ptrs[r]
+        pd.epoch, pd.done_flag = self.epoch.data_ptr(), self.pp_done.data_ptr()
+        self.push_desc = pd
+        self.desc.pp_lo, self.desc.pp_hi, self.desc.pp_done = arena_offset, arena_offset + n, self.pp_done.data_ptr()
+        native.register_wgrad_push(grad_view.data_ptr(), pd)
+        log.info("fused wgrad->push enabled for arena range [%d, %d)", arena_offset, arena_offset + n)
+        return True
 
     def configure_optimizer(self, optimizer, arena: Arena):
         """Allocates optimizer slots with the layout this channel's mode needs (two-shot: only the owned

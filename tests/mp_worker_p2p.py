@@ -125,6 +125,10 @@ def check_model(strategy, graph):
     close = all(np.allclose(a, b, rtol=5e-3, atol=2e-4) for a, b in zip(m.get_weights(), mc.get_weights()))
     if not close:
         print(f"[rank {rank}] FAIL model weights differ from cpu reference", flush=True)
+    from tfde_b200.ops import push as _push
+    if os.environ.get("TFDE_FUSED_PUSH", "1") == "1" and _push.stats["pushed_launches"] == 0:
+        print(f"[rank {rank}] FAIL fused wgrad->push was never used", flush=True)
+        ok = False
     if graph and not m.graph_captured:
         print(f"[rank {rank}] FAIL graph not captured", flush=True)
         ok = False
