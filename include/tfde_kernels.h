@@ -189,6 +189,19 @@ int tfde_cast_transpose_pad_bf16(const float* x, const float* mask, void* y, lon
                                  tfde_stream_t stream);
 int tfde_transpose_bf16(const void* x, void* y, long R, int C, long ldx, long ldy, tfde_stream_t stream);
 
+/* ---- parameter-server push / pull over peer memory (ps_p2p.cu) ---------------------------------------- */
+/* Asynchronous SGD on an owner GPU's shard: push adds -lr*g with NVLink reduction atomics (no barrier),
+ * pull copies the owner's current values. ref: ParameterServerStrategy, mnist_keras_distributed.py:241-242,
+ * tf2_mnist_distributed.py:189 (gRPC RecvTensor in TF). */
+int tfde_ps_push(float* w_owner, const float* g, long n, float lr, tfde_stream_t stream);
+int tfde_ps_pull(float* w_local, const float* w_owner, long n, tfde_stream_t stream);
+/* tfde_dense_wgrad whose epilogue also stores the tiles into the peers' all-reduce receive slots
+ * (`push` is a TfdePush, gemm_fp32.cu): GEMM -> reduce-scatter in one kernel. */
+int tfde_dense_wgrad_push(const float* x, const float* dy, const float* ymask, float* dw, float* db, int M,
+                          int K, int N, float* ws, size_t ws_bytes, unsigned* counters, const void* push,
+                          tfde_stream_t stream);
+size_t tfde_push_desc_bytes(void);
+
 /* ---- diagnostics (debug_util.cu) ---------------------------------------------------------------------- */
 int tfde_capture_status(tfde_stream_t stream); /* 0 none, 1 capturing, 2 capture invalidated */
 int tfde_clear_last_error(void);

@@ -135,6 +135,38 @@ def check_model(strategy, graph):
     return ok and same and close
 
 
+def check_ps_push_pull(strategy):
+    """G16: every rank pushes -lr*g into rank 0's shard with NVLink reduction atomics, then pulls it."""
+    import ctypes
+    L = native.load()
+    L.tfde_ps_push.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long, ctypes.c_float, ctypes.c_void_p]
+    L.tfde_ps_pull.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p]
+    comm = strategy.comm()
+    rank, world = strategy.rank, strategy.world_size
+    n = 100003
+    shard = comm.symm_empty(n + 1, "ps_shard")        # owner copy lives on rank 0
+    buf = comm.buffer_of(shard)
+    w0 = torch.randn(n, generator=torch.Generator().manual_seed(9))
+    if rank == 0:
+        shard[:n] = w0.to(strategy.device)
+    torch.cuda.synchronize(); dist.barrier()
+    g = torch.randn(n, generator=torch.Generator().manual_seed(50 + rank)).to(strategy.device)
+    native.check(L.tfde_ps_push(buf.peer_ptrs[0], g.data_ptr(), n, 0.1, native.stream_ptr()), "ps_push")
+    torch.cuda.synchronize(); dist.barrier()
+    local = torch.empty(n, device=strategy.device)
+    native.check(L.tfde_ps_pull(local.data_ptr(), buf.peer_ptrs[0], n, native.stream_ptr()), "ps_pull")
+    torch.cuda.synchronize()
+    exp = w0.double()
+    for r in range(world):
+        exp = exp - 0.1 * torch.randn(n, generator=torch.Generator().manual_seed(50 + r)).double()
+    err = (local.cpu().double() - exp).abs().max().item()
+    ok = err < 1e-5
+    if not ok:
+        print(f"[rank {rank}] FAIL ps push/pull err {err:.3e}", flush=True)
+    dist.barrier()
+    return ok
+
+
 def sweep(strategy, out_path):
     """Fused all-reduce(+SGD) bus bandwidth: S/t * 2(N-1)/N, device-timed, max over ranks."""
     comm = strategy.comm()
@@ -224,6 +256,7 @@ def main():
     ok &= check_fused(strategy, 347146, "sgd", "one_shot", wire_bf16=True)
     ok &= check_fused(strategy, 347146, "adam", "two_shot", wire_bf16=True)
     strategy.comm().wire_bf16 = False
+    ok &= check_ps_push_pull(strategy)
     ok &= check_model(strategy, graph=False)
     ok &= check_model(strategy, graph=True)
     flag = torch.tensor([1.0 if ok else 0.0], dtype=torch.float64)
