@@ -368,15 +368,34 @@ __global__ void __launch_bounds__(NTHREADS) gemm_fp32_kernel(const GemmParams p)
       if (p.bias != nullptr) v += __ldg(p.bias + n);
       if (p.relu) v = fmaxf(v, 0.f);
       p.C[(size_t)m * p.ldc + n] = v;
-      if (p.push.enabled) {
-        const long gi = p.push.arena_off + (long)m * p.ldc + n;      // index in the gradient arena
+    }
+    if (p.push.enabled && m != p.ones_row) {
+      // push this row's 4 finished outputs (no bias / activation on a filter gradient) as one 16-byte
+      // NVLink store per destination; ranges are 16-byte aligned by construction (arena offsets % 4 == 0)
+      const int nq = n0 + tx * TN;
+      if (nq < p.N) {
+        const long gi = p.push.arena_off + (long)m * p.ldc + nq;      // index in the gradient arena
         const size_t slot_base = ((size_t)parity * p.push.world + p.push.rank) * p.push.slot_floats;
+        const bool vec = (TN == 4) && (nq + 3 < p.N) && ((gi & 3) == 0);
+        const float4 v4 = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
         if (p.push.mode == 0) {
-          for (int r = 0; r < p.push.world; ++r)
-            if (r != p.push.rank) __stcg(p.push.recv[r] + slot_base + gi, v);
+          for (int r = 0; r < p.push.world; ++r) {
+            if (r == p.push.rank) continue;
+            float* dst = p.push.recv[r] + slot_base + gi;
+            if (vec) __stcg(reinterpret_cast<float4*>(dst), v4);
+            else for (int j = 0; j < TN && nq + j < p.N; ++j) __stcg(dst + j, acc[i][j]);
+          }
         } else {
-          const int owner = (int)(gi / p.push.slot_floats);
-          if (owner != p.push.rank) __stcg(p.push.recv[owner] + slot_base + (gi - (long)owner * p.push.slot_floats), v);
+          // a 4-group never straddles two owners: slot_floats % 4 == 0 and gi % 4 == 0 on the vector path
+          for (int j0 = 0; j0 < TN; j0 += (vec ? TN : 1)) {
+            if (nq + j0 >= p.N) break;
+            const long g = gi + j0;
+            const int owner = (int)(g / p.push.slot_floats);
+            if (owner == p.push.rank) continue;
+            float* dst = p.push.recv[owner] + slot_base + (g - (long)owner * p.push.slot_floats);
+            if (vec) __stcg(reinterpret_cast<float4*>(dst), v4);
+            else __stcg(dst, acc[i][j0]);
+          }
         }
       }
     }
