@@ -73,6 +73,8 @@ class _Slot:
         self.host_tail = torch.zeros(4, dtype=torch.float32).pin_memory()
         self.graph = None
         self.event = None
+        self.dev_y = None      # CUDA-tensor aliases of the pinned buffers (zero-copy), created lazily
+        self.dev_tail = None
 
 
 class _GraphState:
@@ -418,11 +420,26 @@ class Sequential:
                 if slot.graph is None:
                     it0 = self.optimizer.iterations
                     g = torch.cuda.CUDAGraph()
+                    zero_copy = os.environ.get("TFDE_ZERO_COPY", "1") == "1"
+                    if zero_copy and slot.dev_y is None:
+                        try:   # labels are read, and the metrics tail is written, straight through PCIe
+                            from ..ops import hostmem
+                            slot.dev_y = hostmem.device_alias(slot.host_y, self.device)
+                            slot.dev_tail = hostmem.device_alias(slot.host_tail, self.device)
+                        except Exception as ex:  # noqa: BLE001  (no UVA alias: fall back to memcpy nodes)
+                            log.warning("zero-copy staging unavailable (%s); using memcpy nodes", ex)
+                            slot.dev_y = slot.dev_tail = None
+                            zero_copy = False
                     with _capture(g, self._stream):
                         st.in_x.copy_(slot.host_x, non_blocking=True)
-                        st.in_y.copy_(slot.host_y, non_blocking=True)
-                        self._step_body(st.in_x, st.in_y, gb)
-                        slot.host_tail.copy_(self.arena.tail, non_blocking=True)
+                        if zero_copy and slot.dev_y is not None:
+                            from ..ops import hostmem
+                            self._step_body(st.in_x, slot.dev_y, gb)
+                            hostmem.copy_small(slot.dev_tail, self.arena.tail)
+                        else:
+                            st.in_y.copy_(slot.host_y, non_blocking=True)
+                            self._step_body(st.in_x, st.in_y, gb)
+                            slot.host_tail.copy_(self.arena.tail, non_blocking=True)
                     self.optimizer.iterations = it0   # capture did not execute anything
                     slot.graph = g
                     slot.event = torch.cuda.Event()
