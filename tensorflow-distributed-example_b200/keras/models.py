@@ -345,6 +345,7 @@ class Sequential:
             dgrad = self._in_buf("dloss", out.shape)
             ops.xent(out, y, 1.0 / float(global_batch), self.loss.from_probs, out_grad=dgrad, out4=a.grad_tail)
             self._backward(dgrad)
+        self.join_forks()              # filter-gradient GEMMs forked onto the side stream are done
         if asynchronous:
             st.push(self)              # the owner applies w -= lr*g without waiting for other workers
             a.w[a.n:] = a.g[a.n:]
@@ -355,6 +356,21 @@ class Sequential:
             self.optimizer.iterations += 1
         else:
             self.optimizer.apply_local(a)
+
+    def fork_stream(self):
+        """Side stream on which layers may run work that only the optimizer consumes (filter gradients)
+        concurrently with the rest of backward. None when disabled."""
+        if self.device.type != "cuda" or os.environ.get("TFDE_FORK_WGRAD", "1") != "1":
+            return None
+        if getattr(self, "_side_stream", None) is None:
+            self._side_stream = torch.cuda.Stream(device=self.device)
+        self._forked = True
+        return self._side_stream
+
+    def join_forks(self):
+        if getattr(self, "_forked", False):
+            torch.cuda.current_stream(self.device).wait_stream(self._side_stream)
+            self._forked = False
 
     def _fusable_head(self, x):
         """The last Dense layer when Dense + loss + its backward can run as the fused head kernel."""

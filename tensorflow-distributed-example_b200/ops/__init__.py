@@ -78,9 +78,9 @@ def dense_fwd(x, w, bias=None, act="none", out=None):
 
 
 def dense_bwd(x, w, y, dy, act="none", need_dx=True, has_bias=True, out_dx=None, out_dw=None,
-              out_db=None, scratch=None):
+              out_db=None, scratch=None, side_stream=None):
     if _cuda(x):
-        return native.dense_bwd(x, w, y, dy, act, need_dx, has_bias, out_dx, out_dw, out_db, scratch)
+        return native.dense_bwd(x, w, y, dy, act, need_dx, has_bias, out_dx, out_dw, out_db, scratch, side_stream)
     dx, dw, db = ref.dense_bwd(x, w, y, dy, act, need_dx, has_bias)
     return (_put(out_dx, dx) if dx is not None else None, _put(out_dw, dw),
             _put(out_db, db) if db is not None else None)

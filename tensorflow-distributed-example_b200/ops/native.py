@@ -257,7 +257,10 @@ def dense_fwd(x, w, bias=None, act="none", out=None):
 
 
 def dense_bwd(x, w, y, dy, act="none", need_dx=True, has_bias=True, out_dx=None, out_dw=None,
-              out_db=None, scratch=None):
+              out_db=None, scratch=None, side_stream=None):
+    """``side_stream``: when given (and a data gradient is needed) the filter-gradient GEMM is forked onto
+    it and runs concurrently with the data-gradient GEMM; the caller joins the side stream before anything
+    consumes dw/db (the optimizer / all-reduce). Captured CUDA graphs keep the two branches parallel."""
     L = load()
     _f32c(x, "x"); _f32c(w, "w"); _f32c(dy, "dy")
     M, K = x.shape
@@ -278,15 +281,24 @@ def dense_bwd(x, w, y, dy, act="none", need_dx=True, has_bias=True, out_dx=None,
         db = out_db if out_db is not None else torch.empty((N,), dtype=torch.float32, device=dev)
     from . import push as _push
     pd = _push.lookup(dw.data_ptr())
-    if pd is not None:
-        # GEMM -> reduce-scatter in one kernel: tiles also go straight into the peers' receive slots
-        check(L.tfde_dense_wgrad_push(x.data_ptr(), dy.data_ptr(), ptr(mask), dw.data_ptr(), ptr(db), M, K, N,
-                                      wsp.ws.data_ptr(), wsp.ws_bytes, wsp.counters.data_ptr(), ctypes.byref(pd),
-                                      stream_ptr()), "dense_wgrad_push")
-        _push.stats["pushed_launches"] += 1
+
+    def launch_wgrad(ws_):
+        if pd is not None:
+            # GEMM -> reduce-scatter in one kernel: tiles also go straight into the peers' receive slots
+            check(L.tfde_dense_wgrad_push(x.data_ptr(), dy.data_ptr(), ptr(mask), dw.data_ptr(), ptr(db), M, K, N,
+                                          ws_.ws.data_ptr(), ws_.ws_bytes, ws_.counters.data_ptr(), ctypes.byref(pd),
+                                          stream_ptr()), "dense_wgrad_push")
+            _push.stats["pushed_launches"] += 1
+        else:
+            check(L.tfde_dense_wgrad(x.data_ptr(), dy.data_ptr(), ptr(mask), dw.data_ptr(), ptr(db), M, K, N,
+                                     *_gemm_tail(ws_)), "dense_wgrad")
+
+    if side_stream is not None and need_dx:
+        side_stream.wait_stream(torch.cuda.current_stream(dev))      # fork: inputs are ready
+        with torch.cuda.stream(side_stream):
+            launch_wgrad(Workspace.current(dev))                     # the side stream has its own scratch
     else:
-        check(L.tfde_dense_wgrad(x.data_ptr(), dy.data_ptr(), ptr(mask), dw.data_ptr(), ptr(db), M, K, N,
-                                 *_gemm_tail(wsp)), "dense_wgrad")
+        launch_wgrad(wsp)
     dx = None
     if need_dx:
         dx = out_dx if out_dx is not None else torch.empty((M, K), dtype=torch.float32, device=dev)
