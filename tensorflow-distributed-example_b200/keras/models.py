@@ -75,6 +75,9 @@ class _Slot:
         self.event = None
         self.dev_y = None      # CUDA-tensor aliases of the pinned buffers (zero-copy), created lazily
         self.dev_tail = None
+        self.overlap = False   # image H2D on a copy stream into dev_x, overlapping the previous step
+        self.dev_x = None
+        self.copy_event = None
 
 
 class _GraphState:
@@ -446,19 +449,38 @@ class Sequential:
                             log.warning("zero-copy staging unavailable (%s); using memcpy nodes", ex)
                             slot.dev_y = slot.dev_tail = None
                             zero_copy = False
+                    slot.overlap = zero_copy and slot.dev_y is not None and os.environ.get("TFDE_OVERLAP_H2D", "1") == "1"
+                    if slot.overlap:
+                        # the image H2D copy is issued on a copy stream into this slot's own device buffer,
+                        # so it overlaps the previous step; the graph waits for it through an event
+                        if getattr(self, "_copy_stream", None) is None:
+                            self._copy_stream = torch.cuda.Stream(device=self.device)
+                        slot.dev_x = torch.empty_like(st.in_x)
+                        slot.copy_event = torch.cuda.Event()
+                        slot.dev_x.copy_(slot.host_x)
                     with _capture(g, self._stream):
-                        st.in_x.copy_(slot.host_x, non_blocking=True)
-                        if zero_copy and slot.dev_y is not None:
+                        if slot.overlap:
                             from ..ops import hostmem
+                            self._step_body(slot.dev_x, slot.dev_y, gb)
+                            hostmem.copy_small(slot.dev_tail, self.arena.tail)
+                        elif zero_copy and slot.dev_y is not None:
+                            from ..ops import hostmem
+                            st.in_x.copy_(slot.host_x, non_blocking=True)
                             self._step_body(st.in_x, slot.dev_y, gb)
                             hostmem.copy_small(slot.dev_tail, self.arena.tail)
                         else:
+                            st.in_x.copy_(slot.host_x, non_blocking=True)
                             st.in_y.copy_(slot.host_y, non_blocking=True)
                             self._step_body(st.in_x, st.in_y, gb)
                             slot.host_tail.copy_(self.arena.tail, non_blocking=True)
                     self.optimizer.iterations = it0   # capture did not execute anything
                     slot.graph = g
                     slot.event = torch.cuda.Event()
+                if slot.overlap:
+                    with torch.cuda.stream(self._copy_stream):
+                        slot.dev_x.copy_(slot.host_x, non_blocking=True)
+                        slot.copy_event.record(self._copy_stream)
+                    self._stream.wait_event(slot.copy_event)
                 slot.graph.replay()
                 slot.event.record(self._stream)
                 self._host_tail = slot.host_tail
