@@ -229,6 +229,7 @@ __device__ __forceinline__ void store_bf16_shadow(__nv_bfloat16* dst, long gi, c
 
 __global__ void __launch_bounds__(AR_THREADS)
 allreduce_fused_kernel(const ARParams p) {
+  TFDE_PDL_PROLOGUE();
   const int b = blockIdx.x, nb = gridDim.x, t = threadIdx.x;
   __shared__ uint32_t s_e;
   if (t == 0) s_e = p.epoch[b] + 1u;
@@ -433,7 +434,7 @@ TFDE_API int tfde_allreduce_fused(const TfdeARDesc* d, cudaStream_t stream) {
   p.timeout_ns = d->timeout_ns ? d->timeout_ns : 20000000000ULL;
   p.pp_lo = d->pp_lo; p.pp_hi = d->pp_hi; p.pp_done = (const uint32_t*)d->pp_done;
   if (d->wire_bf16 || (p.pp_lo & 3) || (p.pp_hi & 3)) p.pp_done = nullptr;   // pushes are fp32, 16-byte groups
-  allreduce_fused_kernel<<<d->blocks, AR_THREADS, 0, stream>>>(p);
+  tfde_launch(allreduce_fused_kernel, dim3(d->blocks), dim3(AR_THREADS), 0, stream, p);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 

@@ -22,6 +22,7 @@ conv3x3c1_relu_pool_fwd_kernel(const void* __restrict__ xin, const float* __rest
                                const float* __restrict__ bias, float* __restrict__ pooled,
                                uint8_t* __restrict__ idx, int Bn, int H, int W, int PH, int PW,
                                float in_scale) {
+  TFDE_PDL_PROLOGUE();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float wr[9];
 #pragma unroll
@@ -69,6 +70,7 @@ conv3x3c1_relu_pool_bwd_kernel(const void* __restrict__ xin, const float* __rest
                                float* __restrict__ dw, float* __restrict__ db,
                                float* __restrict__ partials, unsigned* __restrict__ counter,
                                int Bn, int H, int W, int PH, int PW, float in_scale) {
+  TFDE_PDL_PROLOGUE();
   __shared__ float s_patch[WARPS][16];
   __shared__ __align__(16) float s_red[WARPS][10][32];
   __shared__ int s_last;
@@ -177,9 +179,9 @@ TFDE_API int tfde_conv3x3c1_relu_pool_fwd(const void* x, int x_is_u8, float in_s
   const int PH = (H - 2) / 2, PW = (W - 2) / 2;
   const int grid = grid_for((long)Bn * PH * PW);
   if (x_is_u8)
-    conv3x3c1_relu_pool_fwd_kernel<true><<<grid, WARPS * 32, 0, stream>>>(x, w, bias, pooled, idx, Bn, H, W, PH, PW, in_scale);
+    tfde_launch(conv3x3c1_relu_pool_fwd_kernel<true>, dim3(grid), dim3(WARPS * 32), 0, stream, x, w, bias, pooled, idx, Bn, H, W, PH, PW, in_scale);
   else
-    conv3x3c1_relu_pool_fwd_kernel<false><<<grid, WARPS * 32, 0, stream>>>(x, w, bias, pooled, idx, Bn, H, W, PH, PW, 1.f);
+    tfde_launch(conv3x3c1_relu_pool_fwd_kernel<false>, dim3(grid), dim3(WARPS * 32), 0, stream, x, w, bias, pooled, idx, Bn, H, W, PH, PW, 1.f);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
@@ -198,8 +200,8 @@ TFDE_API int tfde_conv3x3c1_relu_pool_bwd(const void* x, int x_is_u8, float in_s
   if (blocks > 148L * 2) blocks = 148L * 2;
   const int grid = (int)blocks;
   if (x_is_u8)
-    conv3x3c1_relu_pool_bwd_kernel<true><<<grid, WARPS * 32, 0, stream>>>(x, pooled, idx, dpooled, dw, db, partials, counter, Bn, H, W, PH, PW, in_scale);
+    tfde_launch(conv3x3c1_relu_pool_bwd_kernel<true>, dim3(grid), dim3(WARPS * 32), 0, stream, x, pooled, idx, dpooled, dw, db, partials, counter, Bn, H, W, PH, PW, in_scale);
   else
-    conv3x3c1_relu_pool_bwd_kernel<false><<<grid, WARPS * 32, 0, stream>>>(x, pooled, idx, dpooled, dw, db, partials, counter, Bn, H, W, PH, PW, 1.f);
+    tfde_launch(conv3x3c1_relu_pool_bwd_kernel<false>, dim3(grid), dim3(WARPS * 32), 0, stream, x, pooled, idx, dpooled, dw, db, partials, counter, Bn, H, W, PH, PW, 1.f);
   TFDE_RETURN_LAUNCH_STATUS();
 }

@@ -15,10 +15,11 @@ TFDE_API int tfde_clear_last_error() { return (int)cudaGetLastError(); }
 // 4-float metrics tail into device-mapped pinned host memory: a 2 us kernel node instead of a ~6 us memcpy
 // node, and the host reads it after waiting on the step's event.
 __global__ void copy_small_kernel(float* __restrict__ dst, const float* __restrict__ src, int n) {
+  TFDE_PDL_PROLOGUE();
   for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
 }
 TFDE_API int tfde_copy_small(float* dst, const float* src, int n, cudaStream_t stream) {
   if (n < 0 || n > 1024) return TFDE_ERR_INVALID;
-  copy_small_kernel<<<1, 64, 0, stream>>>(dst, src, n);
+  tfde_launch(copy_small_kernel, dim3(1), dim3(64), 0, stream, dst, src, n);
   TFDE_RETURN_LAUNCH_STATUS();
 }

@@ -197,6 +197,7 @@ template <> struct BLoader<B_WROT> {  // B_op[(kh,kw,co), ci] = W[kh,kw,ci,co]
 template <int AM, int BM_, int BMODE, int BN_, int TM, int TN, int BK_ = 16>
 __global__ void __launch_bounds__(NTHREADS) gemm_fp32_kernel(const GemmParams p) {
   static_assert((BM_ / TM) * (BN_ / TN) == NTHREADS, "tile/thread mismatch");
+  TFDE_PDL_PROLOGUE();
   // k-tile depth of this instantiation (shadows the file-level default). BK_ = 64 is used when the whole
   // reduction fits one tile (K <= 64: the batch-64 wgrad/dgrad GEMMs) so every load is in flight at once.
   constexpr int BK = BK_;
@@ -407,16 +408,16 @@ int launch_cfg(const GemmParams& p, cudaStream_t stream) {
   // Tile shape by N: the reference's layers have N in {6,10,12,24,32,64,200}.
   if (p.N <= 16) {
     dim3 grid((p.N + 15) / 16, (p.M + 255) / 256, p.splits);
-    gemm_fp32_kernel<AM, 256, BMODE, 16, 4, 4><<<grid, NTHREADS, 0, stream>>>(p);
+    tfde_launch(gemm_fp32_kernel<AM, 256, BMODE, 16, 4, 4>, grid, dim3(NTHREADS), 0, stream, p);
   } else if (p.N <= 32) {
     dim3 grid((p.N + 31) / 32, (p.M + 127) / 128, p.splits);
-    gemm_fp32_kernel<AM, 128, BMODE, 32, 4, 4><<<grid, NTHREADS, 0, stream>>>(p);
+    tfde_launch(gemm_fp32_kernel<AM, 128, BMODE, 32, 4, 4>, grid, dim3(NTHREADS), 0, stream, p);
   } else {
     dim3 grid((p.N + 63) / 64, (p.M + 63) / 64, p.splits);
     if (p.K <= 64 && p.splits == 1 && (AM == A_DENSE || AM == A_DENSE_T))
-      gemm_fp32_kernel<AM, 64, BMODE, 64, 4, 4, 64><<<grid, NTHREADS, 0, stream>>>(p);   // one deep k tile
+      tfde_launch(gemm_fp32_kernel<AM, 64, BMODE, 64, 4, 4, 64>, grid, dim3(NTHREADS), 0, stream, p);   // one deep k tile
     else
-      gemm_fp32_kernel<AM, 64, BMODE, 64, 4, 4><<<grid, NTHREADS, 0, stream>>>(p);
+      tfde_launch(gemm_fp32_kernel<AM, 64, BMODE, 64, 4, 4>, grid, dim3(NTHREADS), 0, stream, p);
   }
   TFDE_RETURN_LAUNCH_STATUS();
 }

@@ -20,6 +20,7 @@ __global__ void __launch_bounds__(XW * 32)
 xent_kernel(const float* __restrict__ in, const void* __restrict__ labels, int label_is_i64,
             float* __restrict__ dgrad, int rows, int C, float scale, float* __restrict__ partials,
             unsigned* __restrict__ counter, float* __restrict__ out4) {
+  TFDE_PDL_PROLOGUE();
   __shared__ float s_l[XW], s_c[XW];
   __shared__ int s_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -119,6 +120,7 @@ __device__ __forceinline__ void hparams_advance(TfdeHParams* hp) {
 // The last block to finish advances the device-side step / Adam powers: by then every block has
 // consumed the old values, so no second launch and no cooperative grid sync is needed.
 __global__ void optimizer_kernel(OptArgs a, TfdeHParams* hp, unsigned* __restrict__ counter) {
+  TFDE_PDL_PROLOGUE();
   const float lr = hp->lr, mu = hp->momentum, b1 = hp->beta1, b2 = hp->beta2, eps = hp->eps;
   const float gs = hp->grad_scale;
   // Adam bias correction for step t = hp->step + 1, powers maintained on device.
@@ -157,9 +159,9 @@ TFDE_API int tfde_xent(const float* in, const void* labels, int label_is_i64, fl
   if (grid > 148 * 2) grid = 148 * 2;
   if (grid < 1) grid = 1;
   if (from_probs)
-    xent_kernel<1><<<grid, XW * 32, 0, stream>>>(in, labels, label_is_i64, dgrad, rows, C, scale, partials, counter, out4);
+    tfde_launch(xent_kernel<1>, dim3(grid), dim3(XW * 32), 0, stream, in, labels, label_is_i64, dgrad, rows, C, scale, partials, counter, out4);
   else
-    xent_kernel<0><<<grid, XW * 32, 0, stream>>>(in, labels, label_is_i64, dgrad, rows, C, scale, partials, counter, out4);
+    tfde_launch(xent_kernel<0>, dim3(grid), dim3(XW * 32), 0, stream, in, labels, label_is_i64, dgrad, rows, C, scale, partials, counter, out4);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
@@ -172,7 +174,7 @@ TFDE_API int tfde_optimizer_apply(float* w, const float* g, float* s1, float* s2
   long grid = (n + 255) / 256;
   if (grid > 148L * 8) grid = 148L * 8;
   if (grid < 1) grid = 1;
-  optimizer_kernel<<<(int)grid, 256, 0, stream>>>(a, (TfdeHParams*)hparams, counter);
+  tfde_launch(optimizer_kernel, dim3((unsigned)grid), dim3(256), 0, stream, a, (TfdeHParams*)hparams, counter);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 

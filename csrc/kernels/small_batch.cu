@@ -50,6 +50,7 @@ __device__ __forceinline__ void cp_async_wait_all() {
 
 __global__ void __cluster_dims__(SK_CLUSTER, 1, 1) __launch_bounds__(SK_THREADS)
 dense_skinny_fwd_kernel(const SkinnyParams p) {
+  TFDE_PDL_PROLOGUE();
   __shared__ __align__(16) float xs[SK_TM][SK_XLD];      // x slice  [64 rows][kper]
   __shared__ __align__(16) float wsm[SK_KMAX][SK_TN];    // W slice  [kper][64 cols]
   // this CTA's partial tile (read by cluster peers) re-uses the x slice once the products are done
@@ -179,6 +180,7 @@ struct HeadParams {
 // dynamic shared memory: hs[rpb][K+1] | wsm[K][N] | zs[rpb][N] (logits -> probs -> dz) | bias | red
 __global__ void __launch_bounds__(HD_THREADS)
 head_fwd_bwd_kernel(const HeadParams p) {
+  TFDE_PDL_PROLOGUE();
   extern __shared__ __align__(16) float hsm[];
   const int K = p.K, N = p.N, KP = K + 1;
   const int HD_ROWS = p.rpb;
@@ -348,7 +350,7 @@ TFDE_API int tfde_dense_skinny_fwd(const float* x, const float* w, const float* 
   if (nclusters > 32) return TFDE_ERR_INVALID;   // K > 16384: not a job for this kernel
   SkinnyParams p{x, w, bias, y, M, N, K, kper, nclusters, relu, ws, counters};
   dim3 grid(nclusters * SK_CLUSTER, tiles);
-  dense_skinny_fwd_kernel<<<grid, SK_THREADS, 0, stream>>>(p);
+  tfde_launch(dense_skinny_fwd_kernel, grid, dim3(SK_THREADS), 0, stream, p);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
@@ -378,6 +380,6 @@ TFDE_API int tfde_head_fwd_bwd(const float* h, const float* w, const float* bias
   }
   HeadParams p{h, w, bias, labels, label_is_i64, out, dh, dw, db, out4, M, K, N, relu_mask, from_probs, rpb, scale,
                partials, counter};
-  head_fwd_bwd_kernel<<<(M + rpb - 1) / rpb, HD_THREADS, smem, stream>>>(p);
+  tfde_launch(head_fwd_bwd_kernel, dim3((M + rpb - 1) / rpb), dim3(HD_THREADS), smem, stream, p);
   TFDE_RETURN_LAUNCH_STATUS();
 }
