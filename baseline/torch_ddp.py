@@ -59,14 +59,16 @@ def run(args, METRIC, ClockSampler, max_over_ranks, barrier, dist_env, make_batc
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     ends = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     sampler = ClockSampler(local)
-    barrier(world); torch.cuda.synchronize(); sampler.start()
+    sampler.start()
+    time.sleep(0.05)
+    barrier(world); torch.cuda.synchronize(); sampler.begin()
     for i in range(K):
         if flush is not None:
             flush.fill_(i & 0xFF)
         starts[i].record()
         step(in_x, in_y)
         ends[i].record()
-    torch.cuda.synchronize(); barrier(world)
+    torch.cuda.synchronize(); sampler.end(); barrier(world)
     clocks = sampler.stop()
     dev_ms = max_over_ranks(sum(s.elapsed_time(e) for s, e in zip(starts, ends)), world)
     del flush

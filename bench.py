@@ -60,34 +60,94 @@ def parse_args():
 
 
 class ClockSampler:
-    """nvidia-smi sampling DURING the timed region (B200_PROFILING.md clocks line)."""
+    """SM clock + throttle-reason sampling DURING the timed region (B200_PROFILING.md clocks line).
+
+    Reads the counters nvidia-smi prints (clocks.sm, clocks.max.sm, clocks_event_reasons.*) through NVML
+    in-process, every few milliseconds, from a thread. Spawning ``nvidia-smi -lms`` next to a 40 ms timed
+    region does not work: its start-up (NVML attach to every GPU) is longer than the region and perturbs
+    kernel launches on all ranks, so the samples land after the fact. ``begin()``/``end()`` mark the timed
+    window; only samples inside it are reported. Falls back to an nvidia-smi subprocess without pynvml."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+               0x4: "sw_power_cap", 0x80: "hw_power_brake_slowdown"}
 
-    def __init__(self, gpu_index=0):
-        self.gpu_index = gpu_index
+    def __init__(self, gpu_index=0, period_s=0.004):
+        self.gpu_index, self.period_s = gpu_index, period_s
         self.proc = None
         self.lines = []
+        self.samples = []          # (t, sm_mhz, reason_mask)
+        self.windows = []
+        self._stop = threading.Event()
+        self._nvml = None
+        self.max_mhz = None
+
+    def _nvml_handle(self):
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            import torch
+            uuid = str(torch.cuda.get_device_properties(self.gpu_index).uuid)
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.gpu_index)
+        return pynvml, h
 
     def start(self):
         try:
+            self._nvml, self._h = self._nvml_handle()
+            self.max_mhz = float(self._nvml.nvmlDeviceGetMaxClockInfo(self._h, self._nvml.NVML_CLOCK_SM))
+            self._t = threading.Thread(target=self._poll, daemon=True)
+            self._t.start()
+            return
+        except Exception:
+            self._nvml = None
+        try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
                  "-i", str(self.gpu_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self._t = threading.Thread(target=self._read, daemon=True)
             self._t.start()
         except Exception:
             self.proc = None
 
+    def begin(self):
+        self._w0 = time.perf_counter()
+
+    def end(self):
+        self.windows.append((self._w0, time.perf_counter()))
+
+    def _poll(self):
+        n = self._nvml
+        reasons = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self._stop.is_set():
+            try:
+                self.samples.append((time.perf_counter(), float(n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM)),
+                                     int(reasons(self._h))))
+            except Exception:
+                pass
+            self._stop.wait(self.period_s)
+
     def _read(self):
         for line in self.proc.stdout:
             self.lines.append(line.strip())
 
     def stop(self):
+        if self._nvml is not None:
+            self._stop.set()
+            self._t.join(timeout=1)
+            inside = [x for x in self.samples if any(a <= x[0] <= b for a, b in self.windows)] if self.windows else []
+            use = inside or self.samples
+            mask = 0
+            for x in use:
+                mask |= x[2]
+            return {"sm_mhz": statistics.median([x[1] for x in use]) if use else None, "sm_max_mhz": self.max_mhz,
+                    "samples": len(use), "samples_inside_timed_region": len(inside), "source": "nvml",
+                    "reasons": sorted(v for k, v in self.REASONS.items() if mask & k)}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.05)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
@@ -107,7 +167,7 @@ class ClockSampler:
                 if val.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "source": "nvidia-smi", "reasons": sorted(reasons)}
 
 
 def dist_env():
@@ -177,6 +237,8 @@ def run_ours(args):
     if args.model == "b":
         xs = [x.reshape(B, 784).float().div_(255.0).pin_memory() for x in xs]
 
+    sampler = ClockSampler(local)
+    sampler.start()        # started before the warm-up so that its own start-up is outside the timed regions
     # ---- warm-up (>= 3): eager steps, graph capture, first replays ---------------------------------
     W = max(args.warmup, 3)
     c0 = native.launch_count()
@@ -196,10 +258,9 @@ def run_ours(args):
     stream = model._stream
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     ends = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-    sampler = ClockSampler(local)
     barrier(world)
     torch.cuda.synchronize()
-    sampler.start()
+    sampler.begin()
     with torch.cuda.stream(stream):
         step_graph = model.device_step_graph(st, gb) if model.use_cuda_graph else None
         for i in range(K):
@@ -213,8 +274,8 @@ def run_ours(args):
             ends[i].record(stream)
     model.optimizer.iterations += K if step_graph is not None else 0
     torch.cuda.synchronize()
+    sampler.end()
     barrier(world)
-    clocks = sampler.stop()
     dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
     dev_ms = max_over_ranks(dev_ms, world)
     del flush
@@ -222,6 +283,7 @@ def run_ours(args):
     # ---- end-to-end region (public API, H2D every step, D2H loss every step) -------------------------
     barrier(world)
     torch.cuda.synchronize()
+    sampler.begin()
     t0 = time.perf_counter()
     loss = 0.0
     losses_read = 0
@@ -235,11 +297,16 @@ def run_ours(args):
     assert losses_read == K
     torch.cuda.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t0, world)
+    sampler.end()
+    clocks = sampler.stop()
     barrier(world)
     h2d = xs[0].numel() * xs[0].element_size() + ys[0].numel() * ys[0].element_size()
 
+    ar_mode = "n/a"
     if world > 1:
         strategy.comm().check_health()
+        ch = getattr(model.arena, "_channel", None)
+        ar_mode = {0: "p2p one-shot", 1: "p2p two-shot", 2: "NVLS multimem"}.get(getattr(ch, "mode", -1), "?")
     ms_per_step = dev_ms / K
     value = gb * K / (dev_ms / 1e3)
     out = {
@@ -252,7 +319,8 @@ def run_ours(args):
                    "parallelism": f"dp{world}", "optimizer": args.optimizer, "cuda_graph": model.graph_captured,
                    "l2": "flushed between timed steps (256 MiB write outside the event pairs)"
                          if not args.no_flush else "not flushed",
-                   "allreduce": "fused p2p one/two-shot + optimizer (no NCCL on step path)" if world > 1 else "n/a"},
+                   "allreduce": (f"fused {ar_mode} all-reduce + optimizer kernel (no NCCL on step path)"
+                                 if world > 1 else "n/a")},
         "clocks": clocks,
         "e2e": {"value": gb * K / e2e_s, "unit": "images/sec", "ms_per_step": 1e3 * e2e_s / K,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "last_loss": loss,

@@ -61,6 +61,9 @@ struct ARParams {
   unsigned long long timeout_ns;
   long pp_lo, pp_hi;               // arena range a producer kernel may have pushed already (GEMM epilogue)
   const uint32_t* pp_done;         // == this epoch when it did; nullptr when the feature is off
+  // NVLS (mode 2): multicast mappings of the gradient arena, the parameter arena and a signal pad
+  // [2 phase][MAX_BLOCKS]; nv_flags is this rank's ordinary mapping of the same signal pad.
+  const float* mc_g; float* mc_w; uint32_t* mc_flags; const uint32_t* nv_flags;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -361,6 +364,115 @@ allreduce_fused_kernel(const ARParams p) {
   }
 }
 
+// ---- NVLS variant: the NVSwitch does the sum and the fan-out ------------------------------------------
+// Same ownership as two-shot (rank r owns slice r, optimizer state sharded by owner), but no receive
+// slots and no per-peer loops: the owner reads its slice through the MULTICAST mapping of the gradient
+// arena with multimem.ld_reduce (the switch fetches the W replicas and returns their sum), applies the
+// optimizer, and writes the new weights through the multicast mapping of the parameter arena with
+// multimem.st (the switch replicates the store into every GPU, own included). Per GPU and direction that
+// is ~S*(1+1/W) bytes on NVLink instead of 2*S*(W-1)/W, and two signal rounds (one multimem.red each).
+__device__ __forceinline__ float4 mc_ld_reduce4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st4(float* mc, const float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// Arrive on counter `b` of `phase` in EVERY rank's signal pad with one instruction, then wait until all W
+// ranks have arrived on ours. Counters only ever grow: after epoch e each holds e*W.
+__device__ __forceinline__ void nvls_barrier(const ARParams& p, int phase, int b, uint32_t e) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;"
+                 ::"l"(p.mc_flags + phase * MAX_BLOCKS + b), "r"(1u) : "memory");
+    const uint32_t* mine = p.nv_flags + phase * MAX_BLOCKS + b;
+    const uint32_t target = e * (uint32_t)p.world;
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned spins = 0;
+    while ((int)(ld_acquire_sys(mine) - target) < 0) {
+      if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > p.timeout_ns) {
+        if (atomicCAS(p.status, 0, 2) == 0) { p.status[1] = (int)e; p.status[2] = phase; p.status[3] = b; }
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(AR_THREADS)
+allreduce_nvls_kernel(const ARParams p) {
+  TFDE_PDL_PROLOGUE();
+  const int b = blockIdx.x, nb = gridDim.x, t = threadIdx.x;
+  __shared__ uint32_t s_e;
+  if (t == 0) s_e = p.epoch[b] + 1u;
+  __syncthreads();
+  const uint32_t e = s_e;
+  const int R = p.rank;
+
+  Hyper h;
+  if (p.opt >= 0) {
+    h.lr = p.hp->lr; h.mu = p.hp->momentum; h.b1 = p.hp->beta1; h.b2 = p.hp->beta2; h.eps = p.hp->eps;
+    h.gs = p.hp->grad_scale;
+    const float b1p = p.hp->beta1_pow * h.b1, b2p = p.hp->beta2_pow * h.b2;
+    h.lr_t = (p.opt == 3) ? h.lr * sqrtf(1.f - b2p) / (1.f - b1p) : h.lr;
+  } else {
+    h.lr = h.mu = h.b1 = h.b2 = h.eps = h.lr_t = 0.f; h.gs = 1.f;
+  }
+
+  const long slot = p.slot_floats;
+  long chunk = (slot + nb - 1) / nb; chunk = (chunk + 3) & ~3L;
+  const long lo = min((long)b * chunk, slot), hi = min(lo + chunk, slot);
+  const long own0 = (long)R * slot;
+  const long own_cnt4 = max(0L, (min(own0 + hi, p.n_total) - (own0 + lo)) >> 2);
+
+  // phase 0: block b of every rank has entered => every replica's gradients (written by kernels that
+  // precede this one in each rank's stream) are final and may be read through the switch.
+  nvls_barrier(p, 0, b, e);
+  for (long i0 = t; i0 < own_cnt4; i0 += (long)PUSH_U * blockDim.x) {
+    float4 s[PUSH_U];
+#pragma unroll
+    for (int u = 0; u < PUSH_U; ++u) {
+      const long i = i0 + (long)u * blockDim.x;
+      if (i < own_cnt4) s[u] = mc_ld_reduce4(p.mc_g + own0 + lo + (i << 2));
+    }
+#pragma unroll
+    for (int u = 0; u < PUSH_U; ++u) {
+      const long i = i0 + (long)u * blockDim.x;
+      if (i < own_cnt4) {
+        const long li = lo + (i << 2);
+        const float4 nw = update_group(p, h, own0 + li, li, s[u], false);
+        mc_st4(p.mc_w + own0 + li, nw);
+      }
+    }
+  }
+  // phase 1: every rank's block b has issued (and released) its multicast stores => sub-range [lo,hi) of
+  // every slice has landed here; the kernel as a whole ends only when all blocks have seen that, which
+  // also means no peer is still reading our gradients when the next step starts overwriting them.
+  nvls_barrier(p, 1, b, e);
+  if (p.metrics) {
+    for (int j = t; j < p.n_extra; j += blockDim.x) {
+      const long i = p.n + j;
+      const long li = i % slot;
+      if (li >= lo && li < hi) p.metrics[j] += __ldcg(p.w + i);
+    }
+  }
+  __syncthreads();
+  if (t == 0) {
+    p.epoch[b] = e;
+    if (atomicAdd(p.done_counter, 1u) == (unsigned)nb - 1u) {
+      if (p.opt >= 0) {
+        p.hp->beta1_pow *= p.hp->beta1;
+        p.hp->beta2_pow *= p.hp->beta2;
+        p.hp->step += 1u;
+      }
+      *p.done_counter = 0u;
+    }
+  }
+}
+
 // Pull copy used for the initial broadcast (G13): dst(local) <- src(peer-mapped), float4 granularity.
 __global__ void p2p_copy_kernel(float* __restrict__ dst, const float* __restrict__ src, long n) {
   const long n4 = n / 4;
@@ -401,6 +513,7 @@ TFDE_API int tfde_ipc_close_handle(void* p) { return (int)cudaIpcCloseMemHandle(
 TFDE_API int tfde_ipc_handle_bytes() { return (int)sizeof(cudaIpcMemHandle_t); }
 TFDE_API int tfde_ar_max_ranks() { return MAX_RANKS; }
 TFDE_API int tfde_ar_max_blocks() { return MAX_BLOCKS; }
+TFDE_API size_t tfde_ar_nvls_flag_bytes() { return (size_t)2 * MAX_BLOCKS * sizeof(uint32_t); }
 TFDE_API size_t tfde_ar_flag_bytes(int world) { return (size_t)2 * world * MAX_BLOCKS * sizeof(uint32_t); }
 
 // Descriptor filled by the Python side once (pointers are stable), then passed by value per launch.
@@ -412,6 +525,7 @@ struct TfdeARDesc {
   void* epoch; float* metrics; void* hp; void* done_counter; void* status;
   unsigned long long timeout_ns;
   long pp_lo, pp_hi; const void* pp_done;     // pre-pushed range (see ARParams)
+  const void* mc_g; void* mc_w; void* mc_flags; const void* nv_flags;   // mode 2 (NVLS) only
 };
 
 TFDE_API size_t tfde_ar_desc_bytes() { return sizeof(TfdeARDesc); }
@@ -434,6 +548,15 @@ TFDE_API int tfde_allreduce_fused(const TfdeARDesc* d, cudaStream_t stream) {
   p.timeout_ns = d->timeout_ns ? d->timeout_ns : 20000000000ULL;
   p.pp_lo = d->pp_lo; p.pp_hi = d->pp_hi; p.pp_done = (const uint32_t*)d->pp_done;
   if (d->wire_bf16 || (p.pp_lo & 3) || (p.pp_hi & 3)) p.pp_done = nullptr;   // pushes are fp32, 16-byte groups
+  if (d->mode == 2) {
+    // NVLS: fp32 on the wire, no bf16 shadow (it would need its own multicast mapping), W >= 2
+    if (!d->mc_g || !d->mc_w || !d->mc_flags || !d->nv_flags || d->wire_bf16 || d->w_bf16 || d->world < 2)
+      return TFDE_ERR_INVALID;
+    p.mc_g = (const float*)d->mc_g; p.mc_w = (float*)d->mc_w;
+    p.mc_flags = (uint32_t*)d->mc_flags; p.nv_flags = (const uint32_t*)d->nv_flags;
+    tfde_launch(allreduce_nvls_kernel, dim3(d->blocks), dim3(AR_THREADS), 0, stream, p);
+    TFDE_RETURN_LAUNCH_STATUS();
+  }
   tfde_launch(allreduce_fused_kernel, dim3(d->blocks), dim3(AR_THREADS), 0, stream, p);
   TFDE_RETURN_LAUNCH_STATUS();
 }

@@ -28,7 +28,8 @@ log = logging.getLogger("tfde_b200")
 
 MAX_RANKS = 8
 MAX_BLOCKS = 256
-ONE_SHOT, TWO_SHOT = 0, 1
+ONE_SHOT, TWO_SHOT, NVLS = 0, 1, 2
+_MODE_NAMES = {ONE_SHOT: "one_shot", TWO_SHOT: "two_shot", NVLS: "nvls"}
 
 
 def make_comm(strategy):
@@ -52,10 +53,14 @@ class Arena:
         self.device = torch.device(device)
         self.comm = comm
         if comm is not None and isinstance(comm, P2PComm) and comm.world > 1:
-            self.w = comm.symm_empty(self.n_total, "w")
+            # with NVLS both arenas are multicast-bound: gradients are read, parameters written, through
+            # the switch (allreduce_nvls_kernel); without it only w needs peer mappings (two-shot all-gather)
+            self.w = comm.symm_empty(self.n_total, "w", multicast=True)
+            self.g = (comm.symm_empty(self.n_total, "g", multicast=True) if comm.nvls
+                      else torch.zeros(self.n_total, dtype=torch.float32, device=self.device))
         else:
             self.w = torch.zeros(self.n_total, dtype=torch.float32, device=self.device)
-        self.g = torch.zeros(self.n_total, dtype=torch.float32, device=self.device)
+            self.g = torch.zeros(self.n_total, dtype=torch.float32, device=self.device)
         self.metrics = torch.zeros(self.n_extra, dtype=torch.float32, device=self.device)
         self.s1: Optional[torch.Tensor] = None
         self.s2: Optional[torch.Tensor] = None
@@ -133,6 +138,8 @@ class _ARDesc(ctypes.Structure):
         ("done_counter", ctypes.c_void_p), ("status", ctypes.c_void_p),
         ("timeout_ns", ctypes.c_ulonglong),
         ("pp_lo", ctypes.c_long), ("pp_hi", ctypes.c_long), ("pp_done", ctypes.c_void_p),
+        ("mc_g", ctypes.c_void_p), ("mc_w", ctypes.c_void_p), ("mc_flags", ctypes.c_void_p),
+        ("nv_flags", ctypes.c_void_p),
     ]
 
 
@@ -156,6 +163,7 @@ for _n, _a, _r in [
     ("tfde_ipc_handle_bytes", [], ctypes.c_int),
     ("tfde_ar_desc_bytes", [], ctypes.c_size_t),
     ("tfde_ar_flag_bytes", [ctypes.c_int], ctypes.c_size_t),
+    ("tfde_ar_nvls_flag_bytes", [], ctypes.c_size_t),
     ("tfde_allreduce_fused", [ctypes.POINTER(_ARDesc), ctypes.c_void_p], ctypes.c_int),
     ("tfde_p2p_copy", [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p], ctypes.c_int),
     ("tfde_dense_wgrad_push", [ctypes.c_void_p] * 5 + [ctypes.c_int] * 3 + [ctypes.c_void_p, ctypes.c_size_t,
@@ -216,6 +224,38 @@ class SymmBuffer:
             self.local_ptr = 0
 
 
+class McBuffer:
+    """Symmetric allocation that is ALSO bound to an NVSwitch multicast object (NVLS): ``mc_ptr`` is one
+    address that reaches all replicas -- ``multimem.ld_reduce`` through it returns the sum over ranks,
+    ``multimem.st`` writes every replica. The VMM allocation, the file-descriptor exchange and the multicast
+    bind are torch's symmetric-memory plumbing (set-up only); every per-step access is our kernels'."""
+
+    def __init__(self, comm: "P2PComm", nbytes: int, tag: str):
+        from torch._C._distributed_c10d import _SymmetricMemory
+        self.comm, self.nbytes, self.tag = comm, nbytes, tag
+        group = comm.strategy.group if comm.strategy.group is not None else dist.group.WORLD
+        self.bytes_tensor = _SymmetricMemory.empty_strided_p2p((nbytes,), (1,), torch.uint8, comm.device,
+                                                               group.group_name)
+        self.bytes_tensor.zero_()
+        torch.cuda.synchronize(comm.device)
+        self.handle = _SymmetricMemory.rendezvous(self.bytes_tensor, group.group_name)
+        off = int(getattr(self.handle, "offset", 0) or 0)
+        self.local_ptr = self.bytes_tensor.data_ptr()
+        self.peer_ptrs = [int(q) + off for q in self.handle.buffer_ptrs]
+        self.peer_ptrs[comm.rank] = self.local_ptr
+        mc = int(self.handle.multicast_ptr or 0)
+        self.mc_ptr = mc + off if mc else 0
+
+    def view(self, dtype, numel=None):
+        t = self.bytes_tensor.view(dtype)
+        return t if numel is None else t[:numel]
+
+    def free(self):
+        self.handle = None
+        self.bytes_tensor = None
+        self.local_ptr = 0
+
+
 class P2PComm(CommBase):
     """Symmetric heap + fused all-reduce. One instance per strategy; one "channel" (flags, epochs,
     receive slots) per arena so that independent collectives never share signal state."""
@@ -232,17 +272,40 @@ class P2PComm(CommBase):
         self.timeout_s = float(os.environ.get("TFDE_P2P_TIMEOUT_S", "20"))
         self.one_shot_max_bytes = int(os.environ.get("TFDE_ONE_SHOT_MAX_BYTES", str(4 << 20)))
         self.wire_bf16 = os.environ.get("TFDE_WIRE_BF16", "0") == "1"
+        self.nvls_min_bytes = int(os.environ.get("TFDE_NVLS_MIN_BYTES", "0"))
         self._scalar_channel = None
+        self.nvls = self._probe_nvls()
 
     # ---- symmetric memory --------------------------------------------------------------------
-    def symm_buffer(self, nbytes: int, tag: str) -> SymmBuffer:
+    def _probe_nvls(self) -> bool:
+        """NVLS needs multicast objects (NVSwitch + driver support). TFDE_NVLS=0 disables, =1 requires it,
+        default: use it when the probe allocation succeeds on EVERY rank."""
+        want = os.environ.get("TFDE_NVLS", "auto")
+        if self.world < 2 or want == "0":
+            return False
+        ok = 0
+        try:
+            probe = McBuffer(self, 4096, "nvls_probe")
+            ok = 1 if probe.mc_ptr else 0
+            self._buffers.append(probe)
+        except Exception as ex:  # noqa: BLE001
+            log.info("NVLS probe failed on rank %d: %s", self.rank, ex)
+        flags = [None] * self.world
+        dist.all_gather_object(flags, ok, group=self.strategy.group)
+        good = all(flags)
+        if want == "1" and not good:
+            raise RuntimeError(f"TFDE_NVLS=1 but multicast memory is unavailable (per-rank probe: {flags})")
+        log.info("NVLS multicast %s", "available" if good else f"unavailable (per-rank probe: {flags})")
+        return good
+
+    def symm_buffer(self, nbytes: int, tag: str, multicast: bool = False):
         nbytes = (nbytes + 255) // 256 * 256
-        b = SymmBuffer(self, nbytes, tag)
+        b = McBuffer(self, nbytes, tag) if (multicast and self.nvls) else SymmBuffer(self, nbytes, tag)
         self._buffers.append(b)
         return b
 
-    def symm_empty(self, numel: int, tag: str, dtype=torch.float32) -> torch.Tensor:
-        b = self.symm_buffer(numel * torch.empty((), dtype=dtype).element_size(), tag)
+    def symm_empty(self, numel: int, tag: str, dtype=torch.float32, multicast: bool = False) -> torch.Tensor:
+        b = self.symm_buffer(numel * torch.empty((), dtype=dtype).element_size(), tag, multicast)
         t = b.view(dtype, numel)
         self._named[t.data_ptr()] = b
         return t
@@ -343,15 +406,30 @@ class _Channel:
         self.n_total = n_total
         bytes_total = n_total * 4
         self.mode = ONE_SHOT if (W <= 2 or bytes_total * (W - 1) <= comm.one_shot_max_bytes) else TWO_SHOT
+        # NVLS needs both arenas multicast-bound (Arena does that when comm.nvls) and fp32 on the wire
+        g_mc = comm.buffer_of(arena.g) if arena is not None else None
+        w_mc = comm.buffer_of(arena.w) if arena is not None else None
+        nvls_ok = (comm.nvls and W >= 2 and not comm.wire_bf16 and getattr(g_mc, "mc_ptr", 0)
+                   and getattr(w_mc, "mc_ptr", 0))
+        if nvls_ok and bytes_total >= comm.nvls_min_bytes:
+            self.mode = NVLS
         forced = os.environ.get("TFDE_AR_MODE")
         if forced in ("one_shot", "two_shot"):
             self.mode = ONE_SHOT if forced == "one_shot" else TWO_SHOT
+        elif forced == "nvls":
+            if not nvls_ok:
+                raise RuntimeError("TFDE_AR_MODE=nvls but NVLS multicast memory is not available for this arena")
+            self.mode = NVLS
         if self.mode == ONE_SHOT:
             self.slot = n_total
         else:
             self.slot = ((n_total + W - 1) // W + 3) // 4 * 4
-        self.recv = comm.symm_buffer(2 * W * self.slot * 4, "recv")
-        self.flags = comm.symm_buffer(L.tfde_ar_flag_bytes(W), "flags")
+        if self.mode == NVLS:
+            self.recv = None
+            self.flags = comm.symm_buffer(L.tfde_ar_nvls_flag_bytes(), "nvls_flags", multicast=True)
+        else:
+            self.recv = comm.symm_buffer(2 * W * self.slot * 4, "recv")
+            self.flags = comm.symm_buffer(L.tfde_ar_flag_bytes(W), "flags")
         dev = comm.device
         self.epoch = torch.zeros(MAX_BLOCKS, dtype=torch.int32, device=dev)
         self.done = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -369,6 +447,8 @@ class _Channel:
             self.metrics = None
             self.n, self.n_extra = n_total, 0
         default_blocks = 16 if bytes_total <= (256 << 10) else (64 if bytes_total <= (4 << 20) else 144)
+        if self.mode == NVLS:      # the switch does the fan-in/fan-out: few blocks saturate it
+            default_blocks = 8 if bytes_total <= (4 << 20) else (32 if bytes_total <= (64 << 20) else 64)
         self.blocks = int(os.environ.get("TFDE_AR_BLOCKS", str(default_blocks)))
         self.blocks = max(1, min(self.blocks, MAX_BLOCKS))
         self.desc = _ARDesc()
@@ -379,9 +459,12 @@ class _Channel:
         d.n, d.n_total, d.slot_floats = self.n, n_total, self.slot
         d.g, d.w = self.g.data_ptr(), self.w.data_ptr()
         for r in range(W):
-            d.recv[r] = self.recv.peer_ptrs[r]
+            d.recv[r] = self.recv.peer_ptrs[r] if self.recv is not None else None
             d.flags[r] = self.flags.peer_ptrs[r]
             d.wpeer[r] = self.wbuf.peer_ptrs[r] if self.wbuf is not None else self.w.data_ptr()
+        if self.mode == NVLS:
+            d.mc_g, d.mc_w = g_mc.mc_ptr, w_mc.mc_ptr
+            d.mc_flags, d.nv_flags = self.flags.mc_ptr, self.flags.local_ptr
         d.epoch, d.done_counter, d.status = self.epoch.data_ptr(), self.done.data_ptr(), self.status.data_ptr()
         d.metrics = self.metrics.data_ptr() if self.metrics is not None else None
         d.timeout_ns = int(comm.timeout_s * 1e9)
@@ -390,14 +473,15 @@ class _Channel:
             torch.cuda.synchronize(dev)
             dist.barrier(group=comm.strategy.group)
         log.info("p2p channel: n_total=%d mode=%s slot=%d blocks=%d wire_bf16=%s", n_total,
-                 "one_shot" if self.mode == ONE_SHOT else "two_shot", self.slot, self.blocks, comm.wire_bf16)
+                 _MODE_NAMES[self.mode], self.slot, self.blocks, comm.wire_bf16)
 
     def enable_fused_push(self, grad_view: torch.Tensor, arena_offset: int):
         """Registers one gradient tensor (the largest dense kernel) whose wgrad GEMM pushes its tiles into
         the peers' receive slots itself; the all-reduce kernel then skips that range when the GEMM says it
         ran this step (pp_done == epoch)."""
-        if self.comm.world < 2 or self.comm.wire_bf16 or os.environ.get("TFDE_FUSED_PUSH", "1") != "1":
-            return False
+        if (self.comm.world < 2 or self.comm.wire_bf16 or self.mode == NVLS
+                or os.environ.get("TFDE_FUSED_PUSH", "1") != "1"):
+            return False      # NVLS has no receive slots to push into: the switch reads the gradients in place
         n = grad_view.numel()
         if n % 4 or arena_offset % 4 or ctypes.sizeof(_PushDesc) != native.load().tfde_push_desc_bytes():
             return False
@@ -417,13 +501,13 @@ class _Channel:
     def configure_optimizer(self, optimizer, arena: Arena):
         """Allocates optimizer slots with the layout this channel's mode needs (two-shot: only the owned
         slice -- optimizer state is sharded by owner rank)."""
-        n_state = self.slot if self.mode == TWO_SHOT else arena.n_total
+        n_state = self.slot if self.mode in (TWO_SHOT, NVLS) else arena.n_total
         need = optimizer.num_slots
         if need >= 1 and (arena.s1 is None or arena.s1.numel() != n_state):
             arena.s1 = torch.zeros(n_state, dtype=torch.float32, device=arena.device)
         if need >= 2 and (arena.s2 is None or arena.s2.numel() != n_state):
             arena.s2 = torch.zeros(n_state, dtype=torch.float32, device=arena.device)
-        arena.state_sharded = self.mode == TWO_SHOT and self.comm.world > 1
+        arena.state_sharded = self.mode in (TWO_SHOT, NVLS) and self.comm.world > 1
         arena.state_slice = (self.comm.rank * self.slot, self.slot)
 
     def launch(self, opt, hp, s1, s2):

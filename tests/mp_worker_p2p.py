@@ -126,7 +126,8 @@ def check_model(strategy, graph):
     if not close:
         print(f"[rank {rank}] FAIL model weights differ from cpu reference", flush=True)
     from tfde_b200.ops import push as _push
-    if os.environ.get("TFDE_FUSED_PUSH", "1") == "1" and _push.stats["pushed_launches"] == 0:
+    nvls_mode = getattr(m.arena._channel, "mode", -1) == 2      # no receive slots to push into under NVLS
+    if os.environ.get("TFDE_FUSED_PUSH", "1") == "1" and not nvls_mode and _push.stats["pushed_launches"] == 0:
         print(f"[rank {rank}] FAIL fused wgrad->push was never used", flush=True)
         ok = False
     if graph and not m.graph_captured:
@@ -172,7 +173,7 @@ def sweep(strategy, out_path):
     comm = strategy.comm()
     rank, world = strategy.rank, strategy.world_size
     rows = []
-    for mode in ("one_shot", "two_shot"):
+    for mode in ("one_shot", "two_shot") + (("nvls",) if comm.nvls else ()):
         for nbytes in (1 << 10, 1 << 14, 1 << 18, 1388584, 1 << 22, 1 << 24, 1 << 26, 1 << 28):
             if mode == "one_shot" and nbytes * world > (1 << 28):
                 continue
@@ -242,6 +243,8 @@ def main():
     rank, world = strategy.rank, strategy.world_size
     assert world >= 2, "launch with torchrun --nproc-per-node >= 2"
     ok = True
+    if rank == 0:
+        print("NVLS multicast:", "available" if strategy.comm().nvls else "unavailable", flush=True)
     # small scalar all-reduce (G14)
     t = torch.arange(7, dtype=torch.float32, device=strategy.device) + rank
     strategy.all_reduce_sum_(t)
@@ -251,7 +254,7 @@ def main():
         ok = False
     for n in (1000, 347146, 3_000_001):
         for opt_name in ("sgd", "momentum", "adam"):
-            for mode in ("one_shot", "two_shot"):
+            for mode in ("one_shot", "two_shot") + (("nvls",) if strategy.comm().nvls else ()):
                 ok &= check_fused(strategy, n, opt_name, mode)
     ok &= check_fused(strategy, 347146, "sgd", "one_shot", wire_bf16=True)
     ok &= check_fused(strategy, 347146, "adam", "two_shot", wire_bf16=True)
