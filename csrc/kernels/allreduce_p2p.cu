@@ -386,8 +386,14 @@ __device__ __forceinline__ void mc_st4(float* mc, const float4 v) {
 __device__ __forceinline__ void nvls_barrier(const ARParams& p, int phase, int b, uint32_t e) {
   __syncthreads();
   if (threadIdx.x == 0) {
-    asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;"
-                 ::"l"(p.mc_flags + phase * MAX_BLOCKS + b), "r"(1u) : "memory");
+    // phase 0 publishes nothing this kernel wrote (the gradients come from earlier kernels of the stream,
+    // already visible at the kernel boundary), so it skips the release fence (a MEMBAR.SYS round trip).
+    if (phase == 0)
+      asm volatile("multimem.red.relaxed.sys.global.add.u32 [%0], %1;"
+                   ::"l"(p.mc_flags + phase * MAX_BLOCKS + b), "r"(1u) : "memory");
+    else
+      asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;"
+                   ::"l"(p.mc_flags + phase * MAX_BLOCKS + b), "r"(1u) : "memory");
     const uint32_t* mine = p.nv_flags + phase * MAX_BLOCKS + b;
     const uint32_t target = e * (uint32_t)p.world;
     const unsigned long long t0 = globaltimer_ns();

@@ -173,7 +173,10 @@ def sweep(strategy, out_path):
     comm = strategy.comm()
     rank, world = strategy.rank, strategy.world_size
     rows = []
-    for mode in ("one_shot", "two_shot") + (("nvls",) if comm.nvls else ()):
+    modes = ("one_shot", "two_shot") + (("nvls",) if comm.nvls else ())
+    if os.environ.get("TFDE_SWEEP_MODES"):
+        modes = tuple(os.environ["TFDE_SWEEP_MODES"].split(","))
+    for mode in modes:
         for nbytes in (1 << 10, 1 << 14, 1 << 18, 1388584, 1 << 22, 1 << 24, 1 << 26, 1 << 28):
             if mode == "one_shot" and nbytes * world > (1 << 28):
                 continue
@@ -243,6 +246,11 @@ def main():
     rank, world = strategy.rank, strategy.world_size
     assert world >= 2, "launch with torchrun --nproc-per-node >= 2"
     ok = True
+    if "--sweep-only" in sys.argv:
+        sweep(strategy, os.path.join(ROOT, "gpurun_out", os.environ.get("TFDE_SWEEP_OUT", f"allreduce_sweep_n{world}.json")))
+        strategy.shutdown()
+        dist.destroy_process_group()
+        return
     if rank == 0:
         print("NVLS multicast:", "available" if strategy.comm().nvls else "unavailable", flush=True)
     # small scalar all-reduce (G14)
