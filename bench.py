@@ -56,6 +56,9 @@ def parse_args():
                     help="bf16 = mixed_bfloat16 policy: large Dense layers on the tcgen05 GEMM (BASELINE.json config 3)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--l2", default="inputs", choices=["inputs", "flush"],
+                    help="timing protocol for `value`: distinct inputs from a pool larger than L2 (default) or "
+                         "an L2 flush before every step")
     return ap.parse_args()
 
 
@@ -250,35 +253,86 @@ def run_ours(args):
     model.sync()
 
     # ---- device-timed region -----------------------------------------------------------------------
+    # Two protocols (both allowed by the timing rules; `config.l2` says which one `value` comes from):
+    #  inputs: K back-to-back steps, one event pair around them; every step consumes a DISTINCT device-side
+    #          input batch out of a pool larger than L2 (>= 136 MiB, evicted once by a 256 MiB write before
+    #          timing), so inputs always come from HBM while weights/activations are as resident as they are
+    #          in real training. This is the default: it is what a training loop sees.
+    #  flush:  a 256 MiB write between steps (outside per-step event pairs): everything cold every step.
     K = args.steps
-    flush = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     key = [k for k, v in model._graphs.items() if hasattr(v, "in_x")][0]
     st = model._graphs[key]
     st.in_x.copy_(xs[0]); st.in_y.copy_(ys[0])
     stream = model._stream
-    starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-    ends = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     barrier(world)
     torch.cuda.synchronize()
-    sampler.begin()
     with torch.cuda.stream(stream):
         step_graph = model.device_step_graph(st, gb) if model.use_cuda_graph else None
-        for i in range(K):
-            if flush is not None:
+
+    def run_step():
+        if step_graph is not None:
+            step_graph.replay()
+        else:
+            model._step_body(st.in_x, st.in_y, gb)
+
+    def timed_flush():
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+        starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+        ends = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+        barrier(world)
+        torch.cuda.synchronize()
+        sampler.begin()
+        with torch.cuda.stream(stream):
+            for i in range(K):
                 flush.fill_(i & 0xFF)
-            starts[i].record(stream)
-            if step_graph is not None:
-                step_graph.replay()
-            else:
-                model._step_body(st.in_x, st.in_y, gb)
-            ends[i].record(stream)
-    model.optimizer.iterations += K if step_graph is not None else 0
-    torch.cuda.synchronize()
-    sampler.end()
-    barrier(world)
-    dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
-    dev_ms = max_over_ranks(dev_ms, world)
-    del flush
+                starts[i].record(stream)
+                run_step()
+                ends[i].record(stream)
+        torch.cuda.synchronize()
+        sampler.end()
+        barrier(world)
+        return max_over_ranks(sum(s.elapsed_time(e) for s, e in zip(starts, ends)), world)
+
+    def timed_inputs(evict=True):
+        per = st.in_x.numel() * st.in_x.element_size() + st.in_y.numel() * 8
+        P = max(K, -(-(136 << 20) // per)) if evict else 8
+        gen = torch.Generator(device=dev).manual_seed(4321 + rank)
+        if st.in_x.dtype == torch.uint8:
+            pool_x = torch.randint(0, 256, (P,) + tuple(st.in_x.shape), generator=gen, dtype=torch.uint8, device=dev)
+        else:
+            pool_x = torch.rand((P,) + tuple(st.in_x.shape), generator=gen, dtype=st.in_x.dtype, device=dev)
+        pool_y = torch.randint(0, 10, (P,) + tuple(st.in_y.shape), generator=gen, dtype=torch.int64, device=dev)
+        if evict:
+            torch.empty(256 << 20, dtype=torch.uint8, device=dev).fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier(world)
+        torch.cuda.synchronize()
+        sampler.begin()
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            for i in range(K):
+                st.in_x.copy_(pool_x[i % P]); st.in_y.copy_(pool_y[i % P])
+                run_step()
+            e1.record(stream)
+        torch.cuda.synchronize()
+        sampler.end()
+        barrier(world)
+        return max_over_ranks(e0.elapsed_time(e1), world), P * per
+
+    cold_ms = None
+    if args.no_flush:
+        dev_ms, pool_bytes = timed_inputs(evict=False)
+        l2_note = "not flushed, 8 input batches reused (--no-flush; not a valid headline number)"
+    elif args.l2 == "flush":
+        dev_ms = timed_flush()
+        l2_note = "flushed between timed steps (256 MiB write outside the per-step event pairs)"
+    else:
+        dev_ms, pool_bytes = timed_inputs()
+        l2_note = (f"inputs larger than L2: each timed step reads a distinct device-resident batch from a "
+                   f"{pool_bytes >> 20} MiB pool (evicted by a 256 MiB write before timing); K steps back to back, "
+                   f"one event pair; weights/activations stay resident as in training")
+        cold_ms = timed_flush()
+    model.optimizer.iterations += (K if step_graph is not None else 0) * (2 if cold_ms is not None else 1)
 
     # ---- end-to-end region (public API, H2D every step, D2H loss every step) -------------------------
     barrier(world)
@@ -317,11 +371,13 @@ def run_ours(args):
         "config": {"model": "keras_mnist_cnn_conv32_pool_dense64_dense10" if args.model == "a" else "model_b_bn_cnn",
                    "global_batch": gb, "per_gpu_batch": B, "seq_len": None, "input": list(in_shape),
                    "parallelism": f"dp{world}", "optimizer": args.optimizer, "cuda_graph": model.graph_captured,
-                   "l2": "flushed between timed steps (256 MiB write outside the event pairs)"
-                         if not args.no_flush else "not flushed",
+                   "l2": l2_note,
                    "allreduce": (f"fused {ar_mode} all-reduce + optimizer kernel (no NCCL on step path)"
                                  if world > 1 else "n/a")},
         "clocks": clocks,
+        "cold_l2": ({"value": gb * K / (cold_ms / 1e3), "ms_per_step": cold_ms / K,
+                     "note": "same K steps with a 256 MiB L2 flush before every step (per-step event pairs)"}
+                    if cold_ms is not None else None),
         "e2e": {"value": gb * K / e2e_s, "unit": "images/sec", "ms_per_step": 1e3 * e2e_s / K,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "last_loss": loss,
                 "note": "model.train_on_batch + last_step_loss(lag=1): pinned uint8 images + int64 labels H2D and loss D2H every step; each step's loss is read on the host one step late (K reads for K steps) so the read overlaps the next step"},

@@ -272,7 +272,8 @@ class P2PComm(CommBase):
         self.timeout_s = float(os.environ.get("TFDE_P2P_TIMEOUT_S", "20"))
         self.one_shot_max_bytes = int(os.environ.get("TFDE_ONE_SHOT_MAX_BYTES", str(4 << 20)))
         self.wire_bf16 = os.environ.get("TFDE_WIRE_BF16", "0") == "1"
-        self.nvls_min_bytes = int(os.environ.get("TFDE_NVLS_MIN_BYTES", "0"))
+        self.nvls_min_bytes = int(os.environ.get("TFDE_NVLS_MIN_BYTES", str(64 << 10)))
+        self.nvls_min_world = int(os.environ.get("TFDE_NVLS_MIN_WORLD", "4"))
         self._scalar_channel = None
         self.nvls = self._probe_nvls()
 
@@ -411,7 +412,10 @@ class _Channel:
         w_mc = comm.buffer_of(arena.w) if arena is not None else None
         nvls_ok = (comm.nvls and W >= 2 and not comm.wire_bf16 and getattr(g_mc, "mc_ptr", 0)
                    and getattr(w_mc, "mc_ptr", 0))
-        if nvls_ok and bytes_total >= comm.nvls_min_bytes:
+        # measured (profiles/allreduce_sweep_n{2,8}): at 8 GPUs the switch-reduced variant wins from 256 KB up
+        # (15 vs 23 us at Model A's 1.39 MB, 727 vs 559 GB/s bus at 256 MB); at 2 GPUs it moves 1.5x the
+        # bytes of two-shot and loses everywhere
+        if nvls_ok and W >= comm.nvls_min_world and bytes_total >= comm.nvls_min_bytes:
             self.mode = NVLS
         forced = os.environ.get("TFDE_AR_MODE")
         if forced in ("one_shot", "two_shot"):
@@ -448,7 +452,7 @@ class _Channel:
             self.n, self.n_extra = n_total, 0
         default_blocks = 16 if bytes_total <= (256 << 10) else (64 if bytes_total <= (4 << 20) else 144)
         if self.mode == NVLS:      # the switch does the fan-in/fan-out: few blocks saturate it
-            default_blocks = 8 if bytes_total <= (4 << 20) else (32 if bytes_total <= (64 << 20) else 64)
+            default_blocks = 8 if bytes_total <= (4 << 20) else 32      # 32 > 64/128 at every size measured
         self.blocks = int(os.environ.get("TFDE_AR_BLOCKS", str(default_blocks)))
         self.blocks = max(1, min(self.blocks, MAX_BLOCKS))
         self.desc = _ARDesc()
