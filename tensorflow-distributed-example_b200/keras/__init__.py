@@ -26,9 +26,16 @@ class mixed_precision:
     (fp32 master weights, fp32 accumulation); 'float32' (default) is the reference's precision."""
 
     @staticmethod
-    def set_global_policy(name):
+    def set_global_policy(name, activations=None):
+        """``activations='bfloat16'`` (extension): bf16 layer outputs as in Keras' own mixed precision
+        (convolutional networks); default keeps fp32 activations and bf16 GEMM operands only."""
         from ..ops import mixed
-        mixed.set_global_policy(name)
+        mixed.set_global_policy(name, activations)
+
+    @staticmethod
+    def activation_dtype():
+        from ..ops import mixed
+        return mixed.activation_dtype()
 
     @staticmethod
     def global_policy():

@@ -150,6 +150,29 @@ class Layer:
         self._bufs.clear()
 
     # -- execution ---------------------------------------------------------------------------
+    # Activations may be bf16 (policy mixed_bfloat16 with activations='bfloat16', ops/act16.py). ``run`` /
+    # ``run_back`` are what executors call: they adapt the dtype at the boundary of a layer that has no
+    # bf16 kernel path (a plain copy-cast; the ResNet trunk never takes it), then dispatch.
+    def takes_bf16(self, x) -> bool:
+        return False
+
+    def run(self, x, training: bool):
+        self._in_cast = x.dtype == torch.bfloat16 and not self.takes_bf16(x)
+        if self._in_cast:
+            x = self.buf("in_f32", x.shape).copy_(x)
+        y = self.forward(x, training)
+        self._out_dtype = y.dtype
+        return y
+
+    def run_back(self, dy):
+        want = getattr(self, "_out_dtype", dy.dtype)
+        if dy.dtype != want:
+            dy = self.buf("dy_cast", dy.shape, want).copy_(dy)
+        dx = self.backward(dy)
+        if dx is not None and getattr(self, "_in_cast", False):
+            dx = self.buf("dx_b16", dx.shape, torch.bfloat16).copy_(dx)
+        return dx
+
     def forward(self, x, training: bool):
         raise NotImplementedError
 
@@ -205,11 +228,31 @@ class Conv2D(Layer):
         self.bias = self.add_weight("bias", (self.filters,), zeros_init) if self.use_bias else None
         return out
 
+    def _act16_ok(self, x) -> bool:
+        """bf16-activation path (ops/act16.py): policy mixed_bfloat16 + activations='bfloat16', no fused
+        activation, tensor-core-friendly shapes. The fp32 network input is accepted too (stem conv)."""
+        from ..ops import mixed, act16
+        return (x.is_cuda is not None and mixed.global_policy() == "mixed_bfloat16"
+                and mixed.activation_dtype() == "bfloat16" and self.activation is None
+                and act16.conv_supported(x.shape, self.kernel.shape, self.out_shape[0], self.out_shape[1],
+                                         x.dtype == torch.bfloat16))
+
+    def takes_bf16(self, x) -> bool:
+        return self._act16_ok(x)
+
     def forward(self, x, training):
         b = x.shape[0]
         self._x = x
-        y = self.buf("y", (b,) + self.out_shape)
         from ..ops import mixed, mixed_conv
+        self._a16 = self._act16_ok(x)
+        if self._a16:
+            from ..ops import act16
+            y = self.buf("y16", (b,) + self.out_shape, torch.bfloat16)
+            act16.conv2d_fwd(x, self.kernel.value, self.bias.value if self.bias else None, self.strides,
+                             self.pads, out=y)
+            self._y = y
+            return y
+        y = self.buf("y", (b,) + self.out_shape)
         self._mixed = (mixed.global_policy() == "mixed_bfloat16"
                        and mixed_conv.supported(x.shape, self.kernel.shape, self.out_shape[0], self.out_shape[1]))
         if self._mixed:   # tensor-core path: gathered bf16 operands, fp32 accumulation in TMEM
@@ -222,6 +265,15 @@ class Conv2D(Layer):
         return y
 
     def backward(self, dy):
+        if getattr(self, "_a16", False):
+            from ..ops import act16
+            dx = self.buf("dx16", self._x.shape, torch.bfloat16) if self.need_dx else None
+            act16.conv2d_bwd(self._x, self.kernel.value, dy, self.strides, self.pads, self.need_dx, self.use_bias,
+                             getattr(self, "bias_grad_zero", False), out_dx=dx, out_dw=self.kernel.grad,
+                             out_db=self.bias.grad if self.bias else None)
+            if dx is not None and self._x.dtype != torch.bfloat16:
+                dx = self.buf("dx", self._x.shape).copy_(dx)
+            return dx
         dx = self.buf("dx", self._x.shape) if self.need_dx else None
         if getattr(self, "_mixed", False):
             from ..ops import mixed_conv
@@ -250,16 +302,29 @@ class MaxPooling2D(Layer):
         ho, wo, self.pads = ops.conv_geometry(h, w, *self.pool_size, self.strides, self.padding)
         return (ho, wo, c)
 
+    def takes_bf16(self, x) -> bool:
+        return x.shape[-1] % 8 == 0
+
     def forward(self, x, training):
         b = x.shape[0]
         self._x_shape = tuple(x.shape)
-        y = self.buf("y", (b,) + self.out_shape)
+        self._b16 = x.dtype == torch.bfloat16
         idx = self.buf("idx", (b,) + self.out_shape, torch.uint8)
-        ops.maxpool_fwd(x, self.pool_size, self.strides, self.pads, out=y, out_idx=idx)
+        if self._b16:
+            from ..ops import act16
+            y = self.buf("y16", (b,) + self.out_shape, torch.bfloat16)
+            act16.maxpool_fwd(x, self.pool_size, self.strides, self.pads, out=y, out_idx=idx)
+        else:
+            y = self.buf("y", (b,) + self.out_shape)
+            ops.maxpool_fwd(x, self.pool_size, self.strides, self.pads, out=y, out_idx=idx)
         self._idx = idx
         return y
 
     def backward(self, dy):
+        if self._b16:
+            from ..ops import act16
+            dx = self.buf("dx16", self._x_shape, torch.bfloat16)
+            return act16.maxpool_bwd(dy, self._idx, self._x_shape, self.pool_size, self.strides, self.pads, out=dx)
         dx = self.buf("dx", self._x_shape)
         return ops.maxpool_bwd(dy, self._idx, self._x_shape, self.pool_size, self.strides, self.pads, out=dx)
 
@@ -267,6 +332,9 @@ class MaxPooling2D(Layer):
 class Flatten(Layer):
     """reference: distributed_with_keras.py:36 -- row-major (h, w, c) order, a free view in NHWC."""
     _type_name = "flatten"
+
+    def takes_bf16(self, x) -> bool:
+        return True
 
     def compute_output_shape(self, in_shape):
         n = 1
@@ -290,6 +358,9 @@ class Reshape(Layer):
     def __init__(self, target_shape, **kw):
         super().__init__(**kw)
         self.target_shape = tuple(int(s) for s in target_shape)
+
+    def takes_bf16(self, x) -> bool:
+        return True
 
     def compute_output_shape(self, in_shape):
         n = 1
@@ -397,12 +468,27 @@ class BatchNormalization(Layer):
         self.unbiased_moving = len(in_shape) == 3
         return out
 
+    def takes_bf16(self, x) -> bool:
+        from ..ops import act16
+        return act16.channels_supported(x.shape[-1])
+
     def forward(self, x, training):
         c = x.shape[-1]
         self._x = x
-        y = self.buf("y", x.shape)
         sm = self.buf("save_mean", (c,))
         si = self.buf("save_invstd", (c,))
+        self._b16 = x.dtype == torch.bfloat16
+        if self._b16:      # bf16 activations: fp32 statistics, folded scale/shift kept for the backward mask
+            from ..ops import act16
+            y = self.buf("y16", x.shape, torch.bfloat16)
+            sc, sh = self.buf("scale", (c,)), self.buf("shift", (c,))
+            act16.bn_fwd(x, self.gamma.value if self.gamma else None, self.beta.value if self.beta else None,
+                         self.moving_mean.value, self.moving_variance.value, self.momentum, self.epsilon,
+                         training, self.fused_relu, self.unbiased_moving, out=y, save_mean=sm, save_invstd=si,
+                         scale=sc, shift=sh)
+            self._y, self._sm, self._si, self._sc, self._sh = y, sm, si, sc, sh
+            return y
+        y = self.buf("y", x.shape)
         ops.bn_fwd(x, self.gamma.value if self.gamma else None, self.beta.value if self.beta else None,
                    self.moving_mean.value, self.moving_variance.value, self.momentum, self.epsilon,
                    training, self.fused_relu, self.unbiased_moving, out=y, save_mean=sm, save_invstd=si)
@@ -411,9 +497,15 @@ class BatchNormalization(Layer):
 
     def backward(self, dy):
         c = dy.shape[-1]
-        dx = self.buf("dx", self._x.shape)
         dbeta = self.beta.grad if self.beta else self.buf("dbeta", (c,))
         dgamma = self.gamma.grad if self.gamma else self.buf("dgamma", (c,))
+        if getattr(self, "_b16", False):
+            from ..ops import act16
+            dx = self.buf("dx16", self._x.shape, torch.bfloat16)
+            act16.bn_bwd(self._x, dy, self.gamma.value if self.gamma else None, self._sm, self._si, self._sc,
+                         self._sh, self.fused_relu, out_dx=dx, out_dgamma=dgamma, out_dbeta=dbeta)
+            return dx
+        dx = self.buf("dx", self._x.shape)
         ops.bn_bwd(self._x, self._y, dy, self.gamma.value if self.gamma else None, self._sm, self._si,
                    self.fused_relu, out_dx=dx, out_dgamma=dgamma, out_dbeta=dbeta)
         return dx
@@ -429,6 +521,9 @@ class Activation(Layer):
             raise ValueError(f"Activation {activation!r} not supported")
         self.activation = activation
         self.fused_away = False
+
+    def takes_bf16(self, x) -> bool:
+        return self.fused_away or self.activation == "linear"
 
     def forward(self, x, training):
         if self.fused_away or self.activation == "linear":
@@ -486,11 +581,22 @@ class GlobalAveragePooling2D(Layer):
     def compute_output_shape(self, in_shape):
         return (in_shape[2],)
 
+    def takes_bf16(self, x) -> bool:
+        return x.shape[-1] % 8 == 0
+
     def forward(self, x, training):
         self._x_shape = tuple(x.shape)
-        return ops.global_avgpool_fwd(x, out=self.buf("y", (x.shape[0], x.shape[3])))
+        self._b16 = x.dtype == torch.bfloat16
+        y = self.buf("y", (x.shape[0], x.shape[3]))
+        if self._b16:      # bf16 feature map in, fp32 features out: the classifier head stays fp32
+            from ..ops import act16
+            return act16.global_avgpool_fwd(x, out=y)
+        return ops.global_avgpool_fwd(x, out=y)
 
     def backward(self, dy):
+        if self._b16:
+            from ..ops import act16
+            return act16.global_avgpool_bwd(dy, self._x_shape, out=self.buf("dx16", self._x_shape, torch.bfloat16))
         return ops.global_avgpool_bwd(dy, self._x_shape, out=self.buf("dx", self._x_shape))
 
 

@@ -219,6 +219,10 @@ class Sequential:
                     and nxt.activation == "relu"):
                 cur.fused_relu = True
                 nxt.fused_away = True
+            if isinstance(cur, L.Conv2D) and cur.activation is None and isinstance(nxt, L.BatchNormalization):
+                # d(loss)/d(bias) of a convolution feeding a training-mode batch-norm is identically zero
+                # (batch-norm removes any per-channel shift); the bf16-activation path skips that reduction
+                cur.bias_grad_zero = True
             plan.append(cur)
             i += 1
         self.exec_plan = plan
@@ -290,14 +294,14 @@ class Sequential:
     def _forward(self, x, training: bool):
         x = self._prep_input(x)
         for node in self.exec_plan:
-            x = node.forward(x, training)
+            x = node.run(x, training)
         return x
 
     def _backward(self, dy):
         for node in reversed(self.exec_plan):
             if dy is None:
                 break
-            dy = node.backward(dy)
+            dy = node.run_back(dy)
 
     def __call__(self, x, training=False):
         from ..estimator.symbolic import SymbolicOutput, SymbolicTensor
@@ -332,7 +336,7 @@ class Sequential:
             # classifier head in one launch: Dense + loss/accuracy + d(logits) + dW/db + dh
             h = self._prep_input(x)
             for node in self.exec_plan[:-1]:
-                h = node.forward(h, True)
+                h = node.run(h, True)
             dh = head.buf("dx", h.shape) if head.need_dx else None
             ops.head_fwd_bwd(h, head.kernel.value, head.bias.value if head.bias else None, y,
                              1.0 / float(global_batch), self.loss.from_probs, False, head.need_dx,
@@ -342,7 +346,7 @@ class Sequential:
             for node in reversed(self.exec_plan[:-1]):
                 if dy is None:
                     break
-                dy = node.backward(dy)
+                dy = node.run_back(dy)
         else:
             out = self._forward(x, True)
             dgrad = self._in_buf("dloss", out.shape)

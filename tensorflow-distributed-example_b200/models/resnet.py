@@ -43,12 +43,14 @@ class Bottleneck(L.Layer):
         self.c3 = self._mk(L.Conv2D(f * e, 1), "3_conv")
         self.b3 = self._mk(L.BatchNormalization(epsilon=1.001e-5), "3_bn")
         self.b1.fused_relu = self.b2.fused_relu = True
+        self.c1.bias_grad_zero = self.c2.bias_grad_zero = self.c3.bias_grad_zero = True   # each feeds a batch-norm
         shape = tuple(in_shape)
         for l in (self.c1, self.b1, self.c2, self.b2, self.c3, self.b3):
             shape = l.build(shape)
         if self.projection:
             self.c0 = self._mk(L.Conv2D(f * e, 1, strides=self.stride), "0_conv")
             self.b0 = self._mk(L.BatchNormalization(epsilon=1.001e-5), "0_bn")
+            self.c0.bias_grad_zero = True
             s0 = self.b0.build(self.c0.build(tuple(in_shape)))
             if s0 != shape:
                 raise ValueError(f"{self.name}: shortcut {s0} != main {shape}")
@@ -58,24 +60,44 @@ class Bottleneck(L.Layer):
         self.in_shape, self.out_shape, self.built = tuple(in_shape), shape, True
         return shape
 
+    def takes_bf16(self, x) -> bool:
+        return x.shape[-1] % 8 == 0
+
     def forward(self, x, training):
         for l in self.subs:
             l.model = self.model
         h = x
         for l in (self.c1, self.b1, self.c2, self.b2, self.c3, self.b3):
-            h = l.forward(h, training)
-        sc = self.b0.forward(self.c0.forward(x, training), training) if self.projection else x
-        y = self.buf("y", h.shape)
-        ops.add(h, sc, relu=True, out=y)
+            h = l.run(h, training)
+        sc = self.b0.run(self.c0.run(x, training), training) if self.projection else x
+        self._b16 = h.dtype == torch.bfloat16 and sc.dtype == torch.bfloat16
+        if self._b16:       # bf16 activations end to end (ops/act16.py)
+            from ..ops import act16
+            y = self.buf("y16", h.shape, torch.bfloat16)
+            act16.add(h, sc, relu=True, out=y)
+        else:
+            if h.dtype != sc.dtype:
+                h, sc = h.float(), sc.float()
+            y = self.buf("y", h.shape)
+            ops.add(h, sc, relu=True, out=y)
         self._y = y
         return y
 
     def backward(self, dy):
-        d = ops.relu_bwd(self._y, dy, out=self.buf("d", dy.shape))
+        if self._b16:
+            from ..ops import act16
+            d = act16.relu_bwd(self._y, dy, out=self.buf("d16", dy.shape, torch.bfloat16))
+        else:
+            d = ops.relu_bwd(self._y, dy, out=self.buf("d", dy.shape))
         g = d
         for l in (self.b3, self.c3, self.b2, self.c2, self.b1, self.c1):
-            g = l.backward(g)
-        gs = self.c0.backward(self.b0.backward(d)) if self.projection else d
+            g = l.run_back(g)
+        gs = self.c0.run_back(self.b0.run_back(d)) if self.projection else d
+        if self._b16 and g.dtype == torch.bfloat16 and gs.dtype == torch.bfloat16:
+            from ..ops import act16
+            return act16.add(g, gs, relu=False, out=self.buf("dx16", g.shape, torch.bfloat16))
+        if g.dtype != gs.dtype:
+            g, gs = g.float(), gs.float()
         return ops.add(g, gs, relu=False, out=self.buf("dx", g.shape))
 
     def free_buffers(self):

@@ -1,0 +1,381 @@
+"""bf16 activations for convolutional networks (``mixed_bfloat16`` with ``activations='bfloat16'``).
+
+Keras' ``mixed_bfloat16`` policy keeps variables in fp32 and runs every layer's compute -- and therefore
+every tensor handed from one layer to the next -- in bf16. This module is that activation side:
+batch-norm, residual add, ReLU backward, pooling and the convolution GEMM plumbing on bf16 tensors
+(``csrc/kernels/act_bf16.cu``), with fp32 statistics / reductions / master weights. For a memory-bound
+network this halves (batch-norm backward: x0.38) the bytes every elementwise pass moves and removes the
+fp32->bf16 operand casts in front of the tcgen05 GEMMs: a 1x1 convolution reads its A operand straight
+from the previous layer's output.
+
+CPU restatement (the oracle for the GPU tests): the same math in fp32 on the bf16-rounded inputs, rounded
+to bf16 where the CUDA kernel stores bf16.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import native, tensorcore
+from . import reference as ref
+from .mixed import cast_bf16_masked
+from .mixed_conv import _scratch, _geom, _r8
+
+c_p, c_i, c_l, c_f, c_z = native.c_p, native.c_i, native.c_l, native.c_f, native.c_z
+BF = torch.bfloat16
+
+for _n, _a in [
+    ("tfde_act16_supported_channels", [c_i]),
+    ("tfde_bn_fwd_train_bf16", [c_p, c_p, c_l, c_i, c_p, c_p, c_p, c_p, c_f, c_f, c_i, c_i, c_p, c_p, c_p, c_p,
+                                c_p, c_z, c_p, c_p]),
+    ("tfde_bn_apply_bf16", [c_p, c_p, c_l, c_i, c_p, c_p, c_i, c_p]),
+    ("tfde_bn_bwd_bf16", [c_p, c_p, c_p, c_l, c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_p, c_p, c_p, c_z, c_p, c_p]),
+    ("tfde_colsum_bf16", [c_p, c_l, c_i, c_p, c_p, c_z, c_p, c_p]),
+    ("tfde_add_bf16", [c_p, c_p, c_p, c_l, c_i, c_p]),
+    ("tfde_relu_bwd_bf16", [c_p, c_p, c_p, c_p, c_l, c_p]),
+    ("tfde_cast_f32_bf16", [c_p, c_p, c_l, c_p]),
+    ("tfde_maxpool_fwd_bf16", [c_p, c_p, c_p] + [c_i] * 12 + [c_p]),
+    ("tfde_maxpool_bwd_bf16", [c_p, c_p, c_p] + [c_i] * 12 + [c_p]),
+    ("tfde_gap_fwd_bf16", [c_p, c_p, c_i, c_i, c_i, c_p]),
+    ("tfde_gap_bwd_bf16", [c_p, c_p, c_i, c_i, c_i, c_p]),
+    ("tfde_im2col_b2b", [c_p, c_p] + [c_i] * 13 + [c_i, c_p]),
+    ("tfde_dgrad_gather_b2b", [c_p, c_p] + [c_i] * 13 + [c_i, c_p]),
+]:
+    native.register_optional(_n, _a)
+
+
+def channels_supported(c: int) -> bool:
+    """Channel counts the 8-wide kernels take: C % 8 == 0 and (C/8 divides 256 or C % 256 == 0)."""
+    if c < 8 or c % 8:
+        return False
+    t = min(c // 8, 32)
+    return 256 % t == 0 and c % (8 * t) == 0
+
+
+def _ws(device):
+    w = native.Workspace.current(device)
+    return w, w.small.data_ptr(), w.small.numel(), w.counters.data_ptr()
+
+
+def _empty_like_bf(t, out):
+    return out if out is not None else torch.empty(t.shape, dtype=BF, device=t.device)
+
+
+# ----------------------------------------------------------------------------------------------
+# batch normalisation
+# ----------------------------------------------------------------------------------------------
+def bn_fwd(x, gamma, beta, moving_mean, moving_var, momentum, eps, training, relu, unbiased_moving,
+           out=None, save_mean=None, save_invstd=None, scale=None, shift=None):
+    """x, out: bf16 [..., C]. Updates the moving statistics in place when training. Returns
+    (y, save_mean, save_invstd, scale, shift); scale/shift are the folded per-channel affine that the
+    backward uses to recompute the fused-ReLU mask from x."""
+    C = x.shape[-1]
+    M = x.numel() // C
+    dev = x.device
+    f = lambda t: t if t is not None else torch.empty(C, dtype=torch.float32, device=dev)
+    save_mean, save_invstd, scale, shift = f(save_mean), f(save_invstd), f(scale), f(shift)
+    if not x.is_cuda:
+        xf = x.float()
+        if training:
+            y, sm, si, mm, mv = ref.bn_fwd(xf, gamma, beta, moving_mean, moving_var, momentum, eps, True, False,
+                                           unbiased_moving)
+            moving_mean.copy_(mm); moving_var.copy_(mv)
+            save_mean.copy_(sm); save_invstd.copy_(si)
+        else:
+            save_mean.copy_(moving_mean); save_invstd.copy_(torch.rsqrt(moving_var + eps))
+        sc = save_invstd * (gamma if gamma is not None else 1.0)
+        scale.copy_(sc)
+        shift.copy_((beta if beta is not None else 0.0) - save_mean * sc)
+        y = torch.addcmul(shift, xf, scale)
+        y = torch.relu(y) if relu else y
+        y = y.to(BF)
+        if out is not None:
+            out.copy_(y)
+            y = out
+        return y, save_mean, save_invstd, scale, shift
+    L = native.load()
+    y = _empty_like_bf(x, out)
+    if training:
+        _, ws, wsn, cnt = _ws(dev)
+        native.check(L.tfde_bn_fwd_train_bf16(x.data_ptr(), y.data_ptr(), M, C, native.ptr(gamma), native.ptr(beta),
+                                              moving_mean.data_ptr(), moving_var.data_ptr(), momentum, eps,
+                                              1 if relu else 0, 1 if unbiased_moving else 0, save_mean.data_ptr(),
+                                              save_invstd.data_ptr(), scale.data_ptr(), shift.data_ptr(), ws, wsn,
+                                              cnt, native.stream_ptr()), "bn_fwd_train_bf16")
+    else:
+        save_mean.copy_(moving_mean)
+        torch.rsqrt(moving_var + eps, out=save_invstd)
+        torch.mul(save_invstd, gamma, out=scale) if gamma is not None else scale.copy_(save_invstd)
+        shift.copy_((beta if beta is not None else 0.0) - save_mean * scale)
+        native.check(L.tfde_bn_apply_bf16(x.data_ptr(), y.data_ptr(), M, C, scale.data_ptr(), shift.data_ptr(),
+                                          1 if relu else 0, native.stream_ptr()), "bn_apply_bf16")
+    return y, save_mean, save_invstd, scale, shift
+
+
+def bn_bwd(x, dy, gamma, save_mean, save_invstd, scale, shift, relu, out_dx=None, out_dgamma=None, out_dbeta=None):
+    """Returns (dx bf16, dgamma, dbeta). With ``relu`` the mask (y > 0) is recomputed as x*scale+shift > 0."""
+    C = x.shape[-1]
+    M = x.numel() // C
+    dev = x.device
+    dgamma = out_dgamma if out_dgamma is not None else torch.empty(C, dtype=torch.float32, device=dev)
+    dbeta = out_dbeta if out_dbeta is not None else torch.empty(C, dtype=torch.float32, device=dev)
+    if not x.is_cuda:
+        xf, g = x.float(), dy.float()
+        if relu:
+            g = g * (torch.addcmul(shift, xf, scale) > 0).to(g.dtype)
+        dx, dg, db = ref.bn_bwd(xf, None, g, gamma, save_mean, save_invstd, False)
+        dgamma.copy_(dg if dg is not None else (g * (xf - save_mean) * save_invstd).reshape(-1, C).sum(0))
+        dbeta.copy_(db)
+        dx = dx.to(BF)
+        if out_dx is not None:
+            out_dx.copy_(dx)
+            dx = out_dx
+        return dx, dgamma, dbeta
+    L = native.load()
+    dx = _empty_like_bf(x, out_dx)
+    _, ws, wsn, cnt = _ws(dev)
+    native.check(L.tfde_bn_bwd_bf16(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), M, C, native.ptr(gamma),
+                                    save_mean.data_ptr(), save_invstd.data_ptr(), scale.data_ptr(), shift.data_ptr(),
+                                    1 if relu else 0, dgamma.data_ptr(), dbeta.data_ptr(), ws, wsn, cnt,
+                                    native.stream_ptr()), "bn_bwd_bf16")
+    return dx, dgamma, dbeta
+
+
+def colsum(x2, out=None):
+    """fp32 column sums of a bf16 [M, C] matrix (bias gradient)."""
+    M, C = x2.shape
+    o = out if out is not None else torch.empty(C, dtype=torch.float32, device=x2.device)
+    if not x2.is_cuda:
+        o.copy_(x2.float().sum(0))
+        return o
+    _, ws, wsn, cnt = _ws(x2.device)
+    native.check(native.load().tfde_colsum_bf16(x2.data_ptr(), M, C, o.data_ptr(), ws, wsn, cnt, native.stream_ptr()),
+                 "colsum_bf16")
+    return o
+
+
+# ----------------------------------------------------------------------------------------------
+# elementwise / pooling
+# ----------------------------------------------------------------------------------------------
+def add(a, b, relu=False, out=None):
+    if not a.is_cuda:
+        y = a.float() + b.float()
+        y = (torch.relu(y) if relu else y).to(BF)
+        if out is not None:
+            out.copy_(y)
+            return out
+        return y
+    y = _empty_like_bf(a, out)
+    native.check(native.load().tfde_add_bf16(a.data_ptr(), b.data_ptr(), y.data_ptr(), a.numel(), 1 if relu else 0,
+                                             native.stream_ptr()), "add_bf16")
+    return y
+
+
+def relu_bwd(y, dy, addend=None, out=None):
+    """dx = dy * (y > 0) [+ addend]."""
+    if not y.is_cuda:
+        d = dy.float() * (y.float() > 0).float()
+        if addend is not None:
+            d = d + addend.float()
+        d = d.to(BF)
+        if out is not None:
+            out.copy_(d)
+            return out
+        return d
+    dx = _empty_like_bf(y, out)
+    native.check(native.load().tfde_relu_bwd_bf16(y.data_ptr(), dy.data_ptr(), native.ptr(addend), dx.data_ptr(),
+                                                  y.numel(), native.stream_ptr()), "relu_bwd_bf16")
+    return dx
+
+
+def cast_to_bf16(x, out=None):
+    if not x.is_cuda:
+        y = x.to(BF)
+        if out is not None:
+            out.copy_(y)
+            return out
+        return y
+    y = _empty_like_bf(x, out)
+    native.check(native.load().tfde_cast_f32_bf16(x.data_ptr(), y.data_ptr(), x.numel(), native.stream_ptr()),
+                 "cast_f32_bf16")
+    return y
+
+
+def maxpool_fwd(x, pool, stride, pads, out=None, out_idx=None):
+    b, h, w, c = x.shape
+    ho = (h + pads[0] + pads[1] - pool[0]) // stride[0] + 1
+    wo = (w + pads[2] + pads[3] - pool[1]) // stride[1] + 1
+    if not x.is_cuda:
+        y, i = ref.maxpool_fwd(x.float(), pool, stride, pads)
+        y = y.to(BF)
+        if out is not None:
+            out.copy_(y); y = out
+        if out_idx is not None:
+            out_idx.copy_(i); i = out_idx
+        return y, i
+    y = out if out is not None else torch.empty((b, ho, wo, c), dtype=BF, device=x.device)
+    idx = out_idx if out_idx is not None else torch.empty((b, ho, wo, c), dtype=torch.uint8, device=x.device)
+    native.check(native.load().tfde_maxpool_fwd_bf16(x.data_ptr(), y.data_ptr(), idx.data_ptr(), b, h, w, c, pool[0],
+                                                     pool[1], stride[0], stride[1], pads[0], pads[2], ho, wo,
+                                                     native.stream_ptr()), "maxpool_fwd_bf16")
+    return y, idx
+
+
+def maxpool_bwd(dy, idx, x_shape, pool, stride, pads, out=None):
+    b, h, w, c = x_shape
+    ho, wo = dy.shape[1], dy.shape[2]
+    if not dy.is_cuda:
+        dx = ref.maxpool_bwd(dy.float(), idx, x_shape, pool, stride, pads).to(BF)
+        if out is not None:
+            out.copy_(dx)
+            return out
+        return dx
+    dx = out if out is not None else torch.empty(tuple(x_shape), dtype=BF, device=dy.device)
+    native.check(native.load().tfde_maxpool_bwd_bf16(dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), b, h, w, c, pool[0],
+                                                     pool[1], stride[0], stride[1], pads[0], pads[2], ho, wo,
+                                                     native.stream_ptr()), "maxpool_bwd_bf16")
+    return dx
+
+
+def global_avgpool_fwd(x, out=None):
+    """bf16 [B, H, W, C] -> fp32 [B, C] (the classifier head stays fp32)."""
+    b, h, w, c = x.shape
+    if not x.is_cuda:
+        y = x.float().mean(dim=(1, 2))
+        if out is not None:
+            out.copy_(y)
+            return out
+        return y
+    y = out if out is not None else torch.empty((b, c), dtype=torch.float32, device=x.device)
+    native.check(native.load().tfde_gap_fwd_bf16(x.data_ptr(), y.data_ptr(), b, h * w, c, native.stream_ptr()),
+                 "gap_fwd_bf16")
+    return y
+
+
+def global_avgpool_bwd(dy, x_shape, out=None):
+    b, h, w, c = x_shape
+    if not dy.is_cuda:
+        dx = (dy.float() / float(h * w)).reshape(b, 1, 1, c).expand(b, h, w, c).to(BF).contiguous()
+        if out is not None:
+            out.copy_(dx)
+            return out
+        return dx
+    dx = out if out is not None else torch.empty(tuple(x_shape), dtype=BF, device=dy.device)
+    native.check(native.load().tfde_gap_bwd_bf16(dy.data_ptr(), dx.data_ptr(), b, h * w, c, native.stream_ptr()),
+                 "gap_bwd_bf16")
+    return dx
+
+
+# ----------------------------------------------------------------------------------------------
+# convolution: bf16 activations in, bf16 activations out, fp32 weights / weight gradients
+# ----------------------------------------------------------------------------------------------
+def conv_supported(x_shape, w_shape, ho, wo, x_is_bf16=True) -> bool:
+    b, h, wd, c = x_shape
+    cout = w_shape[3]
+    M, Min = b * ho * wo, b * h * wd
+    return (M % 8 == 0 and Min % 8 == 0 and M >= 128 and channels_supported(cout)
+            and (not x_is_bf16 or c % 8 == 0))
+
+
+def _bf(t):
+    return t.to(BF).to(torch.float32)
+
+
+def _a_operand(x, w_shape, stride, pads, ho, wo, tag):
+    """K-major bf16 A operand [M, kp] of the forward / filter-gradient GEMM."""
+    L = native.load()
+    b, h, wd, c = x.shape
+    kh, kw, _, cout = w_shape
+    M, kc = b * ho * wo, kh * kw * c
+    kp = _r8(kc)
+    g = _geom(x.shape, w_shape, stride, pads, ho, wo)
+    if x.dtype == BF:
+        if kh == 1 and kw == 1 and tuple(stride) == (1, 1):
+            return x.reshape(M, c), kp                 # the activation IS the operand
+        a = _scratch(x.device, tag, M * kp).view(M, kp)
+        native.check(L.tfde_im2col_b2b(x.data_ptr(), a.data_ptr(), *g, kp, native.stream_ptr()), "im2col_b2b")
+        return a, kp
+    a = _scratch(x.device, tag, M * kp).view(M, kp)
+    native.check(L.tfde_im2col_bf16(x.data_ptr(), a.data_ptr(), *g, kp, native.stream_ptr()), "im2col_bf16")
+    return a, kp
+
+
+def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None):
+    """x: bf16 NHWC (or the fp32 network input); w: fp32 HWIO; returns bf16 NHWC."""
+    b, h, wd, c = x.shape
+    kh, kw, _, cout = w.shape
+    ho = (h + pads[0] + pads[1] - kh) // stride[0] + 1
+    wo = (wd + pads[2] + pads[3] - kw) // stride[1] + 1
+    if not x.is_cuda:
+        y = ref.conv2d_fwd(_bf(x.float()), _bf(w), bias, stride, pads, False).to(BF)
+        if out is not None:
+            out.copy_(y)
+            return out
+        return y
+    L = native.load()
+    M, kc = b * ho * wo, kh * kw * c
+    a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "A")
+    wt = _scratch(x.device, "B", cout * kp).view(cout, kp)
+    native.check(L.tfde_cast_transpose_pad_bf16(w.data_ptr(), None, wt.data_ptr(), kc, cout, kp, native.stream_ptr()),
+                 "cast_transpose_pad_bf16")
+    y = out if out is not None else torch.empty((b, ho, wo, cout), dtype=BF, device=x.device)
+    tensorcore.gemm_bf16_tn(a, wt, bias, False, BF, out=y.view(M, cout))
+    return y
+
+
+def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bias=True, bias_grad_zero=False,
+               out_dx=None, out_dw=None, out_db=None):
+    """dy: bf16. Returns (dx bf16 | None, dw fp32, db fp32 | None).
+    ``bias_grad_zero``: the convolution feeds a training-mode batch-norm, whose input gradient sums to zero
+    over every channel (batch-norm is invariant to a per-channel shift of its input), so the bias gradient
+    is identically zero and its reduction is skipped."""
+    b, h, wd, c = x.shape
+    kh, kw, _, cout = w.shape
+    ho, wo = dy.shape[1], dy.shape[2]
+    if not x.is_cuda:
+        g = dy.float()
+        dx, dw, _ = ref.conv2d_bwd(_bf(x.float()), _bf(w), None, g, stride, pads, False, need_dx, False)
+        db = None
+        if has_bias:
+            db = torch.zeros(cout) if bias_grad_zero else g.sum(dim=(0, 1, 2))
+        if dx is not None:
+            dx = dx.to(BF)
+        for o, v in ((out_dx, dx), (out_dw, dw), (out_db, db)):
+            if o is not None and v is not None:
+                o.copy_(v)
+        return (out_dx if out_dx is not None and dx is not None else dx, out_dw if out_dw is not None else dw,
+                out_db if out_db is not None and db is not None else db)
+    L = native.load()
+    dev = x.device
+    M, kc, min_, kd = b * ho * wo, kh * kw * c, b * h * wd, kh * kw * cout
+    dy2 = dy.reshape(M, cout)
+    # filter gradient: dW[kc, cout] = A^T[kc, M] . dy^T[cout, M]^T (both K-major after a bf16 transpose)
+    a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "C")
+    at = _scratch(dev, "A", kc * M).view(kc, M)
+    native.check(L.tfde_transpose_bf16(a.data_ptr(), at.data_ptr(), M, kc, kp, M, native.stream_ptr()), "transpose_bf16")
+    dyt = _scratch(dev, "B", cout * M).view(cout, M)
+    native.check(L.tfde_transpose_bf16(dy2.data_ptr(), dyt.data_ptr(), M, cout, cout, M, native.stream_ptr()),
+                 "transpose_bf16")
+    dw = out_dw if out_dw is not None else torch.empty(tuple(w.shape), dtype=torch.float32, device=dev)
+    tensorcore.gemm_bf16_tn(at, dyt, None, False, torch.float32, out=dw.view(kc, cout))
+    db = None
+    if has_bias:
+        if bias_grad_zero:
+            db = out_db if out_db is not None else torch.zeros(cout, dtype=torch.float32, device=dev)
+        else:
+            db = colsum(dy2, out=out_db)
+    dx = None
+    if need_dx:
+        if kh == 1 and kw == 1 and tuple(stride) == (1, 1):
+            ga = dy2                                                     # Min == M: dy IS the operand
+            wr = cast_bf16_masked(w.reshape(c, cout), None, out=_scratch(dev, "B", c * cout).view(c, cout))
+        else:
+            ga = _scratch(dev, "A", min_ * kd).view(min_, kd)
+            g = _geom(x.shape, w.shape, stride, pads, ho, wo)
+            native.check(L.tfde_dgrad_gather_b2b(dy.data_ptr(), ga.data_ptr(), *g, kd, native.stream_ptr()),
+                         "dgrad_gather_b2b")
+            wr = _scratch(dev, "B", c * kd).view(c, kd)
+            native.check(L.tfde_wrot_bf16(w.data_ptr(), wr.data_ptr(), kh, kw, c, cout, kd, native.stream_ptr()),
+                         "wrot_bf16")
+        dx = out_dx if out_dx is not None else torch.empty(tuple(x.shape), dtype=BF, device=dev)
+        tensorcore.gemm_bf16_tn(ga, wr, None, False, BF, out=dx.view(min_, c))
+    return dx, dw, db

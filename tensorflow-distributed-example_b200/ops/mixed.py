@@ -21,18 +21,33 @@ native.register_optional("tfde_cast_bf16_masked", [c_p, c_p, c_p, c_l, c_p])
 native.register_optional("tfde_colsum_masked", [c_p, c_p, c_p, c_l, c_i, c_p, c_p, c_p])
 
 _policy = "float32"
+_activations = "float32"
 
 
-def set_global_policy(name: str):
-    """tf.keras.mixed_precision.set_global_policy: 'float32' (reference default) or 'mixed_bfloat16'."""
-    global _policy
+def set_global_policy(name: str, activations: str = None):
+    """tf.keras.mixed_precision.set_global_policy: 'float32' (reference default) or 'mixed_bfloat16'.
+
+    ``activations`` (extension): dtype of the tensors handed from layer to layer under 'mixed_bfloat16'.
+    'float32' (default) keeps fp32 activations and rounds only the GEMM operands; 'bfloat16' is Keras' own
+    mixed-precision semantics (bf16 layer outputs, fp32 variables) and what convolutional networks should
+    use: see ops/act16.py."""
+    global _policy, _activations
     if name not in ("float32", "mixed_bfloat16"):
         raise ValueError("policy must be 'float32' or 'mixed_bfloat16'")
+    if activations not in (None, "float32", "bfloat16"):
+        raise ValueError("activations must be 'float32' or 'bfloat16'")
+    if activations == "bfloat16" and name != "mixed_bfloat16":
+        raise ValueError("bfloat16 activations need the 'mixed_bfloat16' policy")
     _policy = name
+    _activations = activations or "float32"
 
 
 def global_policy() -> str:
     return _policy
+
+
+def activation_dtype() -> str:
+    return _activations if _policy == "mixed_bfloat16" else "float32"
 
 
 def supported(M: int, K: int, N: int) -> bool:

@@ -1,0 +1,168 @@
+"""bf16-activation kernels (csrc/kernels/act_bf16.cu, ops/act16.py) against their fp32 PyTorch restatement:
+the CPU branch of every op is the plain fp32 reference applied to the same bf16-rounded inputs, rounded to
+bf16 where the kernel stores bf16. Tolerances are one bf16 ulp of the result (2^-8 relative) plus the
+reduction-order noise of the fp32 statistics."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+BF = torch.bfloat16
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    return torch.device("cuda", 0)
+
+
+def _close(a, b, rtol=2e-2, atol=2e-2):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    assert a.shape == b.shape
+    err = (a - b).abs()
+    bound = atol + rtol * b.abs()
+    frac_bad = (err > bound).float().mean().item()
+    assert frac_bad < 1e-3, f"{frac_bad:.4%} of elements out of tolerance, max err {err.max().item():.4g}"
+
+
+@pytest.mark.parametrize("M,C,relu", [(6272, 64, True), (1568, 256, False), (392, 512, True), (200, 2048, True),
+                                      (777, 128, True)])
+def test_bn_fwd_bwd(M, C, relu):
+    from tfde_b200.ops import act16
+    dev = _dev()
+    g = torch.Generator().manual_seed(M + C)
+    x = (torch.randn(M, C, generator=g) * 1.5 + 0.3).to(BF)
+    dy = torch.randn(M, C, generator=g).to(BF)
+    gamma = torch.rand(C, generator=g) + 0.5
+    beta = torch.randn(C, generator=g) * 0.1
+    mm, mv = torch.zeros(C), torch.ones(C)
+    yc, smc, sic, scc, shc = act16.bn_fwd(x, gamma, beta, mm, mv, 0.99, 1e-3, True, relu, True)
+    dxc, dgc, dbc = act16.bn_bwd(x, dy, gamma, smc, sic, scc, shc, relu)
+    mmg, mvg = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    yg, smg, sig, scg, shg = act16.bn_fwd(x.to(dev), gamma.to(dev), beta.to(dev), mmg, mvg, 0.99, 1e-3, True, relu, True)
+    dxg, dgg, dbg = act16.bn_bwd(x.to(dev), dy.to(dev), gamma.to(dev), smg, sig, scg, shg, relu)
+    torch.cuda.synchronize()
+    assert yg.dtype == BF and dxg.dtype == BF
+    _close(smg, smc, 1e-4, 1e-4)
+    _close(sig, sic, 1e-3, 1e-4)
+    _close(mmg, mm, 1e-4, 1e-5)
+    _close(mvg, mv, 1e-3, 1e-5)
+    _close(yg, yc)
+    _close(dbg, dbc, 2e-3, 0.05)
+    _close(dgg, dgc, 2e-3, 0.05)
+    _close(dxg, dxc, 3e-2, 3e-2)
+
+
+def test_bn_inference_and_colsum():
+    from tfde_b200.ops import act16
+    dev = _dev()
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(1000, 64, generator=g).to(BF)
+    gamma, beta = torch.rand(64, generator=g) + 0.5, torch.randn(64, generator=g)
+    mm, mv = torch.randn(64, generator=g) * 0.1, torch.rand(64, generator=g) + 0.5
+    yc = act16.bn_fwd(x, gamma, beta, mm.clone(), mv.clone(), 0.99, 1e-3, False, True, True)[0]
+    yg = act16.bn_fwd(x.to(dev), gamma.to(dev), beta.to(dev), mm.to(dev), mv.to(dev), 0.99, 1e-3, False, True, True)[0]
+    _close(yg, yc)
+    _close(act16.colsum(x.to(dev)), x.float().sum(0), 1e-3, 1e-2)
+
+
+def test_elementwise_and_pools():
+    from tfde_b200.ops import act16
+    dev = _dev()
+    g = torch.Generator().manual_seed(2)
+    a = torch.randn(8, 14, 14, 64, generator=g).to(BF)
+    b = torch.randn(8, 14, 14, 64, generator=g).to(BF)
+    _close(act16.add(a.to(dev), b.to(dev), relu=True), act16.add(a, b, relu=True), 1e-2, 1e-2)
+    _close(act16.relu_bwd(a.to(dev), b.to(dev)), act16.relu_bwd(a, b), 0, 0)
+    _close(act16.relu_bwd(a.to(dev), b.to(dev), addend=a.to(dev)), act16.relu_bwd(a, b, addend=a), 1e-2, 1e-2)
+    x32 = torch.randn(1000, generator=g)
+    _close(act16.cast_to_bf16(x32.to(dev)), x32.to(BF), 0, 0)
+    # max-pool 3x3 / stride 2 / same (the ResNet stem) and its backward
+    x = torch.randn(4, 17, 17, 64, generator=g).to(BF)
+    pads = (0, 1, 0, 1)
+    yc, ic = act16.maxpool_fwd(x, (3, 3), (2, 2), pads)
+    yg, ig = act16.maxpool_fwd(x.to(dev), (3, 3), (2, 2), pads)
+    _close(yg, yc, 0, 0)
+    assert torch.equal(ig.cpu(), ic)
+    dy = torch.randn(*yc.shape, generator=g).to(BF)
+    _close(act16.maxpool_bwd(dy.to(dev), ig, tuple(x.shape), (3, 3), (2, 2), pads),
+           act16.maxpool_bwd(dy, ic, tuple(x.shape), (3, 3), (2, 2), pads), 1e-2, 1e-2)
+    # global average pool
+    _close(act16.global_avgpool_fwd(a.to(dev)), act16.global_avgpool_fwd(a), 1e-4, 1e-4)
+    d = torch.randn(8, 64, generator=g)
+    _close(act16.global_avgpool_bwd(d.to(dev), tuple(a.shape)), act16.global_avgpool_bwd(d, tuple(a.shape)), 1e-2, 1e-4)
+
+
+@pytest.mark.parametrize("cfg", [
+    dict(B=8, H=16, W=16, C=64, K=1, Co=256, s=1, pad="same"),     # 1x1: activation is the GEMM operand
+    dict(B=8, H=16, W=16, C=64, K=3, Co=64, s=1, pad="same"),      # 3x3: bf16 im2col / dgrad gather
+    dict(B=8, H=16, W=16, C=128, K=1, Co=256, s=2, pad="same"),    # strided 1x1 (projection shortcut)
+    dict(B=8, H=32, W=32, C=3, K=7, Co=64, s=2, pad="same", f32in=True),   # stem: fp32 image in
+])
+def test_conv(cfg):
+    from tfde_b200 import ops
+    from tfde_b200.ops import act16
+    dev = _dev()
+    g = torch.Generator().manual_seed(cfg["K"] * 100 + cfg["C"])
+    B, H, W, C, K, Co, s = (cfg[k] for k in ("B", "H", "W", "C", "K", "Co", "s"))
+    ho, wo, pads = ops.conv_geometry(H, W, K, K, (s, s), cfg["pad"])
+    x = torch.randn(B, H, W, C, generator=g)
+    if not cfg.get("f32in"):
+        x = x.to(BF)
+    w = torch.randn(K, K, C, Co, generator=g) * (1.0 / (K * K * C) ** 0.5)
+    bias = torch.randn(Co, generator=g) * 0.1
+    dy = torch.randn(B, ho, wo, Co, generator=g).to(BF)
+    need_dx = not cfg.get("f32in")
+    yc = act16.conv2d_fwd(x, w, bias, (s, s), pads)
+    dxc, dwc, dbc = act16.conv2d_bwd(x, w, dy, (s, s), pads, need_dx=need_dx)
+    yg = act16.conv2d_fwd(x.to(dev), w.to(dev), bias.to(dev), (s, s), pads)
+    dxg, dwg, dbg = act16.conv2d_bwd(x.to(dev), w.to(dev), dy.to(dev), (s, s), pads, need_dx=need_dx)
+    torch.cuda.synchronize()
+    assert yg.dtype == BF
+    _close(yg, yc)
+    _close(dwg, dwc, 1e-2, 5e-2)
+    _close(dbg, dbc, 1e-3, 5e-2)
+    if need_dx:
+        assert dxg.dtype == BF
+        _close(dxg, dxc)
+    # the identically-zero bias gradient of conv -> batch-norm
+    _, _, dbz = act16.conv2d_bwd(x.to(dev), w.to(dev), dy.to(dev), (s, s), pads, need_dx=False, bias_grad_zero=True)
+    assert float(dbz.abs().max()) == 0.0
+
+
+def test_resnet_bf16_activations_match_cpu_restatement():
+    """A small ResNet trained for a few steps with bf16 activations: the CUDA path follows the CPU restatement
+    of the same policy, and both follow the fp32 model."""
+    import tfde_b200 as tf
+    from tfde_b200.models import resnet
+    from tfde_b200.parallel.strategy import Strategy
+    _dev()
+    g = torch.Generator().manual_seed(0)
+    x = torch.rand(32, 32, 32, 3, generator=g)
+    y = torch.randint(0, 10, (32,), generator=g)
+
+    def train(device, policy, acts):
+        tf.keras.mixed_precision.set_global_policy(policy, activations=acts)
+        try:
+            with Strategy(device=device).scope():
+                m = resnet.build_resnet((1, 1, 1, 1), 16, 10, (32, 32, 3), seed=3)
+                m.compile(optimizer=tf.keras.optimizers.SGD(0.05),
+                          loss=tf.keras.losses.SparseCategoricalCrossentropy(from_logits=True), metrics=["accuracy"])
+            out = []
+            for _ in range(4):
+                m.train_on_batch(x, y)
+                out.append(m.last_step_loss())
+            dts = [getattr(l, "_out_dtype", None) for l in m.exec_plan]
+            return out, dts, m
+        finally:
+            tf.keras.mixed_precision.set_global_policy("float32")
+
+    lg, dts, mg = train("cuda", "mixed_bfloat16", "bfloat16")
+    lc, _, _ = train("cpu", "mixed_bfloat16", "bfloat16")
+    lf, _, _ = train("cpu", "float32", None)
+    assert dts[0] == BF and dts[4] == BF, dts          # stem conv and first block really ran in bf16
+    assert mg.graph_captured
+    assert abs(lg[0] - lc[0]) < 0.05 and abs(lg[0] - lf[0]) < 0.1, (lg, lc, lf)
+    for a, b in zip(lg, lc):
+        assert abs(a - b) < 0.25 * max(1.0, abs(b)), (lg, lc, lf)
+    assert lg[-1] < lg[0]

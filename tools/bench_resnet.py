@@ -19,6 +19,8 @@ def main():
     ap.add_argument("--size", type=int, default=224)
     ap.add_argument("--impl", default="ours", choices=["ours", "torch"])
     ap.add_argument("--dtype", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--acts", default="bfloat16", choices=["float32", "bfloat16"],
+                    help="activation dtype under --dtype bf16 (ours): bf16 layer outputs (default) or fp32")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -28,7 +30,7 @@ def main():
     if a.impl == "ours":
         import tfde_b200 as tf
         if a.dtype == "bf16":
-            tf.keras.mixed_precision.set_global_policy("mixed_bfloat16")
+            tf.keras.mixed_precision.set_global_policy("mixed_bfloat16", activations=a.acts)
         st = tf.distribute.MirroredStrategy() if world > 1 else tf.distribute.get_strategy()
         with st.scope():
             m = tf.models.build_and_compile_resnet50(seed=1, input_shape=(a.size, a.size, 3))
@@ -87,7 +89,7 @@ def main():
         ms = t.item()
     if rank == 0:
         print(json.dumps({"metric": "resnet50_train_images_per_sec", "value": a.batch * world / (ms * 1e-3),
-                          "ms_per_step": ms, "n_gpus": world, "per_gpu_batch": a.batch, "dtype": a.dtype,
+                          "ms_per_step": ms, "n_gpus": world, "per_gpu_batch": a.batch, "dtype": a.dtype, "acts": a.acts if a.dtype == "bf16" else "float32",
                           "impl": a.impl, "loss": loss(), "wall_s": time.perf_counter() - t0,
                           "graph": m.graph_captured}), flush=True)
     if a.impl == "ours":
