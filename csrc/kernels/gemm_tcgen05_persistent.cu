@@ -50,6 +50,13 @@ __device__ __forceinline__ void p_tma_load_2d(void* dst, const CUtensorMap* map,
 __device__ __forceinline__ uint64_t p_smem_desc(uint32_t addr) {   // K-major, SWIZZLE_128B (see gemm_tcgen05.cu)
   return (uint64_t)((addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
+// MN-major operand (the non-reduced dimension is the contiguous one in global memory), SWIZZLE_128B:
+// a TMA box of {64 MN elements = 128 B, 64 K rows} lands as 64 rows of 128 B; 8 rows form one 1024-byte
+// swizzle atom (stride-dimension offset, K direction), consecutive 64-wide MN blocks are whole boxes
+// 8192 bytes apart (leading-dimension offset).
+__device__ __forceinline__ uint64_t p_smem_desc_mn(uint32_t addr) {
+  return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)(8192 >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
 __device__ __forceinline__ void p_umma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
@@ -79,7 +86,10 @@ struct PEpilogue {
   int M, N;
 };
 
-template <int BN>
+// MNMAJ = 0: A[M,K], B[N,K] (K contiguous).  MNMAJ = 1: A[K,M], B[K,N] (M / N contiguous) -- the layout a
+// filter-gradient GEMM finds its operands in (activations [rows, Cin] and gradients [rows, Cout], reduced
+// over rows), so no transposed copies are needed.
+template <int BN, int MNMAJ>
 __global__ void __launch_bounds__(P_THREADS, 1)
 gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                                     const PEpilogue ep_in, const int K, const int tiles_m, const int tiles_n,
@@ -135,14 +145,22 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
           p_mbar_wait(&empty_bar[s], ph ^ 1u);
           p_mbar_expect_tx(&full_bar[s], STAGE_BYTES);
           uint8_t* a_dst = smem + (size_t)s * STAGE_BYTES;
-          p_tma_load_2d(a_dst, &tmA, &full_bar[s], kb * P_BK, m0);
-          p_tma_load_2d(a_dst + A_BYTES, &tmB, &full_bar[s], kb * P_BK, n0);
+          if (MNMAJ) {
+#pragma unroll
+            for (int j = 0; j < P_BM / 64; ++j) p_tma_load_2d(a_dst + j * 8192, &tmA, &full_bar[s], m0 + j * 64, kb * P_BK);
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) p_tma_load_2d(a_dst + A_BYTES + j * 8192, &tmB, &full_bar[s], n0 + j * 64, kb * P_BK);
+          } else {
+            p_tma_load_2d(a_dst, &tmA, &full_bar[s], kb * P_BK, m0);
+            p_tma_load_2d(a_dst + A_BYTES, &tmB, &full_bar[s], kb * P_BK, n0);
+          }
         }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(P_BM >> 4) << 24);
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(P_BM >> 4) << 24) |
+                             (MNMAJ ? ((1u << 15) | (1u << 16)) : 0u);
       uint32_t it = 0, tl = 0;                           // tl: tiles done by this CTA
       for (int item = blockIdx.x; item < num_tiles; item += gridDim.x, ++tl) {
         const int z = item % splits;
@@ -157,9 +175,12 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
           const uint32_t a_addr = p_smem_u32(smem + (size_t)s * STAGE_BYTES);
           const uint32_t b_addr = a_addr + A_BYTES;
 #pragma unroll
-          for (int k = 0; k < P_BK / P_UMMA_K; ++k)
-            p_umma(tmem_d + acc * BN, p_smem_desc(a_addr + k * P_UMMA_K * 2), p_smem_desc(b_addr + k * P_UMMA_K * 2),
-                   idesc, (kb != kb_begin || k != 0) ? 1u : 0u);
+          for (int k = 0; k < P_BK / P_UMMA_K; ++k) {
+            // K-major: 16 elements = 32 bytes along the swizzled row; MN-major: 16 K rows = 2 atoms = 2048 bytes
+            const uint64_t da = MNMAJ ? p_smem_desc_mn(a_addr + k * 2048) : p_smem_desc(a_addr + k * P_UMMA_K * 2);
+            const uint64_t db = MNMAJ ? p_smem_desc_mn(b_addr + k * 2048) : p_smem_desc(b_addr + k * P_UMMA_K * 2);
+            p_umma(tmem_d + acc * BN, da, db, idesc, (kb != kb_begin || k != 0) ? 1u : 0u);
+          }
           p_commit(&empty_bar[s]);
         }
         p_commit(&tmem_full[acc]);
@@ -271,21 +292,27 @@ typedef CUresult (*PEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, voi
 PEncodeFn p_encode = nullptr;
 std::mutex p_encode_mu;
 
-int p_make_map(CUtensorMap* map, const void* ptr, long rows, long cols, int box_rows) {
+int p_resolve_encode() {
+  std::lock_guard<std::mutex> lock(p_encode_mu);
+  if (p_encode == nullptr) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    const cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+    if (e != cudaSuccess) return (int)e;
+    if (q != cudaDriverEntryPointSuccess || fn == nullptr) return (int)cudaErrorNotSupported;
+    p_encode = reinterpret_cast<PEncodeFn>(fn);
+  }
+  return 0;
+}
+
+int p_make_map(CUtensorMap* map, const void* ptr, long rows, long cols, int box_rows, int box_cols = P_BK) {
   {
-    std::lock_guard<std::mutex> lock(p_encode_mu);
-    if (p_encode == nullptr) {
-      void* fn = nullptr;
-      cudaDriverEntryPointQueryResult q;
-      const cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
-      if (e != cudaSuccess) return (int)e;
-      if (q != cudaDriverEntryPointSuccess || fn == nullptr) return (int)cudaErrorNotSupported;
-      p_encode = reinterpret_cast<PEncodeFn>(fn);
-    }
+    const int rc0 = p_resolve_encode();
+    if (rc0 != 0) return rc0;
   }
   cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t gstride[1] = {(cuuint64_t)cols * 2};
-  cuuint32_t box[2] = {(cuuint32_t)P_BK, (cuuint32_t)box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   const CUresult r = p_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -293,14 +320,28 @@ int p_make_map(CUtensorMap* map, const void* ptr, long rows, long cols, int box_
   return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
 }
 
-template <int BN>
+// rows x cols view with row stride `ld` elements
+int p_make_map_ld(CUtensorMap* map, const void* ptr, long rows, long cols, long ld, int box_rows, int box_cols) {
+  const int rc = p_resolve_encode();
+  if (rc != 0) return rc;
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  const CUresult r = p_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+}
+
+template <int BN, int MNMAJ>
 int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, int M, int N, int K, float* ws,
              size_t ws_bytes, cudaStream_t stream) {
   constexpr int STAGES = (BN == 256) ? 4 : 6;
   constexpr size_t smem = (size_t)STAGES * (P_BM * P_BK * 2 + BN * P_BK * 2) + 4 * 32 * 33 * sizeof(float) + 1024;
   static bool configured = false;
   if (!configured) {
-    const cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_persistent_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     configured = true;
   }
@@ -322,7 +363,7 @@ int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, 
   }
   const int items = tiles * splits;
   const int grid = items < 148 ? items : 148;
-  gemm_bf16_tcgen05_persistent_kernel<BN><<<grid, P_THREADS, smem, stream>>>(ta, tb, ep, K, tiles_m, tiles_n, splits, ws);
+  gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ><<<grid, P_THREADS, smem, stream>>>(ta, tb, ep, K, tiles_m, tiles_n, splits, ws);
   if (splits > 1) {
     long blocks = ((long)M * N + 255) / 256;
     if (blocks > 148L * 8) blocks = 148L * 8;
@@ -350,7 +391,30 @@ TFDE_API int tfde_gemm_bf16_tn_persistent(const void* A, const void* B, float* c
   rc = p_make_map(&tb, B, N, K, BN);
   if (rc != 0) return rc;
   PEpilogue ep{c_f32, (__nv_bfloat16*)c_bf16, ldc, bias, relu, M, N};
-  if (BN == 64) return p_launch<64>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
-  if (BN == 128) return p_launch<128>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
-  return p_launch<256>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  if (BN == 64) return p_launch<64, 0>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  if (BN == 128) return p_launch<128, 0>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  return p_launch<256, 0>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+}
+
+// C[M,N] = A[K,M]^T . B[K,N]: both operands "MN-major" (row-major with the REDUCED dimension as rows), which
+// is how a filter-gradient GEMM finds them: A = activations / im2col [rows, Kc], B = output gradients
+// [rows, Cout], reduced over rows. No transposed copies; M % 8 == 0 and N % 8 == 0 (16-byte TMA strides),
+// K arbitrary (rows past K are zero-filled by TMA). lda / ldb: row strides in elements (multiples of 8).
+TFDE_API int tfde_gemm_bf16_nt_persistent(const void* A, const void* B, float* c_f32, void* c_bf16, long ldc,
+                                          int M, int N, int K, long lda, long ldb, float* ws, size_t ws_bytes,
+                                          cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || (M & 7) || (N & 7) || (lda & 7) || (ldb & 7) || lda < M || ldb < N || !A || !B ||
+      (!c_f32 && !c_bf16))
+    return TFDE_ERR_INVALID;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return TFDE_ERR_INVALID;
+  const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+  CUtensorMap ta, tb;
+  int rc = p_make_map_ld(&ta, A, K, M, lda, P_BK, 64);
+  if (rc != 0) return rc;
+  rc = p_make_map_ld(&tb, B, K, N, ldb, P_BK, 64);
+  if (rc != 0) return rc;
+  PEpilogue ep{c_f32, (__nv_bfloat16*)c_bf16, ldc, nullptr, 0, M, N};
+  if (BN == 64) return p_launch<64, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  if (BN == 128) return p_launch<128, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  return p_launch<256, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
 }

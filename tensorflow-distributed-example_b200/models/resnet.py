@@ -76,7 +76,7 @@ class Bottleneck(L.Layer):
             y = self.buf("y16", h.shape, torch.bfloat16)
             act16.add(h, sc, relu=True, out=y)
         else:
-            if h.dtype != sc.dtype:
+            if h.dtype != torch.float32 or sc.dtype != torch.float32:
                 h, sc = h.float(), sc.float()
             y = self.buf("y", h.shape)
             ops.add(h, sc, relu=True, out=y)
@@ -93,10 +93,10 @@ class Bottleneck(L.Layer):
         for l in (self.b3, self.c3, self.b2, self.c2, self.b1, self.c1):
             g = l.run_back(g)
         gs = self.c0.run_back(self.b0.run_back(d)) if self.projection else d
-        if self._b16 and g.dtype == torch.bfloat16 and gs.dtype == torch.bfloat16:
+        if g.dtype == torch.bfloat16 and gs.dtype == torch.bfloat16:
             from ..ops import act16
             return act16.add(g, gs, relu=False, out=self.buf("dx16", g.shape, torch.bfloat16))
-        if g.dtype != gs.dtype:
+        if g.dtype != torch.float32 or gs.dtype != torch.float32:
             g, gs = g.float(), gs.float()
         return ops.add(g, gs, relu=False, out=self.buf("dx", g.shape))
 

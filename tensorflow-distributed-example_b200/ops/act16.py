@@ -22,6 +22,7 @@ from .mixed_conv import _scratch, _geom, _r8
 
 c_p, c_i, c_l, c_f, c_z = native.c_p, native.c_i, native.c_l, native.c_f, native.c_z
 BF = torch.bfloat16
+_WGRAD_NT = __import__("os").environ.get("TFDE_WGRAD_NT", "1") == "1"   # MN-major filter-gradient GEMM
 
 for _n, _a in [
     ("tfde_act16_supported_channels", [c_i]),
@@ -52,8 +53,10 @@ def channels_supported(c: int) -> bool:
 
 
 def _ws(device):
+    # partials of the statistics kernels live in the big per-stream scratch (shared, in stream order, with the
+    # split-K GEMMs): 2048 channels x 111 row blocks x 2 sums do not fit the 1 MB `small` buffer
     w = native.Workspace.current(device)
-    return w, w.small.data_ptr(), w.small.numel(), w.counters.data_ptr()
+    return w, w.ws.data_ptr(), w.ws.numel(), w.counters.data_ptr()
 
 
 def _empty_like_bf(t, out):
@@ -350,13 +353,19 @@ def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bia
     dy2 = dy.reshape(M, cout)
     # filter gradient: dW[kc, cout] = A^T[kc, M] . dy^T[cout, M]^T (both K-major after a bf16 transpose)
     a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "C")
-    at = _scratch(dev, "A", kc * M).view(kc, M)
-    native.check(L.tfde_transpose_bf16(a.data_ptr(), at.data_ptr(), M, kc, kp, M, native.stream_ptr()), "transpose_bf16")
-    dyt = _scratch(dev, "B", cout * M).view(cout, M)
-    native.check(L.tfde_transpose_bf16(dy2.data_ptr(), dyt.data_ptr(), M, cout, cout, M, native.stream_ptr()),
-                 "transpose_bf16")
     dw = out_dw if out_dw is not None else torch.empty(tuple(w.shape), dtype=torch.float32, device=dev)
-    tensorcore.gemm_bf16_tn(at, dyt, None, False, torch.float32, out=dw.view(kc, cout))
+    if _WGRAD_NT and kc % 8 == 0:
+        # operands as the forward pass left them: A[M, kc] and dy[M, cout], reduced over rows -> the tcgen05
+        # GEMM reads them MN-major, no transposed copies
+        tensorcore.gemm_bf16_nt(a[:, :kc] if kp != kc else a, dy2, out=dw.view(kc, cout))
+    else:
+        at = _scratch(dev, "A", kc * M).view(kc, M)
+        native.check(L.tfde_transpose_bf16(a.data_ptr(), at.data_ptr(), M, kc, kp, M, native.stream_ptr()),
+                     "transpose_bf16")
+        dyt = _scratch(dev, "B", cout * M).view(cout, M)
+        native.check(L.tfde_transpose_bf16(dy2.data_ptr(), dyt.data_ptr(), M, cout, cout, M, native.stream_ptr()),
+                     "transpose_bf16")
+        tensorcore.gemm_bf16_tn(at, dyt, None, False, torch.float32, out=dw.view(kc, cout))
     db = None
     if has_bias:
         if bias_grad_zero:

@@ -55,3 +55,31 @@ def gemm_bf16_tn(a, b, bias=None, relu=False, out_dtype=torch.float32, out=None,
         native.check(L.tfde_gemm_bf16_tn(a.data_ptr(), b.data_ptr(), f32, b16, c.stride(0), native.ptr(bias),
                                          1 if relu else 0, M, N, K, native.stream_ptr()), "gemm_bf16_tn[tile]")
     return c
+
+
+native.register_optional("tfde_gemm_bf16_nt_persistent",
+                         [c_p, c_p, c_p, c_p, c_l, c_i, c_i, c_i, c_l, c_l, c_p, native.c_z, c_p])
+
+
+def gemm_bf16_nt(a, b, out_dtype=torch.float32, out=None):
+    """C[M,N] = A[K,M]^T @ B[K,N]: both operands row-major with the REDUCED dimension as rows ("MN-major" for
+    tcgen05). This is the filter-gradient GEMM of a convolution / dense layer with its operands exactly as
+    the forward pass left them (activations [rows, Cin], output gradients [rows, Cout]) -- no transposed
+    copies. M % 8 == 0, N % 8 == 0, any K; row strides may exceed M / N (multiples of 8)."""
+    L = native.load()
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
+        raise TypeError("gemm_bf16_nt expects bf16 operands")
+    K, M = a.shape
+    K2, N = b.shape
+    if K != K2:
+        raise ValueError(f"K mismatch: {K} vs {K2}")
+    if a.stride(1) != 1 or b.stride(1) != 1:
+        raise ValueError("operands must be row-major")
+    c = out if out is not None else torch.empty((M, N), dtype=out_dtype, device=a.device)
+    f32 = c.data_ptr() if c.dtype == torch.float32 else None
+    b16 = c.data_ptr() if c.dtype == torch.bfloat16 else None
+    wsp = native.Workspace.current(a.device)
+    native.check(L.tfde_gemm_bf16_nt_persistent(a.data_ptr(), b.data_ptr(), f32, b16, c.stride(0), M, N, K,
+                                                a.stride(0), b.stride(0), wsp.ws.data_ptr(), wsp.ws_bytes,
+                                                native.stream_ptr()), "gemm_bf16_nt[persistent]")
+    return c

@@ -166,3 +166,23 @@ def test_resnet_bf16_activations_match_cpu_restatement():
     for a, b in zip(lg, lc):
         assert abs(a - b) < 0.25 * max(1.0, abs(b)), (lg, lc, lf)
     assert lg[-1] < lg[0]
+
+
+@pytest.mark.parametrize("K,M,N", [(4096, 64, 64), (1000, 576, 64), (6272, 256, 128), (777, 128, 512), (50176, 64, 256)])
+def test_gemm_nt_mn_major(K, M, N):
+    """tcgen05 GEMM with MN-major operands (A[K,M]^T B[K,N]) against fp32 matmul of the same bf16 inputs."""
+    from tfde_b200.ops import tensorcore
+    dev = _dev()
+    g = torch.Generator().manual_seed(K + M + N)
+    a = torch.randn(K, M, generator=g).to(BF).to(dev)
+    b = torch.randn(K, N, generator=g).to(BF).to(dev)
+    c = tensorcore.gemm_bf16_nt(a, b)
+    ref = a.float().t() @ b.float()
+    torch.cuda.synchronize()
+    err = (c - ref).abs().max().item()
+    assert err <= 2e-3 * (K ** 0.5) * 4, f"max err {err}"
+    # strided operand: columns [0, M) of a wider matrix (im2col with padded leading dimension)
+    wide = torch.randn(K, M + 8, generator=g).to(BF).to(dev)
+    c2 = tensorcore.gemm_bf16_nt(wide[:, :M], b)
+    ref2 = wide[:, :M].float().t() @ b.float()
+    assert (c2 - ref2).abs().max().item() <= 2e-3 * (K ** 0.5) * 4
