@@ -61,6 +61,7 @@ struct StatArgs {
 
 template <int MODE>
 __global__ void __launch_bounds__(256) colstats_bf16_kernel(const StatArgs a) {
+  TFDE_PDL_PROLOGUE();
   extern __shared__ float smem[];   // [2][rows][8*tpr]
   __shared__ int s_last;
   const int tpr = a.tpr, rows = 256 / tpr, cw = 8 * tpr;
@@ -76,32 +77,10 @@ __global__ void __launch_bounds__(256) colstats_bf16_kernel(const StatArgs a) {
   }
   const long stride = (long)gridDim.y * rows;
   long m = (long)blockIdx.y * rows + ty;
-  // two rows in flight per thread
-  for (; m + stride < a.M; m += 2 * stride) {
-    const uint4 r0 = ldg16(a.x + m * a.C + c0), r1 = ldg16(a.x + (m + stride) * a.C + c0);
-    uint4 d0, d1;
-    if (MODE == 1) { d0 = ldg16(a.dy + m * a.C + c0); d1 = ldg16(a.dy + (m + stride) * a.C + c0); }
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const F8 xv = unpack8(h ? r1 : r0);
-      if (MODE == 1) {
-        const F8 g = unpack8(h ? d1 : d0);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float gj = g.v[j];
-          if (a.relu && !(fmaf(xv.v[j], fs.v[j], fb.v[j]) > 0.f)) gj = 0.f;
-          s[j] += gj; q[j] = fmaf(gj, (xv.v[j] - mu.v[j]) * iv.v[j], q[j]);
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { s[j] += xv.v[j]; if (MODE == 0) q[j] = fmaf(xv.v[j], xv.v[j], q[j]); }
-      }
-    }
-  }
-  for (; m < a.M; m += stride) {
-    const F8 xv = unpack8(ldg16(a.x + m * a.C + c0));
+  auto accumulate = [&](const uint4 xr, const uint4 dr) {
+    const F8 xv = unpack8(xr);
     if (MODE == 1) {
-      const F8 g = unpack8(ldg16(a.dy + m * a.C + c0));
+      const F8 g = unpack8(dr);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         float gj = g.v[j];
@@ -112,7 +91,22 @@ __global__ void __launch_bounds__(256) colstats_bf16_kernel(const StatArgs a) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) { s[j] += xv.v[j]; if (MODE == 0) q[j] = fmaf(xv.v[j], xv.v[j], q[j]); }
     }
+  };
+  // four rows (64 or 128 bytes) in flight per thread: with two 256-thread blocks per SM that is the
+  // memory-level parallelism a pure streaming reduction needs
+  constexpr int U = 4;
+  for (; m + (U - 1) * stride < a.M; m += U * stride) {
+    uint4 xr[U], dr[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      xr[u] = ldg16(a.x + (m + u * stride) * a.C + c0);
+      dr[u] = (MODE == 1) ? ldg16(a.dy + (m + u * stride) * a.C + c0) : make_uint4(0u, 0u, 0u, 0u);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) accumulate(xr[u], dr[u]);
   }
+  for (; m < a.M; m += stride)
+    accumulate(ldg16(a.x + m * a.C + c0), (MODE == 1) ? ldg16(a.dy + m * a.C + c0) : make_uint4(0u, 0u, 0u, 0u));
   float* sa = smem; float* sb = smem + rows * cw;
 #pragma unroll
   for (int j = 0; j < 8; ++j) { sa[ty * cw + tx * 8 + j] = s[j]; sb[ty * cw + tx * 8 + j] = q[j]; }
@@ -129,12 +123,38 @@ __global__ void __launch_bounds__(256) colstats_bf16_kernel(const StatArgs a) {
   __syncthreads();
   if (!s_last) return;
   __threadfence();
+  // Finalise with the whole block: 256/cw thread groups each sum an interleaved subset of the row-block
+  // partials (4 loads in flight), then the groups are combined in fixed order through shared memory.
+  {
+    const int groups = 256 / cw, gi = threadIdx.x / cw, cl = threadIdx.x % cw;
+    double ds = 0.0, dq = 0.0;
+    const float* base = a.partials + (size_t)blockIdx.x * gridDim.y * 2 * cw;
+    unsigned rb = gi;
+    for (; rb + 3 * groups < gridDim.y; rb += 4 * groups) {
+      float vs[4], vq[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float* pp = base + (size_t)(rb + u * groups) * 2 * cw;
+        vs[u] = __ldcg(pp + cl); vq[u] = __ldcg(pp + cw + cl);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { ds += (double)vs[u]; dq += (double)vq[u]; }
+    }
+    for (; rb < gridDim.y; rb += groups) {
+      const float* pp = base + (size_t)rb * 2 * cw;
+      ds += (double)__ldcg(pp + cl); dq += (double)__ldcg(pp + cw + cl);
+    }
+    double* dsm = reinterpret_cast<double*>(smem);      // [2][256] doubles = 4 KB of the 16 KB
+    __syncthreads();
+    dsm[threadIdx.x] = ds; dsm[256 + threadIdx.x] = dq;
+    __syncthreads();
+  }
   for (int cl = threadIdx.x; cl < cw; cl += 256) {
     const int c = blockIdx.x * cw + cl;
     double ds = 0.0, dq = 0.0;
-    for (unsigned rb = 0; rb < gridDim.y; ++rb) {
-      const float* pp = a.partials + ((size_t)blockIdx.x * gridDim.y + rb) * 2 * cw;
-      ds += (double)__ldcg(pp + cl); dq += (double)__ldcg(pp + cw + cl);
+    {
+      const double* dsm = reinterpret_cast<const double*>(smem);
+      for (int gi = 0; gi < 256 / cw; ++gi) { ds += dsm[gi * cw + cl]; dq += dsm[256 + gi * cw + cl]; }
     }
     if (MODE == 0) {
       const double mean = ds / (double)a.M;
@@ -160,6 +180,7 @@ __global__ void __launch_bounds__(256) colstats_bf16_kernel(const StatArgs a) {
 __global__ void bn_apply_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long n8,
                                      int C, const float* __restrict__ scale, const float* __restrict__ shift,
                                      int relu) {
+  TFDE_PDL_PROLOGUE();
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long)gridDim.x * blockDim.x) {
     const int c = (int)((i << 3) % C);
     const F8 xv = unpack8(ldg16(x + (i << 3)));
@@ -181,6 +202,7 @@ __global__ void bn_bwd_apply_bf16_kernel(const __nv_bfloat16* __restrict__ x, co
                                          const float* __restrict__ gamma, const float* __restrict__ scale,
                                          const float* __restrict__ shift, const float* __restrict__ dbeta,
                                          const float* __restrict__ dgamma, int relu) {
+  TFDE_PDL_PROLOGUE();
   const float invM = 1.f / (float)M;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long)gridDim.x * blockDim.x) {
     const int c = (int)((i << 3) % C);
@@ -203,6 +225,7 @@ __global__ void bn_bwd_apply_bf16_kernel(const __nv_bfloat16* __restrict__ x, co
 // y = relu?(a + b)
 __global__ void add_bf16_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
                                 __nv_bfloat16* __restrict__ y, long n8, int relu) {
+  TFDE_PDL_PROLOGUE();
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long)gridDim.x * blockDim.x) {
     const F8 av = unpack8(ldg16(a + (i << 3))), bv = unpack8(ldg16(b + (i << 3)));
     F8 o;
@@ -216,6 +239,7 @@ __global__ void add_bf16_kernel(const __nv_bfloat16* __restrict__ a, const __nv_
 __global__ void relu_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ dy,
                                      const __nv_bfloat16* __restrict__ addend, __nv_bfloat16* __restrict__ dx,
                                      long n8) {
+  TFDE_PDL_PROLOGUE();
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long)gridDim.x * blockDim.x) {
     const F8 yv = unpack8(ldg16(y + (i << 3))), g = unpack8(ldg16(dy + (i << 3)));
     F8 o;
@@ -231,6 +255,7 @@ __global__ void relu_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ y, const 
 
 // fp32 -> bf16 and back (network boundary: image in, pooled features out)
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long n) {
+  TFDE_PDL_PROLOGUE();
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
     y[i] = __float2bfloat16(__ldg(x + i));
 }
@@ -242,6 +267,7 @@ struct PG { int Bn, H, W, C, PH, PW, sh, sw, pt, pl, Ho, Wo; };
 
 __global__ void maxpool_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                         uint8_t* __restrict__ idx, const PG g) {
+  TFDE_PDL_PROLOGUE();
   const int c8n = g.C >> 3;
   const long total = (long)g.Bn * g.Ho * g.Wo * c8n;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -277,6 +303,7 @@ __global__ void maxpool_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ x, __n
 // Gather formulation (no atomics): each input position sums the windows whose arg-max it is.
 __global__ void maxpool_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ idx,
                                         __nv_bfloat16* __restrict__ dx, const PG g) {
+  TFDE_PDL_PROLOGUE();
   const int c8n = g.C >> 3;
   const long total = (long)g.Bn * g.H * g.W * c8n;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -313,6 +340,7 @@ __global__ void maxpool_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ dy, co
 
 // Global average pool: bf16 [B, HW, C] -> fp32 [B, C]; backward fp32 [B, C] -> bf16 [B, HW, C].
 __global__ void gap_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ y, int Bn, int HW, int C) {
+  TFDE_PDL_PROLOGUE();
   const int c8n = C >> 3;
   const long total = (long)Bn * c8n;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -331,6 +359,7 @@ __global__ void gap_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* 
   }
 }
 __global__ void gap_bwd_bf16_kernel(const float* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int Bn, int HW, int C) {
+  TFDE_PDL_PROLOGUE();
   const int c8n = C >> 3;
   const long total = (long)Bn * HW * c8n;
   const float inv = 1.f / (float)HW;
@@ -351,6 +380,7 @@ struct CG { int B, H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout; };
 
 __global__ void im2col_b2b_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, const CG g,
                                   long M, int Kc, int ldo) {
+  TFDE_PDL_PROLOGUE();
   const int k8n = ldo >> 3;
   const long total = M * k8n;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -372,6 +402,7 @@ __global__ void im2col_b2b_kernel(const __nv_bfloat16* __restrict__ x, __nv_bflo
 
 __global__ void dgrad_gather_b2b_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ out,
                                         const CG g, long Min, int Kd, int ldo) {
+  TFDE_PDL_PROLOGUE();
   const int k8n = ldo >> 3;
   const long total = Min * k8n;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -410,7 +441,7 @@ inline bool stat_ok(int C) {
 inline int stat_row_blocks(long M, int C) {
   const int tpr = stat_tpr(C), rows = 256 / tpr, ctiles = C / (8 * tpr);
   long want = (M + (long)rows * 8 - 1) / ((long)rows * 8);     // >= 8 rows per thread
-  long cap = (148L * 6 + ctiles - 1) / ctiles;
+  long cap = (148L * 2 + ctiles - 1) / ctiles;                 // two blocks per SM; few partials => short finalise
   if (want > cap) want = cap;
   if (want < 1) want = 1;
   return (int)want;
@@ -424,7 +455,7 @@ int launch_stats(StatArgs& a, float* ws, size_t ws_floats, unsigned* counters, c
   if ((size_t)ctiles * rb * 2 * cw > ws_floats || ctiles > TFDE_MAX_COUNTERS) return TFDE_ERR_INVALID;
   a.partials = ws; a.counters = counters;
   const size_t smem = (size_t)2 * (256 / a.tpr) * cw * sizeof(float);     // = 16 KB
-  colstats_bf16_kernel<MODE><<<dim3(ctiles, rb), 256, smem, stream>>>(a);
+  tfde_launch(colstats_bf16_kernel<MODE>, dim3(ctiles, rb), dim3(256), smem, stream, a);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
@@ -452,7 +483,7 @@ TFDE_API int tfde_bn_fwd_train_bf16(const void* x, void* y, long M, int C, const
   const int rc = launch_stats<0>(a, ws, ws_floats, counters, stream);
   if (rc != 0) return rc;
   const long n8 = M * C / 8;
-  bn_apply_bf16_kernel<<<ew_blocks(n8), 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n8, C, scale,
+  tfde_launch(bn_apply_bf16_kernel, dim3(ew_blocks(n8)), dim3(256), 0, stream, (const __nv_bfloat16*)x, (__nv_bfloat16*)y, n8, C, scale,
                                                           shift, relu);
   TFDE_RETURN_LAUNCH_STATUS();
 }
@@ -462,7 +493,7 @@ TFDE_API int tfde_bn_apply_bf16(const void* x, void* y, long M, int C, const flo
                                 int relu, cudaStream_t stream) {
   if (C & 7) return TFDE_ERR_INVALID;
   const long n8 = M * C / 8;
-  bn_apply_bf16_kernel<<<ew_blocks(n8), 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n8, C, scale,
+  tfde_launch(bn_apply_bf16_kernel, dim3(ew_blocks(n8)), dim3(256), 0, stream, (const __nv_bfloat16*)x, (__nv_bfloat16*)y, n8, C, scale,
                                                           shift, relu);
   TFDE_RETURN_LAUNCH_STATUS();
 }
@@ -478,7 +509,7 @@ TFDE_API int tfde_bn_bwd_bf16(const void* x, const void* dy, void* dx, long M, i
   const int rc = launch_stats<1>(a, ws, ws_floats, counters, stream);
   if (rc != 0) return rc;
   const long n8 = M * C / 8;
-  bn_bwd_apply_bf16_kernel<<<ew_blocks(n8), 256, 0, stream>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
+  tfde_launch(bn_bwd_apply_bf16_kernel, dim3(ew_blocks(n8)), dim3(256), 0, stream, (const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
                                                               (__nv_bfloat16*)dx, n8, M, C, save_mean, save_invstd,
                                                               gamma, scale, shift, dbeta, dgamma, relu);
   TFDE_RETURN_LAUNCH_STATUS();
@@ -493,7 +524,7 @@ TFDE_API int tfde_colsum_bf16(const void* x, long M, int C, float* out, float* w
 
 TFDE_API int tfde_add_bf16(const void* a, const void* b, void* y, long n, int relu, cudaStream_t stream) {
   if (n & 7) return TFDE_ERR_INVALID;
-  add_bf16_kernel<<<ew_blocks(n / 8), 256, 0, stream>>>((const __nv_bfloat16*)a, (const __nv_bfloat16*)b,
+  tfde_launch(add_bf16_kernel, dim3(ew_blocks(n / 8)), dim3(256), 0, stream, (const __nv_bfloat16*)a, (const __nv_bfloat16*)b,
                                                         (__nv_bfloat16*)y, n / 8, relu);
   TFDE_RETURN_LAUNCH_STATUS();
 }
@@ -501,13 +532,13 @@ TFDE_API int tfde_add_bf16(const void* a, const void* b, void* y, long n, int re
 TFDE_API int tfde_relu_bwd_bf16(const void* y, const void* dy, const void* addend, void* dx, long n,
                                 cudaStream_t stream) {
   if (n & 7) return TFDE_ERR_INVALID;
-  relu_bwd_bf16_kernel<<<ew_blocks(n / 8), 256, 0, stream>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)dy,
+  tfde_launch(relu_bwd_bf16_kernel, dim3(ew_blocks(n / 8)), dim3(256), 0, stream, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy,
                                                              (const __nv_bfloat16*)addend, (__nv_bfloat16*)dx, n / 8);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
 TFDE_API int tfde_cast_f32_bf16(const float* x, void* y, long n, cudaStream_t stream) {
-  cast_f32_bf16_kernel<<<ew_blocks(n), 256, 0, stream>>>(x, (__nv_bfloat16*)y, n);
+  tfde_launch(cast_f32_bf16_kernel, dim3(ew_blocks(n)), dim3(256), 0, stream, x, (__nv_bfloat16*)y, n);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
@@ -515,7 +546,7 @@ TFDE_API int tfde_maxpool_fwd_bf16(const void* x, void* y, uint8_t* idx, int Bn,
                                    int sh, int sw, int pt, int pl, int Ho, int Wo, cudaStream_t stream) {
   if (C & 7) return TFDE_ERR_INVALID;
   PG g{Bn, H, W, C, PH, PW, sh, sw, pt, pl, Ho, Wo};
-  maxpool_fwd_bf16_kernel<<<ew_blocks((long)Bn * Ho * Wo * (C / 8)), 256, 0, stream>>>(
+  tfde_launch(maxpool_fwd_bf16_kernel, dim3(ew_blocks((long)Bn * Ho * Wo * (C / 8))), dim3(256), 0, stream, 
       (const __nv_bfloat16*)x, (__nv_bfloat16*)y, idx, g);
   TFDE_RETURN_LAUNCH_STATUS();
 }
@@ -523,19 +554,19 @@ TFDE_API int tfde_maxpool_bwd_bf16(const void* dy, const uint8_t* idx, void* dx,
                                    int PW, int sh, int sw, int pt, int pl, int Ho, int Wo, cudaStream_t stream) {
   if (C & 7) return TFDE_ERR_INVALID;
   PG g{Bn, H, W, C, PH, PW, sh, sw, pt, pl, Ho, Wo};
-  maxpool_bwd_bf16_kernel<<<ew_blocks((long)Bn * H * W * (C / 8)), 256, 0, stream>>>(
+  tfde_launch(maxpool_bwd_bf16_kernel, dim3(ew_blocks((long)Bn * H * W * (C / 8))), dim3(256), 0, stream, 
       (const __nv_bfloat16*)dy, idx, (__nv_bfloat16*)dx, g);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
 TFDE_API int tfde_gap_fwd_bf16(const void* x, float* y, int Bn, int HW, int C, cudaStream_t stream) {
   if (C & 7) return TFDE_ERR_INVALID;
-  gap_fwd_bf16_kernel<<<ew_blocks((long)Bn * (C / 8)), 256, 0, stream>>>((const __nv_bfloat16*)x, y, Bn, HW, C);
+  tfde_launch(gap_fwd_bf16_kernel, dim3(ew_blocks((long)Bn * (C / 8))), dim3(256), 0, stream, (const __nv_bfloat16*)x, y, Bn, HW, C);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 TFDE_API int tfde_gap_bwd_bf16(const float* dy, void* dx, int Bn, int HW, int C, cudaStream_t stream) {
   if (C & 7) return TFDE_ERR_INVALID;
-  gap_bwd_bf16_kernel<<<ew_blocks((long)Bn * HW * (C / 8)), 256, 0, stream>>>(dy, (__nv_bfloat16*)dx, Bn, HW, C);
+  tfde_launch(gap_bwd_bf16_kernel, dim3(ew_blocks((long)Bn * HW * (C / 8))), dim3(256), 0, stream, dy, (__nv_bfloat16*)dx, Bn, HW, C);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
@@ -544,7 +575,7 @@ TFDE_API int tfde_im2col_b2b(const void* x, void* out, int B, int H, int W, int 
   if ((ldo & 7) || (C & 7)) return TFDE_ERR_INVALID;
   const long M = (long)B * Ho * Wo;
   CG g{B, H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout};
-  im2col_b2b_kernel<<<ew_blocks(M * (ldo >> 3)), 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)out, g, M,
+  tfde_launch(im2col_b2b_kernel, dim3(ew_blocks(M * (ldo >> 3))), dim3(256), 0, stream, (const __nv_bfloat16*)x, (__nv_bfloat16*)out, g, M,
                                                                    KH * KW * C, ldo);
   TFDE_RETURN_LAUNCH_STATUS();
 }
@@ -553,7 +584,7 @@ TFDE_API int tfde_dgrad_gather_b2b(const void* dy, void* out, int B, int H, int 
   if ((ldo & 7) || (Cout & 7)) return TFDE_ERR_INVALID;
   const long Min = (long)B * H * W;
   CG g{B, H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout};
-  dgrad_gather_b2b_kernel<<<ew_blocks(Min * (ldo >> 3)), 256, 0, stream>>>((const __nv_bfloat16*)dy,
+  tfde_launch(dgrad_gather_b2b_kernel, dim3(ew_blocks(Min * (ldo >> 3))), dim3(256), 0, stream, (const __nv_bfloat16*)dy,
                                                                            (__nv_bfloat16*)out, g, Min, KH * KW * Cout, ldo);
   TFDE_RETURN_LAUNCH_STATUS();
 }

@@ -28,6 +28,7 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
 // out[m, k] (ld = ldo) ; one thread = 8 consecutive k of one row m
 __global__ void im2col_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, const CG g,
                                    long M, int Kc, int ldo) {
+  TFDE_PDL_PROLOGUE();
   const int k8n = ldo >> 3;
   const long total = M * k8n;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -73,6 +74,7 @@ __global__ void im2col_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* _
 // out[k, m] (ld = ldo >= M): 32x32 tiles through shared memory; reads coalesced along k, writes along m.
 __global__ void im2colT_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, const CG g,
                                     long M, int Kc, long ldo) {
+  TFDE_PDL_PROLOGUE();
   __shared__ float tile[32][33];
   const long m0 = (long)blockIdx.x * 32;
   const int k0 = blockIdx.y * 32;
@@ -102,6 +104,7 @@ __global__ void im2colT_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* 
 // out[(b,h,w), (kh,kw,co)] = dy[b, (h+pt-kh)/sh, (w+pl-kw)/sw, co] * (mask > 0); one thread = 8 k
 __global__ void dgrad_gather_bf16_kernel(const float* __restrict__ dy, const float* __restrict__ mask,
                                          __nv_bfloat16* __restrict__ out, const CG g, long Min, int Kd, int ldo) {
+  TFDE_PDL_PROLOGUE();
   const int k8n = ldo >> 3;
   const long total = Min * k8n;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -154,6 +157,7 @@ __global__ void dgrad_gather_bf16_kernel(const float* __restrict__ dy, const flo
 // out[ci, (kh,kw,co)] = w[kh,kw,ci,co]  (ld = ldo), zero padded
 __global__ void wrot_bf16_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int KHW, int Cin,
                                  int Cout, int ldo) {
+  TFDE_PDL_PROLOGUE();
   const long total = (long)Cin * ldo;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int k = (int)(i % ldo); const int ci = (int)(i / ldo);
@@ -169,6 +173,7 @@ __global__ void wrot_bf16_kernel(const float* __restrict__ w, __nv_bfloat16* __r
 // y[c, r] (ld = ldy >= R, zero padded) = bf16(x[r, c] * (mask > 0)) for fp32 x[R, C]
 __global__ void cast_transpose_pad_bf16_kernel(const float* __restrict__ x, const float* __restrict__ mask,
                                                __nv_bfloat16* __restrict__ y, long R, int C, long ldy) {
+  TFDE_PDL_PROLOGUE();
   __shared__ float tile[32][33];
   const int c0 = blockIdx.x * 32; const long r0 = (long)blockIdx.y * 32;
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
@@ -204,7 +209,7 @@ TFDE_API int tfde_im2col_bf16(const float* x, void* out, int B, int H, int W, in
                               int sh, int sw, int pt, int pl, int Cout, int ldo, cudaStream_t stream) {
   if (ldo & 7) return TFDE_ERR_INVALID;
   const long M = (long)B * Ho * Wo;
-  im2col_bf16_kernel<<<ew_blocks(M * (ldo >> 3)), 256, 0, stream>>>(x, (__nv_bfloat16*)out, mk(B, H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout), M, KH * KW * C, ldo);
+  tfde_launch(im2col_bf16_kernel, dim3(ew_blocks(M * (ldo >> 3))), dim3(256), 0, stream, x, (__nv_bfloat16*)out, mk(B, H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout), M, KH * KW * C, ldo);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 TFDE_API int tfde_im2colT_bf16(const float* x, void* out, int B, int H, int W, int C, int KH, int KW, int Ho, int Wo,
@@ -213,7 +218,7 @@ TFDE_API int tfde_im2colT_bf16(const float* x, void* out, int B, int H, int W, i
   const int Kc = KH * KW * C;
   if ((ldo & 7) || ldo < M) return TFDE_ERR_INVALID;
   dim3 grid((unsigned)((ldo + 31) / 32), (Kc + 31) / 32), block(32, 8);
-  im2colT_bf16_kernel<<<grid, block, 0, stream>>>(x, (__nv_bfloat16*)out, mk(B, H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout), M, Kc, ldo);
+  tfde_launch(im2colT_bf16_kernel, dim3(grid), dim3(block), 0, stream, x, (__nv_bfloat16*)out, mk(B, H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout), M, Kc, ldo);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 TFDE_API int tfde_dgrad_gather_bf16(const float* dy, const float* mask, void* out, int B, int H, int W, int C, int KH,
@@ -221,19 +226,19 @@ TFDE_API int tfde_dgrad_gather_bf16(const float* dy, const float* mask, void* ou
                                     cudaStream_t stream) {
   if (ldo & 7) return TFDE_ERR_INVALID;
   const long Min = (long)B * H * W;
-  dgrad_gather_bf16_kernel<<<ew_blocks(Min * (ldo >> 3)), 256, 0, stream>>>(dy, mask, (__nv_bfloat16*)out, mk(B, H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout), Min, KH * KW * Cout, ldo);
+  tfde_launch(dgrad_gather_bf16_kernel, dim3(ew_blocks(Min * (ldo >> 3))), dim3(256), 0, stream, dy, mask, (__nv_bfloat16*)out, mk(B, H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout), Min, KH * KW * Cout, ldo);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 TFDE_API int tfde_wrot_bf16(const float* w, void* out, int KH, int KW, int Cin, int Cout, int ldo, cudaStream_t stream) {
   if (ldo & 7) return TFDE_ERR_INVALID;
-  wrot_bf16_kernel<<<ew_blocks((long)Cin * ldo), 256, 0, stream>>>(w, (__nv_bfloat16*)out, KH * KW, Cin, Cout, ldo);
+  tfde_launch(wrot_bf16_kernel, dim3(ew_blocks((long)Cin * ldo)), dim3(256), 0, stream, w, (__nv_bfloat16*)out, KH * KW, Cin, Cout, ldo);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 TFDE_API int tfde_cast_transpose_pad_bf16(const float* x, const float* mask, void* y, long R, int C, long ldy,
                                           cudaStream_t stream) {
   if ((ldy & 7) || ldy < R) return TFDE_ERR_INVALID;
   dim3 grid((C + 31) / 32, (unsigned)((ldy + 31) / 32)), block(32, 8);
-  cast_transpose_pad_bf16_kernel<<<grid, block, 0, stream>>>(x, mask, (__nv_bfloat16*)y, R, C, ldy);
+  tfde_launch(cast_transpose_pad_bf16_kernel, dim3(grid), dim3(block), 0, stream, x, mask, (__nv_bfloat16*)y, R, C, ldy);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
@@ -246,6 +251,7 @@ namespace {
 __global__ void __launch_bounds__(256)
 transpose_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long R, int C, long ldx,
                       long ldy) {
+  TFDE_PDL_PROLOGUE();
   __shared__ __nv_bfloat16 tile[64][66];
   const long r0 = (long)blockIdx.x * 64;
   const int c0 = blockIdx.y * 64;
@@ -278,6 +284,6 @@ transpose_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __rest
 TFDE_API int tfde_transpose_bf16(const void* x, void* y, long R, int C, long ldx, long ldy, cudaStream_t stream) {
   if ((ldx & 1) || (ldy & 1) || ldy < R) return TFDE_ERR_INVALID;
   dim3 grid((unsigned)((ldy + 63) / 64), (C + 63) / 64);
-  transpose_bf16_kernel<<<grid, 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, R, C, ldx, ldy);
+  tfde_launch(transpose_bf16_kernel, dim3(grid), dim3(256), 0, stream, (const __nv_bfloat16*)x, (__nv_bfloat16*)y, R, C, ldx, ldy);
   TFDE_RETURN_LAUNCH_STATUS();
 }

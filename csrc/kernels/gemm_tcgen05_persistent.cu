@@ -108,6 +108,10 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
   __shared__ __align__(8) uint64_t tmem_empty[2];
   __shared__ uint32_t tmem_base_smem;
 
+  // Programmatic dependent launch: let the next kernel of the stream get scheduled now; our own set-up
+  // (barriers, TMEM allocation, tensor-map prefetch) overlaps the tail of the previous kernel, and every
+  // thread waits for that kernel's memory before the first global access (pdl_wait below).
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_k = (K + P_BK - 1) / P_BK;
   // work item = (output tile, k split); split z covers k-blocks [z*kb_per, min(num_k, (z+1)*kb_per)).
@@ -132,6 +136,7 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_d = tmem_base_smem;
+  pdl_wait();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -267,7 +272,38 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __restrict__ c_f32,
                                      __nv_bfloat16* __restrict__ c_bf16, long ldc, const float* __restrict__ bias,
                                      int relu, int M, int N, int splits) {
+  TFDE_PDL_PROLOGUE();
   const long total = (long)M * N;
+  if ((N & 3) == 0 && (ldc & 3) == 0) {
+    // 16-byte path: 4 consecutive columns per thread, 8 partials in flight
+    const long total4 = total >> 2;
+    const float4* ws4 = reinterpret_cast<const float4*>(ws);
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (long)gridDim.x * blockDim.x) {
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int z0 = 0; z0 < splits; z0 += 8) {
+        float4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          v[u] = (z0 + u < splits) ? __ldcg(ws4 + (size_t)(z0 + u) * total4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+      }
+      const int col = (int)((i << 2) % N);
+      const long row = (i << 2) / N;
+      if (bias != nullptr) {
+        const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + col));
+        s.x += bv.x; s.y += bv.y; s.z += bv.z; s.w += bv.w;
+      }
+      if (relu) { s.x = fmaxf(s.x, 0.f); s.y = fmaxf(s.y, 0.f); s.z = fmaxf(s.z, 0.f); s.w = fmaxf(s.w, 0.f); }
+      if (c_f32 != nullptr) *reinterpret_cast<float4*>(c_f32 + row * ldc + col) = s;
+      if (c_bf16 != nullptr) {
+        __nv_bfloat162 p0 = __floats2bfloat162_rn(s.x, s.y), p1 = __floats2bfloat162_rn(s.z, s.w);
+        uint2 o; o.x = *reinterpret_cast<uint32_t*>(&p0); o.y = *reinterpret_cast<uint32_t*>(&p1);
+        *reinterpret_cast<uint2*>(c_bf16 + row * ldc + col) = o;
+      }
+    }
+    return;
+  }
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     float s = 0.f;
     for (int z0 = 0; z0 < splits; z0 += 4) {
@@ -363,11 +399,14 @@ int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, 
   }
   const int items = tiles * splits;
   const int grid = items < 148 ? items : 148;
-  gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ><<<grid, P_THREADS, smem, stream>>>(ta, tb, ep, K, tiles_m, tiles_n, splits, ws);
+  tfde_launch(gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ>, dim3(grid), dim3(P_THREADS), smem, stream, ta, tb, ep, K, tiles_m,
+              tiles_n, splits, ws);
   if (splits > 1) {
-    long blocks = ((long)M * N + 255) / 256;
+    long blocks = ((long)M * N / 4 + 255) / 256;
     if (blocks > 148L * 8) blocks = 148L * 8;
-    splitk_reduce_kernel<<<(int)blocks, 256, 0, stream>>>(ws, ep.c_f32, ep.c_bf16, ep.ldc, ep.bias, ep.relu, M, N, splits);
+    if (blocks < 1) blocks = 1;
+    tfde_launch(splitk_reduce_kernel, dim3((int)blocks), dim3(256), 0, stream, (const float*)ws, ep.c_f32, ep.c_bf16, ep.ldc,
+                ep.bias, ep.relu, M, N, splits);
   }
   TFDE_RETURN_LAUNCH_STATUS();
 }

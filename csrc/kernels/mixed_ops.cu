@@ -9,6 +9,7 @@ namespace {
 // y = bf16(x * (mask > 0)), 4 elements per thread where alignment allows
 __global__ void cast_bf16_masked_kernel(const float* __restrict__ x, const float* __restrict__ mask,
                                         __nv_bfloat16* __restrict__ y, long n) {
+  TFDE_PDL_PROLOGUE();
   const long n4 = n >> 2;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
     float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
@@ -34,6 +35,7 @@ __global__ void cast_bf16_masked_kernel(const float* __restrict__ x, const float
 __global__ void __launch_bounds__(256)
 colsum_masked_kernel(const float* __restrict__ x, const float* __restrict__ mask, float* __restrict__ out,
                      long R, int C, float* __restrict__ partials, unsigned* __restrict__ counters) {
+  TFDE_PDL_PROLOGUE();
   __shared__ float s[8][33];
   __shared__ int s_last;
   const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
@@ -80,7 +82,7 @@ TFDE_API int tfde_cast_bf16_masked(const float* x, const float* mask, void* y, l
   long grid = (n / 4 + 255) / 256;
   if (grid > 148L * 8) grid = 148L * 8;
   if (grid < 1) grid = 1;
-  cast_bf16_masked_kernel<<<(int)grid, 256, 0, stream>>>(x, mask, (__nv_bfloat16*)y, n);
+  tfde_launch(cast_bf16_masked_kernel, dim3((int)grid), dim3(256), 0, stream, x, mask, (__nv_bfloat16*)y, n);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
@@ -94,6 +96,6 @@ TFDE_API int tfde_colsum_masked(const float* x, const float* mask, float* out, l
   if (rb > cap) rb = cap;
   if (rb > 128) rb = 128;
   if (rb < 1 || partials == nullptr || counters == nullptr) rb = 1;
-  colsum_masked_kernel<<<dim3(ct, (unsigned)rb), 256, 0, stream>>>(x, mask, out, R, C, partials, counters);
+  tfde_launch(colsum_masked_kernel, dim3(ct, (unsigned)rb), dim3(256), 0, stream, x, mask, out, R, C, partials, counters);
   TFDE_RETURN_LAUNCH_STATUS();
 }

@@ -23,6 +23,7 @@ import torch
 from .. import ops
 
 _ACTS = (None, "linear", "relu", "softmax")
+_CACHE_IM2COL = __import__("os").environ.get("TFDE_CACHE_IM2COL", "1") == "1"
 
 
 def _pair(v) -> Tuple[int, int]:
@@ -248,8 +249,13 @@ class Conv2D(Layer):
         if self._a16:
             from ..ops import act16
             y = self.buf("y16", (b,) + self.out_shape, torch.bfloat16)
+            # the gathered im2col operand is kept for the filter-gradient GEMM (HBM is plentiful, bandwidth is not)
+            ashape = act16.a_operand_shape(x.shape, self.kernel.shape, self.strides, self.out_shape[0],
+                                           self.out_shape[1], x.dtype == torch.bfloat16)
+            self._a_cache = (self.buf("a16", ashape, torch.bfloat16)
+                             if ashape is not None and training and _CACHE_IM2COL else None)
             act16.conv2d_fwd(x, self.kernel.value, self.bias.value if self.bias else None, self.strides,
-                             self.pads, out=y)
+                             self.pads, out=y, a_cache=self._a_cache)
             self._y = y
             return y
         y = self.buf("y", (b,) + self.out_shape)
@@ -270,7 +276,7 @@ class Conv2D(Layer):
             dx = self.buf("dx16", self._x.shape, torch.bfloat16) if self.need_dx else None
             act16.conv2d_bwd(self._x, self.kernel.value, dy, self.strides, self.pads, self.need_dx, self.use_bias,
                              getattr(self, "bias_grad_zero", False), out_dx=dx, out_dw=self.kernel.grad,
-                             out_db=self.bias.grad if self.bias else None)
+                             out_db=self.bias.grad if self.bias else None, a_cache=getattr(self, "_a_cache", None))
             if dx is not None and self._x.dtype != torch.bfloat16:
                 dx = self.buf("dx", self._x.shape).copy_(dx)
             return dx

@@ -283,8 +283,19 @@ def _bf(t):
     return t.to(BF).to(torch.float32)
 
 
-def _a_operand(x, w_shape, stride, pads, ho, wo, tag):
-    """K-major bf16 A operand [M, kp] of the forward / filter-gradient GEMM."""
+def a_operand_shape(x_shape, w_shape, stride, ho, wo, x_is_bf16=True):
+    """(M, kp) of the gathered A operand, or None when the activation itself is the operand (1x1, stride 1)."""
+    b, h, wd, c = x_shape
+    kh, kw = w_shape[0], w_shape[1]
+    if x_is_bf16 and kh == 1 and kw == 1 and tuple(stride) == (1, 1):
+        return None
+    return (b * ho * wo, _r8(kh * kw * c))
+
+
+def _a_operand(x, w_shape, stride, pads, ho, wo, tag, cache=None, reuse=False):
+    """K-major bf16 A operand [M, kp] of the forward / filter-gradient GEMM. ``cache``: a caller-owned
+    [M, kp] bf16 buffer to gather into (forward) or, with ``reuse``, to take as is (backward: the im2col
+    matrix of the forward pass is kept instead of being gathered a second time -- memory for time)."""
     L = native.load()
     b, h, wd, c = x.shape
     kh, kw, _, cout = w_shape
@@ -294,15 +305,19 @@ def _a_operand(x, w_shape, stride, pads, ho, wo, tag):
     if x.dtype == BF:
         if kh == 1 and kw == 1 and tuple(stride) == (1, 1):
             return x.reshape(M, c), kp                 # the activation IS the operand
-        a = _scratch(x.device, tag, M * kp).view(M, kp)
+        if cache is not None and reuse:
+            return cache, kp
+        a = cache if cache is not None else _scratch(x.device, tag, M * kp).view(M, kp)
         native.check(L.tfde_im2col_b2b(x.data_ptr(), a.data_ptr(), *g, kp, native.stream_ptr()), "im2col_b2b")
         return a, kp
-    a = _scratch(x.device, tag, M * kp).view(M, kp)
+    if cache is not None and reuse:
+        return cache, kp
+    a = cache if cache is not None else _scratch(x.device, tag, M * kp).view(M, kp)
     native.check(L.tfde_im2col_bf16(x.data_ptr(), a.data_ptr(), *g, kp, native.stream_ptr()), "im2col_bf16")
     return a, kp
 
 
-def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None):
+def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None, a_cache=None):
     """x: bf16 NHWC (or the fp32 network input); w: fp32 HWIO; returns bf16 NHWC."""
     b, h, wd, c = x.shape
     kh, kw, _, cout = w.shape
@@ -316,7 +331,7 @@ def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None):
         return y
     L = native.load()
     M, kc = b * ho * wo, kh * kw * c
-    a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "A")
+    a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "A", cache=a_cache)
     wt = _scratch(x.device, "B", cout * kp).view(cout, kp)
     native.check(L.tfde_cast_transpose_pad_bf16(w.data_ptr(), None, wt.data_ptr(), kc, cout, kp, native.stream_ptr()),
                  "cast_transpose_pad_bf16")
@@ -326,7 +341,7 @@ def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None):
 
 
 def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bias=True, bias_grad_zero=False,
-               out_dx=None, out_dw=None, out_db=None):
+               out_dx=None, out_dw=None, out_db=None, a_cache=None):
     """dy: bf16. Returns (dx bf16 | None, dw fp32, db fp32 | None).
     ``bias_grad_zero``: the convolution feeds a training-mode batch-norm, whose input gradient sums to zero
     over every channel (batch-norm is invariant to a per-channel shift of its input), so the bias gradient
@@ -352,7 +367,7 @@ def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bia
     M, kc, min_, kd = b * ho * wo, kh * kw * c, b * h * wd, kh * kw * cout
     dy2 = dy.reshape(M, cout)
     # filter gradient: dW[kc, cout] = A^T[kc, M] . dy^T[cout, M]^T (both K-major after a bf16 transpose)
-    a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "C")
+    a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "C", cache=a_cache, reuse=a_cache is not None)
     dw = out_dw if out_dw is not None else torch.empty(tuple(w.shape), dtype=torch.float32, device=dev)
     if _WGRAD_NT and kc % 8 == 0:
         # operands as the forward pass left them: A[M, kc] and dy[M, cout], reduced over rows -> the tcgen05
