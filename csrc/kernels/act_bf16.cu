@@ -59,12 +59,16 @@ struct StatArgs {
   float* colsum;
 };
 
+// One fat block per SM (512 threads): the per-block partials are few (<= 148 per channel tile), so the
+// last block's finalise is a couple of load rounds instead of the dominant tail of a 5-microsecond kernel.
+constexpr int ST = 512;
+
 template <int MODE>
-__global__ void __launch_bounds__(256) colstats_bf16_kernel(const StatArgs a) {
+__global__ void __launch_bounds__(ST) colstats_bf16_kernel(const StatArgs a) {
   TFDE_PDL_PROLOGUE();
   extern __shared__ float smem[];   // [2][rows][8*tpr]
   __shared__ int s_last;
-  const int tpr = a.tpr, rows = 256 / tpr, cw = 8 * tpr;
+  const int tpr = a.tpr, rows = ST / tpr, cw = 8 * tpr;
   const int tx = threadIdx.x % tpr, ty = threadIdx.x / tpr;
   const int c0 = blockIdx.x * cw + tx * 8;
   float s[8], q[8];
@@ -112,7 +116,7 @@ __global__ void __launch_bounds__(256) colstats_bf16_kernel(const StatArgs a) {
   for (int j = 0; j < 8; ++j) { sa[ty * cw + tx * 8 + j] = s[j]; sb[ty * cw + tx * 8 + j] = q[j]; }
   __syncthreads();
   float* part = a.partials + ((size_t)blockIdx.x * gridDim.y + blockIdx.y) * 2 * cw;
-  for (int c = threadIdx.x; c < cw; c += 256) {
+  for (int c = threadIdx.x; c < cw; c += ST) {
     float ts = 0.f, tq = 0.f;
     for (int r = 0; r < rows; ++r) { ts += sa[r * cw + c]; tq += sb[r * cw + c]; }
     __stcg(part + c, ts); __stcg(part + cw + c, tq);
@@ -126,7 +130,7 @@ __global__ void __launch_bounds__(256) colstats_bf16_kernel(const StatArgs a) {
   // Finalise with the whole block: 256/cw thread groups each sum an interleaved subset of the row-block
   // partials (4 loads in flight), then the groups are combined in fixed order through shared memory.
   {
-    const int groups = 256 / cw, gi = threadIdx.x / cw, cl = threadIdx.x % cw;
+    const int groups = ST / cw, gi = threadIdx.x / cw, cl = threadIdx.x % cw;
     double ds = 0.0, dq = 0.0;
     const float* base = a.partials + (size_t)blockIdx.x * gridDim.y * 2 * cw;
     unsigned rb = gi;
@@ -144,17 +148,17 @@ __global__ void __launch_bounds__(256) colstats_bf16_kernel(const StatArgs a) {
       const float* pp = base + (size_t)rb * 2 * cw;
       ds += (double)__ldcg(pp + cl); dq += (double)__ldcg(pp + cw + cl);
     }
-    double* dsm = reinterpret_cast<double*>(smem);      // [2][256] doubles = 4 KB of the 16 KB
+    double* dsm = reinterpret_cast<double*>(smem);      // [2][ST] doubles = 8 KB of the 32 KB
     __syncthreads();
-    dsm[threadIdx.x] = ds; dsm[256 + threadIdx.x] = dq;
+    dsm[threadIdx.x] = ds; dsm[ST + threadIdx.x] = dq;
     __syncthreads();
   }
-  for (int cl = threadIdx.x; cl < cw; cl += 256) {
+  for (int cl = threadIdx.x; cl < cw; cl += ST) {
     const int c = blockIdx.x * cw + cl;
     double ds = 0.0, dq = 0.0;
     {
       const double* dsm = reinterpret_cast<const double*>(smem);
-      for (int gi = 0; gi < 256 / cw; ++gi) { ds += dsm[gi * cw + cl]; dq += dsm[256 + gi * cw + cl]; }
+      for (int gi = 0; gi < ST / cw; ++gi) { ds += dsm[gi * cw + cl]; dq += dsm[ST + gi * cw + cl]; }
     }
     if (MODE == 0) {
       const double mean = ds / (double)a.M;
@@ -436,12 +440,12 @@ inline int stat_tpr(int C) { int t = C / 8; return t > 32 ? 32 : t; }
 inline bool stat_ok(int C) {
   if (C < 8 || (C & 7)) return false;
   const int t = stat_tpr(C);
-  return (256 % t) == 0 && (C % (8 * t)) == 0;
+  return (ST % t) == 0 && (C % (8 * t)) == 0;
 }
 inline int stat_row_blocks(long M, int C) {
-  const int tpr = stat_tpr(C), rows = 256 / tpr, ctiles = C / (8 * tpr);
+  const int tpr = stat_tpr(C), rows = ST / tpr, ctiles = C / (8 * tpr);
   long want = (M + (long)rows * 8 - 1) / ((long)rows * 8);     // >= 8 rows per thread
-  long cap = (148L * 2 + ctiles - 1) / ctiles;                 // two blocks per SM; few partials => short finalise
+  long cap = (148L + ctiles - 1) / ctiles;                     // one 512-thread block per SM
   if (want > cap) want = cap;
   if (want < 1) want = 1;
   return (int)want;
@@ -454,8 +458,8 @@ int launch_stats(StatArgs& a, float* ws, size_t ws_floats, unsigned* counters, c
   const int cw = 8 * a.tpr, ctiles = a.C / cw, rb = stat_row_blocks(a.M, a.C);
   if ((size_t)ctiles * rb * 2 * cw > ws_floats || ctiles > TFDE_MAX_COUNTERS) return TFDE_ERR_INVALID;
   a.partials = ws; a.counters = counters;
-  const size_t smem = (size_t)2 * (256 / a.tpr) * cw * sizeof(float);     // = 16 KB
-  tfde_launch(colstats_bf16_kernel<MODE>, dim3(ctiles, rb), dim3(256), smem, stream, a);
+  const size_t smem = (size_t)2 * (ST / a.tpr) * cw * sizeof(float);      // = 32 KB
+  tfde_launch(colstats_bf16_kernel<MODE>, dim3(ctiles, rb), dim3(ST), smem, stream, a);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 

@@ -24,6 +24,7 @@ from .. import ops
 
 _ACTS = (None, "linear", "relu", "softmax")
 _CACHE_IM2COL = __import__("os").environ.get("TFDE_CACHE_IM2COL", "1") == "1"
+_FORK_CONV_WGRAD = __import__("os").environ.get("TFDE_FORK_CONV_WGRAD", "1") == "1"
 
 
 def _pair(v) -> Tuple[int, int]:
@@ -276,7 +277,8 @@ class Conv2D(Layer):
             dx = self.buf("dx16", self._x.shape, torch.bfloat16) if self.need_dx else None
             act16.conv2d_bwd(self._x, self.kernel.value, dy, self.strides, self.pads, self.need_dx, self.use_bias,
                              getattr(self, "bias_grad_zero", False), out_dx=dx, out_dw=self.kernel.grad,
-                             out_db=self.bias.grad if self.bias else None, a_cache=getattr(self, "_a_cache", None))
+                             out_db=self.bias.grad if self.bias else None, a_cache=getattr(self, "_a_cache", None),
+                             side_stream=(self.model.fork_stream() if dy.is_cuda and _FORK_CONV_WGRAD else None))
             if dx is not None and self._x.dtype != torch.bfloat16:
                 dx = self.buf("dx", self._x.shape).copy_(dx)
             return dx

@@ -341,7 +341,7 @@ def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None, a_ca
 
 
 def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bias=True, bias_grad_zero=False,
-               out_dx=None, out_dw=None, out_db=None, a_cache=None):
+               out_dx=None, out_dw=None, out_db=None, a_cache=None, side_stream=None):
     """dy: bf16. Returns (dx bf16 | None, dw fp32, db fp32 | None).
     ``bias_grad_zero``: the convolution feeds a training-mode batch-norm, whose input gradient sums to zero
     over every channel (batch-norm is invariant to a per-channel shift of its input), so the bias gradient
@@ -372,7 +372,16 @@ def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bia
     if _WGRAD_NT and kc % 8 == 0:
         # operands as the forward pass left them: A[M, kc] and dy[M, cout], reduced over rows -> the tcgen05
         # GEMM reads them MN-major, no transposed copies
-        tensorcore.gemm_bf16_nt(a[:, :kc] if kp != kc else a, dy2, out=dw.view(kc, cout))
+        a_nt = a[:, :kc] if kp != kc else a
+        owns_a = a_cache is not None or a.data_ptr() == x.data_ptr()     # not in the shared scratch pool
+        if side_stream is not None and need_dx and owns_a:
+            # only the optimizer consumes dW: fork it so it overlaps the data-gradient chain of this layer and
+            # the batch-norm backward of the previous one (joined before the optimizer / all-reduce)
+            side_stream.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side_stream):
+                tensorcore.gemm_bf16_nt(a_nt, dy2, out=dw.view(kc, cout))
+        else:
+            tensorcore.gemm_bf16_nt(a_nt, dy2, out=dw.view(kc, cout))
     else:
         at = _scratch(dev, "A", kc * M).view(kc, M)
         native.check(L.tfde_transpose_bf16(a.data_ptr(), at.data_ptr(), M, kc, kp, M, native.stream_ptr()),
