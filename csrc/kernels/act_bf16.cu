@@ -429,6 +429,25 @@ __global__ void dgrad_gather_b2b_kernel(const __nv_bfloat16* __restrict__ dy, __
   }
 }
 
+// Data gradient of a strided 1x1 convolution: the GEMM runs on the compact [B*Ho*Wo, Cin] problem and this
+// kernel spreads its rows over the input grid (positions the stride skipped get zero) -- instead of a
+// [B*H*W, Cout] gathered operand that is 1 - 1/(sh*sw) zeros and a GEMM sh*sw times too large.
+__global__ void strided_scatter_b2b_kernel(const __nv_bfloat16* __restrict__ g, __nv_bfloat16* __restrict__ dx,
+                                           int Bn, int H, int W, int C, int Ho, int Wo, int sh, int sw) {
+  TFDE_PDL_PROLOGUE();
+  const int c8n = C >> 3;
+  const long total = (long)Bn * H * W * c8n;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % c8n) * 8; long t = i / c8n;
+    const int w = (int)(t % W); t /= W;
+    const int h = (int)(t % H); const long b = t / H;
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    const int oh = h / sh, ow = w / sw;
+    if (oh * sh == h && ow * sw == w && oh < Ho && ow < Wo) o = ldg16(g + ((b * Ho + oh) * Wo + ow) * (long)C + c);
+    *reinterpret_cast<uint4*>(dx + (i << 3)) = o;
+  }
+}
+
 inline int ew_blocks(long work) {
   long b = (work + 255) / 256;
   if (b > 148L * 16) b = 148L * 16;
@@ -571,6 +590,14 @@ TFDE_API int tfde_gap_fwd_bf16(const void* x, float* y, int Bn, int HW, int C, c
 TFDE_API int tfde_gap_bwd_bf16(const float* dy, void* dx, int Bn, int HW, int C, cudaStream_t stream) {
   if (C & 7) return TFDE_ERR_INVALID;
   tfde_launch(gap_bwd_bf16_kernel, dim3(ew_blocks((long)Bn * HW * (C / 8))), dim3(256), 0, stream, dy, (__nv_bfloat16*)dx, Bn, HW, C);
+  TFDE_RETURN_LAUNCH_STATUS();
+}
+
+TFDE_API int tfde_strided_scatter_b2b(const void* g, void* dx, int Bn, int H, int W, int C, int Ho, int Wo, int sh,
+                                      int sw, cudaStream_t stream) {
+  if (C & 7) return TFDE_ERR_INVALID;
+  tfde_launch(strided_scatter_b2b_kernel, dim3(ew_blocks((long)Bn * H * W * (C / 8))), dim3(256), 0, stream,
+              (const __nv_bfloat16*)g, (__nv_bfloat16*)dx, Bn, H, W, C, Ho, Wo, sh, sw);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 

@@ -322,6 +322,53 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __rest
   }
 }
 
+// Small outputs with many splits (the 1x1 filter gradients: 64x256 outputs, 64 partials) are latency-bound in
+// the kernel above: few threads, each walking all partials. Here ZP adjacent lanes share one 4-column group,
+// each sums every ZP-th partial with all loads in flight, and a fixed xor-shuffle tree combines them
+// (fixed order => still deterministic). Requires N % 4 == 0 and ldc % 4 == 0.
+template <int ZP>
+__global__ void splitk_reduce_zpar_kernel(const float* __restrict__ ws, float* __restrict__ c_f32,
+                                          __nv_bfloat16* __restrict__ c_bf16, long ldc, const float* __restrict__ bias,
+                                          int relu, int M, int N, int splits) {
+  TFDE_PDL_PROLOGUE();
+  const long total4 = ((long)M * N) >> 2;
+  const float4* ws4 = reinterpret_cast<const float4*>(ws);
+  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long i = tid / ZP;
+  const int zl = (int)(tid % ZP);
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (i < total4) {
+    for (int z0 = zl; z0 < splits; z0 += 8 * ZP) {
+      float4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        v[u] = (z0 + u * ZP < splits) ? __ldcg(ws4 + (size_t)(z0 + u * ZP) * total4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+    }
+  }
+#pragma unroll
+  for (int off = ZP / 2; off >= 1; off >>= 1) {
+    s.x += __shfl_xor_sync(0xffffffffu, s.x, off); s.y += __shfl_xor_sync(0xffffffffu, s.y, off);
+    s.z += __shfl_xor_sync(0xffffffffu, s.z, off); s.w += __shfl_xor_sync(0xffffffffu, s.w, off);
+  }
+  if (i < total4 && zl == 0) {
+    const int col = (int)((i << 2) % N);
+    const long row = (i << 2) / N;
+    if (bias != nullptr) {
+      const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + col));
+      s.x += bv.x; s.y += bv.y; s.z += bv.z; s.w += bv.w;
+    }
+    if (relu) { s.x = fmaxf(s.x, 0.f); s.y = fmaxf(s.y, 0.f); s.z = fmaxf(s.z, 0.f); s.w = fmaxf(s.w, 0.f); }
+    if (c_f32 != nullptr) *reinterpret_cast<float4*>(c_f32 + row * ldc + col) = s;
+    if (c_bf16 != nullptr) {
+      __nv_bfloat162 p0 = __floats2bfloat162_rn(s.x, s.y), p1 = __floats2bfloat162_rn(s.z, s.w);
+      uint2 o; o.x = *reinterpret_cast<uint32_t*>(&p0); o.y = *reinterpret_cast<uint32_t*>(&p1);
+      *reinterpret_cast<uint2*>(c_bf16 + row * ldc + col) = o;
+    }
+  }
+}
+
 typedef CUresult (*PEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -402,7 +449,15 @@ int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, 
   tfde_launch(gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ>, dim3(grid), dim3(P_THREADS), smem, stream, ta, tb, ep, K, tiles_m,
               tiles_n, splits, ws);
   if (splits > 1) {
-    long blocks = ((long)M * N / 4 + 255) / 256;
+    const long total4 = (long)M * N / 4;
+    const bool vec = (N & 3) == 0 && (ep.ldc & 3) == 0;
+    if (vec && splits >= 8 && total4 * 8 <= 148L * 8 * 256) {      // small output, many partials: z-parallel lanes
+      const long zblocks = (total4 * 8 + 255) / 256;
+      tfde_launch(splitk_reduce_zpar_kernel<8>, dim3((int)zblocks), dim3(256), 0, stream, (const float*)ws, ep.c_f32,
+                  ep.c_bf16, ep.ldc, ep.bias, ep.relu, M, N, splits);
+      TFDE_RETURN_LAUNCH_STATUS();
+    }
+    long blocks = (total4 + 255) / 256;
     if (blocks > 148L * 8) blocks = 148L * 8;
     if (blocks < 1) blocks = 1;
     tfde_launch(splitk_reduce_kernel, dim3((int)blocks), dim3(256), 0, stream, (const float*)ws, ep.c_f32, ep.c_bf16, ep.ldc,

@@ -40,6 +40,7 @@ for _n, _a in [
     ("tfde_gap_bwd_bf16", [c_p, c_p, c_i, c_i, c_i, c_p]),
     ("tfde_im2col_b2b", [c_p, c_p] + [c_i] * 13 + [c_i, c_p]),
     ("tfde_dgrad_gather_b2b", [c_p, c_p] + [c_i] * 13 + [c_i, c_p]),
+    ("tfde_strided_scatter_b2b", [c_p, c_p] + [c_i] * 8 + [c_p]),
 ]:
     native.register_optional(_n, _a)
 
@@ -398,6 +399,16 @@ def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bia
             db = colsum(dy2, out=out_db)
     dx = None
     if need_dx:
+        dx = out_dx if out_dx is not None else torch.empty(tuple(x.shape), dtype=BF, device=dev)
+        if kh == 1 and kw == 1 and tuple(stride) != (1, 1) and tuple(pads) == (0, 0, 0, 0) and M >= 128:
+            # strided 1x1 (projection shortcuts): GEMM on the compact [M, c] problem, then spread the rows over the
+            # input grid with zeros in between -- not a [B*H*W, cout] operand that is 3/4 zeros
+            wr = cast_bf16_masked(w.reshape(c, cout), None, out=_scratch(dev, "B", c * cout).view(c, cout))
+            gc = _scratch(dev, "A", M * c).view(M, c)
+            tensorcore.gemm_bf16_tn(dy2, wr, None, False, BF, out=gc)
+            native.check(L.tfde_strided_scatter_b2b(gc.data_ptr(), dx.data_ptr(), b, h, wd, c, ho, wo, stride[0],
+                                                    stride[1], native.stream_ptr()), "strided_scatter_b2b")
+            return dx, dw, db
         if kh == 1 and kw == 1 and tuple(stride) == (1, 1):
             ga = dy2                                                     # Min == M: dy IS the operand
             wr = cast_bf16_masked(w.reshape(c, cout), None, out=_scratch(dev, "B", c * cout).view(c, cout))
@@ -409,6 +420,5 @@ def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bia
             wr = _scratch(dev, "B", c * kd).view(c, kd)
             native.check(L.tfde_wrot_bf16(w.data_ptr(), wr.data_ptr(), kh, kw, c, cout, kd, native.stream_ptr()),
                          "wrot_bf16")
-        dx = out_dx if out_dx is not None else torch.empty(tuple(x.shape), dtype=BF, device=dev)
         tensorcore.gemm_bf16_tn(ga, wr, None, False, BF, out=dx.view(min_, c))
     return dx, dw, db
