@@ -96,9 +96,9 @@ __global__ void __launch_bounds__(ST) colstats_bf16_kernel(const StatArgs a) {
       for (int j = 0; j < 8; ++j) { s[j] += xv.v[j]; if (MODE == 0) q[j] = fmaf(xv.v[j], xv.v[j], q[j]); }
     }
   };
-  // four rows (64 or 128 bytes) in flight per thread: with two 256-thread blocks per SM that is the
-  // memory-level parallelism a pure streaming reduction needs
-  constexpr int U = 4;
+  // U rows (16 bytes each, 32 with dy) in flight per thread: a pure streaming reduction is bound by
+  // memory-level parallelism (measured: 4 rows x 148 blocks reached 2.8 of 6.5 TB/s)
+  constexpr int U = (MODE == 1) ? 4 : 8;
   for (; m + (U - 1) * stride < a.M; m += U * stride) {
     uint4 xr[U], dr[U];
 #pragma unroll
@@ -129,28 +129,37 @@ __global__ void __launch_bounds__(ST) colstats_bf16_kernel(const StatArgs a) {
   __threadfence();
   // Finalise with the whole block: 256/cw thread groups each sum an interleaved subset of the row-block
   // partials (4 loads in flight), then the groups are combined in fixed order through shared memory.
+  // Each thread owns 4 channels (one 16-byte load per partial row and statistic); 4*ST/cw thread groups walk
+  // interleaved subsets of the row blocks with 4 rows in flight: <= 5 dependent load rounds for any shape.
+  const int groups = 4 * ST / cw;
   {
-    const int groups = ST / cw, gi = threadIdx.x / cw, cl = threadIdx.x % cw;
-    double ds = 0.0, dq = 0.0;
+    const int gi = threadIdx.x / (cw >> 2), c4 = (threadIdx.x % (cw >> 2)) << 2;
+    double ds[4] = {0.0, 0.0, 0.0, 0.0}, dq[4] = {0.0, 0.0, 0.0, 0.0};
     const float* base = a.partials + (size_t)blockIdx.x * gridDim.y * 2 * cw;
     unsigned rb = gi;
     for (; rb + 3 * groups < gridDim.y; rb += 4 * groups) {
-      float vs[4], vq[4];
+      float4 vs[4], vq[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const float* pp = base + (size_t)(rb + u * groups) * 2 * cw;
-        vs[u] = __ldcg(pp + cl); vq[u] = __ldcg(pp + cw + cl);
+        vs[u] = __ldcg(reinterpret_cast<const float4*>(pp + c4)); vq[u] = __ldcg(reinterpret_cast<const float4*>(pp + cw + c4));
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) { ds += (double)vs[u]; dq += (double)vq[u]; }
+      for (int u = 0; u < 4; ++u) {
+        ds[0] += (double)vs[u].x; ds[1] += (double)vs[u].y; ds[2] += (double)vs[u].z; ds[3] += (double)vs[u].w;
+        dq[0] += (double)vq[u].x; dq[1] += (double)vq[u].y; dq[2] += (double)vq[u].z; dq[3] += (double)vq[u].w;
+      }
     }
     for (; rb < gridDim.y; rb += groups) {
       const float* pp = base + (size_t)rb * 2 * cw;
-      ds += (double)__ldcg(pp + cl); dq += (double)__ldcg(pp + cw + cl);
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(pp + c4)), w = __ldcg(reinterpret_cast<const float4*>(pp + cw + c4));
+      ds[0] += (double)v.x; ds[1] += (double)v.y; ds[2] += (double)v.z; ds[3] += (double)v.w;
+      dq[0] += (double)w.x; dq[1] += (double)w.y; dq[2] += (double)w.z; dq[3] += (double)w.w;
     }
-    double* dsm = reinterpret_cast<double*>(smem);      // [2][ST] doubles = 8 KB of the 32 KB
+    double* dsm = reinterpret_cast<double*>(smem);      // [2][groups][cw] doubles = 2 * 4*ST * 8 B = 32 KB
     __syncthreads();
-    dsm[threadIdx.x] = ds; dsm[ST + threadIdx.x] = dq;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { dsm[gi * cw + c4 + j] = ds[j]; dsm[groups * cw + gi * cw + c4 + j] = dq[j]; }
     __syncthreads();
   }
   for (int cl = threadIdx.x; cl < cw; cl += ST) {
@@ -158,7 +167,7 @@ __global__ void __launch_bounds__(ST) colstats_bf16_kernel(const StatArgs a) {
     double ds = 0.0, dq = 0.0;
     {
       const double* dsm = reinterpret_cast<const double*>(smem);
-      for (int gi = 0; gi < ST / cw; ++gi) { ds += dsm[gi * cw + cl]; dq += dsm[ST + gi * cw + cl]; }
+      for (int gi = 0; gi < groups; ++gi) { ds += dsm[gi * cw + cl]; dq += dsm[groups * cw + gi * cw + cl]; }
     }
     if (MODE == 0) {
       const double mean = ds / (double)a.M;
@@ -185,7 +194,36 @@ __global__ void bn_apply_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_b
                                      int C, const float* __restrict__ scale, const float* __restrict__ shift,
                                      int relu) {
   TFDE_PDL_PROLOGUE();
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long)gridDim.x * blockDim.x) {
+  const long T = (long)gridDim.x * blockDim.x;
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int c8n = C >> 3;
+  if (T % c8n == 0) {
+    // the grid stride is a multiple of the row length: this thread sees ONE channel group for its whole
+    // life, so the per-channel constants are loaded once (no modulo, no parameter loads in the loop)
+    const int c = (int)(i % c8n) << 3;
+    const F8 sc = load8f(scale + c), sh = load8f(shift + c);
+    for (; i + T < n8; i += 2 * T) {          // two independent 16-byte loads in flight
+      const uint4 r0 = ldg16(x + (i << 3)), r1 = ldg16(x + ((i + T) << 3));
+      const F8 x0 = unpack8(r0), x1 = unpack8(r1);
+      F8 o0, o1;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float v0 = fmaf(x0.v[j], sc.v[j], sh.v[j]), v1 = fmaf(x1.v[j], sc.v[j], sh.v[j]);
+        o0.v[j] = relu ? fmaxf(v0, 0.f) : v0; o1.v[j] = relu ? fmaxf(v1, 0.f) : v1;
+      }
+      *reinterpret_cast<uint4*>(y + (i << 3)) = pack8(o0);
+      *reinterpret_cast<uint4*>(y + ((i + T) << 3)) = pack8(o1);
+    }
+    for (; i < n8; i += T) {
+      const F8 xv = unpack8(ldg16(x + (i << 3)));
+      F8 o;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { const float v = fmaf(xv.v[j], sc.v[j], sh.v[j]); o.v[j] = relu ? fmaxf(v, 0.f) : v; }
+      *reinterpret_cast<uint4*>(y + (i << 3)) = pack8(o);
+    }
+    return;
+  }
+  for (; i < n8; i += T) {
     const int c = (int)((i << 3) % C);
     const F8 xv = unpack8(ldg16(x + (i << 3)));
     const F8 sc = load8f(scale + c), sh = load8f(shift + c);
@@ -208,7 +246,42 @@ __global__ void bn_bwd_apply_bf16_kernel(const __nv_bfloat16* __restrict__ x, co
                                          const float* __restrict__ dgamma, int relu) {
   TFDE_PDL_PROLOGUE();
   const float invM = 1.f / (float)M;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long)gridDim.x * blockDim.x) {
+  const long T = (long)gridDim.x * blockDim.x;
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int c8n = C >> 3;
+  if (T % c8n == 0) {
+    // one channel group per thread for its whole life (see bn_apply_bf16_kernel): fold the per-channel
+    // terms once:  dx = A*(g - B - (x - mu)*D),  A = gamma*invstd, B = dbeta/M, D = invstd*dgamma/M
+    const int c = (int)(i % c8n) << 3;
+    const F8 mu = load8f(mean + c), iv = load8f(invstd + c), db = load8f(dbeta + c), dg = load8f(dgamma + c);
+    F8 A, Bc, D, sc, sh;
+    if (gamma) A = load8f(gamma + c);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      A.v[j] = (gamma ? A.v[j] : 1.f) * iv.v[j]; Bc.v[j] = invM * db.v[j]; D.v[j] = invM * dg.v[j] * iv.v[j];
+    }
+    if (relu) { sc = load8f(scale + c); sh = load8f(shift + c); }
+    auto one = [&](const uint4 xr, const uint4 gr) {
+      const F8 xv = unpack8(xr), g = unpack8(gr);
+      F8 o;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float gj = g.v[j];
+        if (relu && !(fmaf(xv.v[j], sc.v[j], sh.v[j]) > 0.f)) gj = 0.f;
+        o.v[j] = A.v[j] * (gj - Bc.v[j] - (xv.v[j] - mu.v[j]) * D.v[j]);
+      }
+      return pack8(o);
+    };
+    for (; i + T < n8; i += 2 * T) {          // four independent 16-byte loads in flight
+      const uint4 x0 = ldg16(x + (i << 3)), g0 = ldg16(dy + (i << 3));
+      const uint4 x1 = ldg16(x + ((i + T) << 3)), g1 = ldg16(dy + ((i + T) << 3));
+      *reinterpret_cast<uint4*>(dx + (i << 3)) = one(x0, g0);
+      *reinterpret_cast<uint4*>(dx + ((i + T) << 3)) = one(x1, g1);
+    }
+    for (; i < n8; i += T) *reinterpret_cast<uint4*>(dx + (i << 3)) = one(ldg16(x + (i << 3)), ldg16(dy + (i << 3)));
+    return;
+  }
+  for (; i < n8; i += T) {
     const int c = (int)((i << 3) % C);
     const F8 xv = unpack8(ldg16(x + (i << 3))), g = unpack8(ldg16(dy + (i << 3)));
     const F8 mu = load8f(mean + c), iv = load8f(invstd + c), db = load8f(dbeta + c), dg = load8f(dgamma + c);
@@ -385,47 +458,62 @@ struct CG { int B, H, W, C, KH, KW, Ho, Wo, sh, sw, pt, pl, Cout; };
 __global__ void im2col_b2b_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, const CG g,
                                   long M, int Kc, int ldo) {
   TFDE_PDL_PROLOGUE();
-  const int k8n = ldo >> 3;
-  const long total = M * k8n;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const long m = i / k8n;
-    const int k0 = (int)(i % k8n) * 8;
-    uint4 o = make_uint4(0u, 0u, 0u, 0u);
-    if (k0 < Kc) {
-      const int ow = (int)(m % g.Wo); const long t = m / g.Wo;
-      const int oh = (int)(t % g.Ho); const long b = t / g.Ho;
-      const int ci = k0 % g.C; const int tt = k0 / g.C;
-      const int kw = tt % g.KW, kh = tt / g.KW;
-      const int ih = oh * g.sh - g.pt + kh, iw = ow * g.sw - g.pl + kw;
-      if ((unsigned)ih < (unsigned)g.H && (unsigned)iw < (unsigned)g.W)
-        o = ldg16(x + ((b * g.H + ih) * g.W + iw) * (long)g.C + ci);
+  // One warp per output row m: the (b, oh, ow) decomposition is warp-uniform and done once in 32-bit
+  // arithmetic; lanes walk the row's 16-byte groups (the version with one flat 64-bit index per 16 bytes
+  // spent its time in emulated 64-bit divisions: 1.8 TB/s).
+  const unsigned k8n = (unsigned)ldo >> 3;
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned warps = (gridDim.x * blockDim.x) >> 5;
+  const unsigned Mu = (unsigned)M, Wo = (unsigned)g.Wo, Ho = (unsigned)g.Ho, Cu = (unsigned)g.C, KW = (unsigned)g.KW;
+  for (unsigned m = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; m < Mu; m += warps) {
+    const unsigned t = m / Wo, ow = m - t * Wo;
+    const unsigned b = t / Ho, oh = t - b * Ho;
+    const int ih0 = (int)(oh * g.sh) - g.pt, iw0 = (int)(ow * g.sw) - g.pl;
+    const __nv_bfloat16* xb = x + (size_t)b * g.H * g.W * g.C;
+    __nv_bfloat16* orow = out + (size_t)m * ldo;
+    for (unsigned k8 = lane; k8 < k8n; k8 += 32u) {
+      const unsigned k0 = k8 << 3;
+      uint4 o = make_uint4(0u, 0u, 0u, 0u);
+      if (k0 < (unsigned)Kc) {
+        const unsigned tap = k0 / Cu, ci = k0 - tap * Cu;
+        const unsigned kh = tap / KW, kw = tap - kh * KW;
+        const int ih = ih0 + (int)kh, iw = iw0 + (int)kw;
+        if ((unsigned)ih < (unsigned)g.H && (unsigned)iw < (unsigned)g.W)
+          o = ldg16(xb + ((size_t)ih * g.W + iw) * g.C + ci);
+      }
+      *reinterpret_cast<uint4*>(orow + k0) = o;
     }
-    *reinterpret_cast<uint4*>(out + m * ldo + k0) = o;
   }
 }
 
 __global__ void dgrad_gather_b2b_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ out,
                                         const CG g, long Min, int Kd, int ldo) {
   TFDE_PDL_PROLOGUE();
-  const int k8n = ldo >> 3;
-  const long total = Min * k8n;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const long m = i / k8n;
-    const int k0 = (int)(i % k8n) * 8;
-    uint4 o = make_uint4(0u, 0u, 0u, 0u);
-    if (k0 < Kd) {
-      const int w = (int)(m % g.W); const long t = m / g.W;
-      const int h = (int)(t % g.H); const long b = t / g.H;
-      const int co = k0 % g.Cout; const int tt = k0 / g.Cout;
-      const int kw = tt % g.KW, kh = tt / g.KW;
-      const int th = h + g.pt - kh, tw = w + g.pl - kw;
-      if (th >= 0 && tw >= 0) {
-        const int oh = th / g.sh, ow = tw / g.sw;
-        if (oh * g.sh == th && ow * g.sw == tw && oh < g.Ho && ow < g.Wo)
-          o = ldg16(dy + ((b * g.Ho + oh) * g.Wo + ow) * (long)g.Cout + co);
+  // one warp per input position m = (b, h, w); see im2col_b2b_kernel
+  const unsigned k8n = (unsigned)ldo >> 3;
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned warps = (gridDim.x * blockDim.x) >> 5;
+  const unsigned Mu = (unsigned)Min, Wd = (unsigned)g.W, Hd = (unsigned)g.H, Co = (unsigned)g.Cout, KW = (unsigned)g.KW;
+  for (unsigned m = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; m < Mu; m += warps) {
+    const unsigned t = m / Wd, w = m - t * Wd;
+    const unsigned b = t / Hd, h = t - b * Hd;
+    const __nv_bfloat16* db = dy + (size_t)b * g.Ho * g.Wo * g.Cout;
+    __nv_bfloat16* orow = out + (size_t)m * ldo;
+    for (unsigned k8 = lane; k8 < k8n; k8 += 32u) {
+      const unsigned k0 = k8 << 3;
+      uint4 o = make_uint4(0u, 0u, 0u, 0u);
+      if (k0 < (unsigned)Kd) {
+        const unsigned tap = k0 / Co, co = k0 - tap * Co;
+        const unsigned kh = tap / KW, kw = tap - kh * KW;
+        const int th = (int)h + g.pt - (int)kh, tw = (int)w + g.pl - (int)kw;
+        if (th >= 0 && tw >= 0) {
+          const int oh = th / g.sh, ow = tw / g.sw;
+          if (oh * g.sh == th && ow * g.sw == tw && oh < g.Ho && ow < g.Wo)
+            o = ldg16(db + ((size_t)oh * g.Wo + ow) * g.Cout + co);
+        }
       }
+      *reinterpret_cast<uint4*>(orow + k0) = o;
     }
-    *reinterpret_cast<uint4*>(out + m * ldo + k0) = o;
   }
 }
 
@@ -464,7 +552,7 @@ inline bool stat_ok(int C) {
 inline int stat_row_blocks(long M, int C) {
   const int tpr = stat_tpr(C), rows = ST / tpr, ctiles = C / (8 * tpr);
   long want = (M + (long)rows * 8 - 1) / ((long)rows * 8);     // >= 8 rows per thread
-  long cap = (148L + ctiles - 1) / ctiles;                     // one 512-thread block per SM
+  long cap = (148L * 2 + ctiles - 1) / ctiles;                 // two 512-thread blocks per SM
   if (want > cap) want = cap;
   if (want < 1) want = 1;
   return (int)want;

@@ -31,6 +31,33 @@ __global__ void im2col_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* _
   TFDE_PDL_PROLOGUE();
   const int k8n = ldo >> 3;
   const long total = M * k8n;
+  if (total < (1L << 31) && (g.C & 7) != 0) {
+    // Few-channel input (the 3-channel network stem): 32-bit index arithmetic and an incrementally advanced
+    // (kh, kw, ci) tap instead of four divisions per element.
+    const unsigned k8 = (unsigned)k8n, Wo = (unsigned)g.Wo, Ho = (unsigned)g.Ho, Cu = (unsigned)g.C, KW = (unsigned)g.KW;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < (unsigned)total; i += gridDim.x * blockDim.x) {
+      const unsigned m = i / k8, k0 = (i - m * k8) << 3;
+      const unsigned t = m / Wo, ow = m - t * Wo;
+      const unsigned b = t / Ho, oh = t - b * Ho;
+      const int ih0 = (int)(oh * g.sh) - g.pt, iw0 = (int)(ow * g.sw) - g.pl;
+      const float* xb = x + (size_t)b * g.H * g.W * g.C;
+      unsigned tap = k0 / Cu, ci = k0 - tap * Cu;
+      unsigned kh = tap / KW, kw = tap - kh * KW;
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float e = 0.f;
+        const int ih = ih0 + (int)kh, iw = iw0 + (int)kw;
+        if (k0 + j < (unsigned)Kc && (unsigned)ih < (unsigned)g.H && (unsigned)iw < (unsigned)g.W)
+          e = __ldg(xb + ((size_t)ih * g.W + iw) * g.C + ci);
+        v[j] = e;
+        if (++ci == Cu) { ci = 0; if (++kw == KW) { kw = 0; ++kh; } }
+      }
+      uint4 o; o.x = pack2(v[0], v[1]); o.y = pack2(v[2], v[3]); o.z = pack2(v[4], v[5]); o.w = pack2(v[6], v[7]);
+      *reinterpret_cast<uint4*>(out + (size_t)m * ldo + k0) = o;
+    }
+    return;
+  }
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const long m = i / k8n;
     const int k0 = (int)(i % k8n) * 8;

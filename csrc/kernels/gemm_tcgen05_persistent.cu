@@ -86,9 +86,12 @@ struct PEpilogue {
   int M, N;
 };
 
-// MNMAJ = 0: A[M,K], B[N,K] (K contiguous).  MNMAJ = 1: A[K,M], B[K,N] (M / N contiguous) -- the layout a
-// filter-gradient GEMM finds its operands in (activations [rows, Cin] and gradients [rows, Cout], reduced
-// over rows), so no transposed copies are needed.
+// MNMAJ is a bit mask: bit 0 = A is MN-major (stored [K, M], M contiguous), bit 1 = B is MN-major (stored
+// [K, N], N contiguous); a clear bit means K-major ([M, K] / [N, K], K contiguous).
+//   0: A[M,K] B[N,K]   forward / data-gradient GEMMs with pre-transposed weights
+//   2: A[M,K] B[K,N]   forward convolution / dense with the weights exactly as Keras stores them (HWIO, (in,out))
+//   3: A[K,M] B[K,N]   filter gradient: activations [rows, Cin] and gradients [rows, Cout], reduced over rows
+// so no transposed copies of weights, activations or gradients are needed.
 template <int BN, int MNMAJ>
 __global__ void __launch_bounds__(P_THREADS, 1)
 gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -150,13 +153,16 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
           p_mbar_wait(&empty_bar[s], ph ^ 1u);
           p_mbar_expect_tx(&full_bar[s], STAGE_BYTES);
           uint8_t* a_dst = smem + (size_t)s * STAGE_BYTES;
-          if (MNMAJ) {
+          if (MNMAJ & 1) {
 #pragma unroll
             for (int j = 0; j < P_BM / 64; ++j) p_tma_load_2d(a_dst + j * 8192, &tmA, &full_bar[s], m0 + j * 64, kb * P_BK);
+          } else {
+            p_tma_load_2d(a_dst, &tmA, &full_bar[s], kb * P_BK, m0);
+          }
+          if (MNMAJ & 2) {
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j) p_tma_load_2d(a_dst + A_BYTES + j * 8192, &tmB, &full_bar[s], n0 + j * 64, kb * P_BK);
           } else {
-            p_tma_load_2d(a_dst, &tmA, &full_bar[s], kb * P_BK, m0);
             p_tma_load_2d(a_dst + A_BYTES, &tmB, &full_bar[s], kb * P_BK, n0);
           }
         }
@@ -165,7 +171,7 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
   } else if (warp == 1) {
     if (lane == 0) {
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(P_BM >> 4) << 24) |
-                             (MNMAJ ? ((1u << 15) | (1u << 16)) : 0u);
+                             ((MNMAJ & 1) ? (1u << 15) : 0u) | ((MNMAJ & 2) ? (1u << 16) : 0u);
       uint32_t it = 0, tl = 0;                           // tl: tiles done by this CTA
       for (int item = blockIdx.x; item < num_tiles; item += gridDim.x, ++tl) {
         const int z = item % splits;
@@ -182,8 +188,8 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
 #pragma unroll
           for (int k = 0; k < P_BK / P_UMMA_K; ++k) {
             // K-major: 16 elements = 32 bytes along the swizzled row; MN-major: 16 K rows = 2 atoms = 2048 bytes
-            const uint64_t da = MNMAJ ? p_smem_desc_mn(a_addr + k * 2048) : p_smem_desc(a_addr + k * P_UMMA_K * 2);
-            const uint64_t db = MNMAJ ? p_smem_desc_mn(b_addr + k * 2048) : p_smem_desc(b_addr + k * P_UMMA_K * 2);
+            const uint64_t da = (MNMAJ & 1) ? p_smem_desc_mn(a_addr + k * 2048) : p_smem_desc(a_addr + k * P_UMMA_K * 2);
+            const uint64_t db = (MNMAJ & 2) ? p_smem_desc_mn(b_addr + k * 2048) : p_smem_desc(b_addr + k * P_UMMA_K * 2);
             p_umma(tmem_d + acc * BN, da, db, idesc, (kb != kb_begin || k != 0) ? 1u : 0u);
           }
           p_commit(&empty_bar[s]);
@@ -508,7 +514,30 @@ TFDE_API int tfde_gemm_bf16_nt_persistent(const void* A, const void* B, float* c
   rc = p_make_map_ld(&tb, B, K, N, ldb, P_BK, 64);
   if (rc != 0) return rc;
   PEpilogue ep{c_f32, (__nv_bfloat16*)c_bf16, ldc, nullptr, 0, M, N};
-  if (BN == 64) return p_launch<64, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
-  if (BN == 128) return p_launch<128, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
-  return p_launch<256, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  if (BN == 64) return p_launch<64, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  if (BN == 128) return p_launch<128, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  return p_launch<256, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+}
+
+// C[M,N] = act(A[M,K] . B[K,N] + bias): A K-major, B MN-major -- a convolution / dense forward with the weight
+// matrix exactly as Keras stores it ([KH*KW*Cin, Cout] = HWIO flattened, or (in, out)): no per-step
+// transposed weight copy. K % 8 == 0 is required of A's row stride only (lda); B may have fewer than lda rows
+// (`kb` valid rows: padded im2col columns meet zero-filled weight rows). N % 8 == 0.
+TFDE_API int tfde_gemm_bf16_nn_persistent(const void* A, const void* B, float* c_f32, void* c_bf16, long ldc,
+                                          const float* bias, int relu, int M, int N, int K, int kb, long ldb,
+                                          float* ws, size_t ws_bytes, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || (K & 7) || (N & 7) || (ldb & 7) || ldb < N || kb <= 0 || kb > K || !A || !B ||
+      (!c_f32 && !c_bf16))
+    return TFDE_ERR_INVALID;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return TFDE_ERR_INVALID;
+  const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+  CUtensorMap ta, tb;
+  int rc = p_make_map(&ta, A, M, K, P_BM);
+  if (rc != 0) return rc;
+  rc = p_make_map_ld(&tb, B, kb, N, ldb, P_BK, 64);
+  if (rc != 0) return rc;
+  PEpilogue ep{c_f32, (__nv_bfloat16*)c_bf16, ldc, bias, relu, M, N};
+  if (BN == 64) return p_launch<64, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  if (BN == 128) return p_launch<128, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  return p_launch<256, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
 }

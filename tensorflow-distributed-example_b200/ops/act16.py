@@ -23,6 +23,7 @@ from .mixed_conv import _scratch, _geom, _r8
 c_p, c_i, c_l, c_f, c_z = native.c_p, native.c_i, native.c_l, native.c_f, native.c_z
 BF = torch.bfloat16
 _WGRAD_NT = __import__("os").environ.get("TFDE_WGRAD_NT", "1") == "1"   # MN-major filter-gradient GEMM
+_FWD_NN = __import__("os").environ.get("TFDE_FWD_NN", "1") == "1"       # forward GEMM on untransposed weights
 
 for _n, _a in [
     ("tfde_act16_supported_channels", [c_i]),
@@ -318,7 +319,7 @@ def _a_operand(x, w_shape, stride, pads, ho, wo, tag, cache=None, reuse=False):
     return a, kp
 
 
-def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None, a_cache=None):
+def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None, a_cache=None, w16=None):
     """x: bf16 NHWC (or the fp32 network input); w: fp32 HWIO; returns bf16 NHWC."""
     b, h, wd, c = x.shape
     kh, kw, _, cout = w.shape
@@ -333,10 +334,17 @@ def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None, a_ca
     L = native.load()
     M, kc = b * ho * wo, kh * kw * c
     a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "A", cache=a_cache)
+    y = out if out is not None else torch.empty((b, ho, wo, cout), dtype=BF, device=x.device)
+    if _FWD_NN:
+        # weights exactly as Keras stores them (HWIO = [kc, cout] row-major): the GEMM reads them MN-major, the
+        # only per-step weight work is a flat fp32 -> bf16 cast (padded im2col columns meet zero-filled rows)
+        wb = w16 if w16 is not None else cast_bf16_masked(w.reshape(kc, cout), None,
+                                                          out=_scratch(x.device, "B", kc * cout).view(kc, cout))
+        tensorcore.gemm_bf16_nn(a, wb.reshape(kc, cout), bias, False, BF, out=y.view(M, cout))
+        return y
     wt = _scratch(x.device, "B", cout * kp).view(cout, kp)
     native.check(L.tfde_cast_transpose_pad_bf16(w.data_ptr(), None, wt.data_ptr(), kc, cout, kp, native.stream_ptr()),
                  "cast_transpose_pad_bf16")
-    y = out if out is not None else torch.empty((b, ho, wo, cout), dtype=BF, device=x.device)
     tensorcore.gemm_bf16_tn(a, wt, bias, False, BF, out=y.view(M, cout))
     return y
 

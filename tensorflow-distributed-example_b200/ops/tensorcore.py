@@ -83,3 +83,28 @@ def gemm_bf16_nt(a, b, out_dtype=torch.float32, out=None):
                                                 a.stride(0), b.stride(0), wsp.ws.data_ptr(), wsp.ws_bytes,
                                                 native.stream_ptr()), "gemm_bf16_nt[persistent]")
     return c
+
+
+native.register_optional("tfde_gemm_bf16_nn_persistent",
+                         [c_p, c_p, c_p, c_p, c_l, c_p, c_i, c_i, c_i, c_i, c_i, c_l, c_p, native.c_z, c_p])
+
+
+def gemm_bf16_nn(a, b, bias=None, relu=False, out_dtype=torch.float32, out=None):
+    """C[M,N] = act(A[M,K] @ B[Kb,N] + bias): A K-major as usual, B row-major [Kb, N] ("MN-major") -- the weight
+    matrix of a convolution / dense layer as Keras stores it, so the forward GEMM needs no transposed weight copy.
+    Kb <= K (A may carry zero-padded columns up to a multiple of 8); N % 8 == 0."""
+    L = native.load()
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
+        raise TypeError("gemm_bf16_nn expects bf16 operands")
+    M, K = a.shape
+    Kb, N = b.shape
+    if Kb > K or not a.is_contiguous() or b.stride(1) != 1:
+        raise ValueError("gemm_bf16_nn: A must be contiguous [M,K], B row-major [Kb<=K, N]")
+    c = out if out is not None else torch.empty((M, N), dtype=out_dtype, device=a.device)
+    f32 = c.data_ptr() if c.dtype == torch.float32 else None
+    b16 = c.data_ptr() if c.dtype == torch.bfloat16 else None
+    wsp = native.Workspace.current(a.device)
+    native.check(L.tfde_gemm_bf16_nn_persistent(a.data_ptr(), b.data_ptr(), f32, b16, c.stride(0), native.ptr(bias),
+                                                1 if relu else 0, M, N, K, Kb, b.stride(0), wsp.ws.data_ptr(),
+                                                wsp.ws_bytes, native.stream_ptr()), "gemm_bf16_nn[persistent]")
+    return c

@@ -186,3 +186,21 @@ def test_gemm_nt_mn_major(K, M, N):
     c2 = tensorcore.gemm_bf16_nt(wide[:, :M], b)
     ref2 = wide[:, :M].float().t() @ b.float()
     assert (c2 - ref2).abs().max().item() <= 2e-3 * (K ** 0.5) * 4
+
+
+@pytest.mark.parametrize("M,K,Kb,N", [(1024, 64, 64, 256), (6272, 576, 576, 64), (3000, 152, 147, 64), (512, 2048, 2048, 512)])
+def test_gemm_nn_weights_as_stored(M, K, Kb, N):
+    """A[M,K] K-major x B[Kb,N] row-major (MN-major): the forward GEMM on weights exactly as Keras stores them;
+    Kb < K = zero-padded im2col columns meeting TMA-zero-filled weight rows."""
+    from tfde_b200.ops import tensorcore
+    dev = _dev()
+    g = torch.Generator().manual_seed(M + K + N)
+    a = torch.randn(M, K, generator=g).to(BF)
+    a[:, Kb:] = 0
+    a = a.to(dev)
+    b = torch.randn(Kb, N, generator=g).to(BF).to(dev)
+    bias = torch.randn(N, generator=g).to(dev)
+    c = tensorcore.gemm_bf16_nn(a, b, bias, True, BF)
+    ref = torch.relu(a[:, :Kb].float() @ b.float() + bias)
+    torch.cuda.synchronize()
+    _close(c, ref, 2e-2, 2e-2 * (K ** 0.5) / 8)
