@@ -188,8 +188,64 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 #pragma unroll 1
     for (int mt = 0; mt < MT; ++mt) {
       const int row0 = m0 + mt * TC_BM + q * 32;
+      // Staged path (one output dtype, 16-byte aligned rows): each warp bounces a 32-row x 128-byte slab
+      // through a private padded tile in the (now idle) pipeline shared memory and stores it with 8 lanes per
+      // row, so every store instruction covers 4 complete 128-byte lines instead of 32 half-sectors
+      // (see gemm_tcgen05_persistent.cu; profiles/ncu_resnet_gemm_direct_epilogue.json for the measurement).
+      int c_done = 0;
+      if (((ep.c_f32 == nullptr) != (ep.c_bf16 == nullptr)) && (ep.ldc & 7) == 0) {
+        constexpr int PITCH = 144;
+        uint8_t* stg = smem + q * (32 * PITCH);
+        const bool out16 = ep.c_bf16 != nullptr;
+        const int pass = out16 ? 64 : 32;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = 0; c0 + pass <= BN && n0 + c0 + pass <= ep.N; c0 += pass) {
+          const int nbase = n0 + c0;
+#pragma unroll 1
+          for (int h = 0; h * 32 < pass; ++h) {
+            uint32_t r[32];
+            tmem_ld_32x32(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(mt * BN + c0 + h * 32), r);
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              float x = __uint_as_float(r[j]);
+              if (ep.bias != nullptr) x += __ldg(ep.bias + nbase + h * 32 + j);
+              v[j] = ep.relu ? fmaxf(x, 0.f) : x;
+            }
+            uint4* srow = reinterpret_cast<uint4*>(stg + lane * PITCH);
+            if (out16) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                uint4 o;
+                __nv_bfloat162 p0 = __floats2bfloat162_rn(v[j], v[j + 1]), p1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+                __nv_bfloat162 p2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]), p3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
+                o.x = *reinterpret_cast<uint32_t*>(&p0); o.y = *reinterpret_cast<uint32_t*>(&p1);
+                o.z = *reinterpret_cast<uint32_t*>(&p2); o.w = *reinterpret_cast<uint32_t*>(&p3);
+                srow[h * 4 + (j >> 3)] = o;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                srow[j >> 2] = make_uint4(__float_as_uint(v[j]), __float_as_uint(v[j + 1]), __float_as_uint(v[j + 2]),
+                                          __float_as_uint(v[j + 3]));
+            }
+          }
+          __syncwarp();
+          uint8_t* gbase = out16 ? reinterpret_cast<uint8_t*>(ep.c_bf16 + nbase) : reinterpret_cast<uint8_t*>(ep.c_f32 + nbase);
+          const size_t gpitch = (size_t)ep.ldc * (out16 ? 2 : 4);
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + (lane >> 3), piece = lane & 7;
+            const uint4 val = *reinterpret_cast<const uint4*>(stg + rr * PITCH + piece * 16);
+            const int row = row0 + rr;
+            if (row < ep.M) *reinterpret_cast<uint4*>(gbase + (size_t)row * gpitch + piece * 16) = val;
+          }
+          __syncwarp();
+          c_done = c0 + pass;
+        }
+      }
+#pragma unroll 1
+      for (int c0 = c_done; c0 < BN; c0 += 32) {
         const int nbase = n0 + c0;
         if (nbase >= ep.N) break;
         uint32_t r[32];
