@@ -256,7 +256,7 @@ class Conv2D(Layer):
             self._a_cache = (self.buf("a16", ashape, torch.bfloat16)
                              if ashape is not None and training and _CACHE_IM2COL else None)
             act16.conv2d_fwd(x, self.kernel.value, self.bias.value if self.bias else None, self.strides,
-                             self.pads, out=y, a_cache=self._a_cache)
+                             self.pads, out=y, a_cache=self._a_cache, w16=getattr(self.kernel, "value16", None))
             self._y = y
             return y
         y = self.buf("y", (b,) + self.out_shape)
@@ -278,6 +278,7 @@ class Conv2D(Layer):
             act16.conv2d_bwd(self._x, self.kernel.value, dy, self.strides, self.pads, self.need_dx, self.use_bias,
                              getattr(self, "bias_grad_zero", False), out_dx=dx, out_dw=self.kernel.grad,
                              out_db=self.bias.grad if self.bias else None, a_cache=getattr(self, "_a_cache", None),
+                             w16=getattr(self.kernel, "value16", None),
                              side_stream=(self.model.fork_stream() if dy.is_cuda and _FORK_CONV_WGRAD else None))
             if dx is not None and self._x.dtype != torch.bfloat16:
                 dx = self.buf("dx", self._x.shape).copy_(dx)

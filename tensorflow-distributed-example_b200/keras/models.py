@@ -174,7 +174,7 @@ class Sequential:
             off = 0
             for v in vs:
                 v.offset = off
-                off += (v.size + 3) // 4 * 4   # 16-byte aligned slices (vector loads / TMA friendly)
+                off += (v.size + 7) // 8 * 8   # slices 32-byte aligned in fp32, 16-byte aligned in the bf16 shadow (TMA)
             return off
 
         train = [v for v in self.variables if v.trainable]
@@ -189,6 +189,19 @@ class Sequential:
             v.grad = self.arena.g[v.offset:v.offset + v.size].view(v.shape)
         for v in frozen:
             v.value = self.state[v.offset:v.offset + v.size].view(v.shape)
+        # bf16 activations: the tensor-core GEMMs read the weights from ONE bf16 shadow of the parameter arena,
+        # refreshed by a single cast kernel per step (instead of one cast/transpose kernel per layer and GEMM)
+        from ..ops import mixed
+        self._w16 = None
+        if self.device.type == "cuda" and mixed.activation_dtype() == "bfloat16":
+            self._w16 = torch.zeros(self.arena.n_total, dtype=torch.bfloat16, device=self.device)
+            for v in train:
+                v.value16 = self._w16[v.offset:v.offset + v.size].view(v.shape)
+
+    def _refresh_w16(self):
+        if getattr(self, "_w16", None) is not None:
+            from ..ops import mixed
+            mixed.cast_bf16_masked(self.arena.w, None, out=self._w16)
 
     def _initialize(self):
         gen = torch.Generator(device="cpu")
@@ -292,6 +305,7 @@ class Sequential:
         return b
 
     def _forward(self, x, training: bool):
+        self._refresh_w16()
         x = self._prep_input(x)
         for node in self.exec_plan:
             x = node.run(x, training)
@@ -334,6 +348,7 @@ class Sequential:
         head = self._fusable_head(x)
         if head is not None:
             # classifier head in one launch: Dense + loss/accuracy + d(logits) + dW/db + dh
+            self._refresh_w16()
             h = self._prep_input(x)
             for node in self.exec_plan[:-1]:
                 h = node.run(h, True)

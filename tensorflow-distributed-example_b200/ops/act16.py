@@ -350,7 +350,7 @@ def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None, a_ca
 
 
 def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bias=True, bias_grad_zero=False,
-               out_dx=None, out_dw=None, out_db=None, a_cache=None, side_stream=None):
+               out_dx=None, out_dw=None, out_db=None, a_cache=None, side_stream=None, w16=None):
     """dy: bf16. Returns (dx bf16 | None, dw fp32, db fp32 | None).
     ``bias_grad_zero``: the convolution feeds a training-mode batch-norm, whose input gradient sums to zero
     over every channel (batch-norm is invariant to a per-channel shift of its input), so the bias gradient
@@ -411,7 +411,8 @@ def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bia
         if kh == 1 and kw == 1 and tuple(stride) != (1, 1) and tuple(pads) == (0, 0, 0, 0) and M >= 128:
             # strided 1x1 (projection shortcuts): GEMM on the compact [M, c] problem, then spread the rows over the
             # input grid with zeros in between -- not a [B*H*W, cout] operand that is 3/4 zeros
-            wr = cast_bf16_masked(w.reshape(c, cout), None, out=_scratch(dev, "B", c * cout).view(c, cout))
+            wr = (w16.reshape(c, cout) if w16 is not None else
+                  cast_bf16_masked(w.reshape(c, cout), None, out=_scratch(dev, "B", c * cout).view(c, cout)))
             gc = _scratch(dev, "A", M * c).view(M, c)
             tensorcore.gemm_bf16_tn(dy2, wr, None, False, BF, out=gc)
             native.check(L.tfde_strided_scatter_b2b(gc.data_ptr(), dx.data_ptr(), b, h, wd, c, ho, wo, stride[0],
@@ -419,7 +420,8 @@ def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bia
             return dx, dw, db
         if kh == 1 and kw == 1 and tuple(stride) == (1, 1):
             ga = dy2                                                     # Min == M: dy IS the operand
-            wr = cast_bf16_masked(w.reshape(c, cout), None, out=_scratch(dev, "B", c * cout).view(c, cout))
+            wr = (w16.reshape(c, cout) if w16 is not None else
+                  cast_bf16_masked(w.reshape(c, cout), None, out=_scratch(dev, "B", c * cout).view(c, cout)))
         else:
             ga = _scratch(dev, "A", min_ * kd).view(min_, kd)
             g = _geom(x.shape, w.shape, stride, pads, ho, wo)
