@@ -64,7 +64,9 @@ struct StatArgs {
 constexpr int ST = 512;
 
 template <int MODE>
-__global__ void __launch_bounds__(ST) colstats_bf16_kernel(const StatArgs a) {
+__global__ void __launch_bounds__(ST, (MODE == 1) ? 1 : 2) colstats_bf16_kernel(const StatArgs a) {
+  // MODE 0/2: two blocks per SM (<= 64 registers, no spills); MODE 1 keeps 4 more per-channel vectors live and
+  // gets a whole SM (the host sizes the grid accordingly)
   TFDE_PDL_PROLOGUE();
   extern __shared__ float smem[];   // [2][rows][8*tpr]
   __shared__ int s_last;
@@ -549,10 +551,10 @@ inline bool stat_ok(int C) {
   const int t = stat_tpr(C);
   return (ST % t) == 0 && (C % (8 * t)) == 0;
 }
-inline int stat_row_blocks(long M, int C) {
+inline int stat_row_blocks(long M, int C, int blocks_per_sm = 2) {
   const int tpr = stat_tpr(C), rows = ST / tpr, ctiles = C / (8 * tpr);
   long want = (M + (long)rows * 8 - 1) / ((long)rows * 8);     // >= 8 rows per thread
-  long cap = (148L * 2 + ctiles - 1) / ctiles;                 // two 512-thread blocks per SM
+  long cap = (148L * blocks_per_sm + ctiles - 1) / ctiles;     // exactly one resident wave
   if (want > cap) want = cap;
   if (want < 1) want = 1;
   return (int)want;
@@ -562,7 +564,7 @@ template <int MODE>
 int launch_stats(StatArgs& a, float* ws, size_t ws_floats, unsigned* counters, cudaStream_t stream) {
   if (!stat_ok(a.C)) return TFDE_ERR_INVALID;
   a.tpr = stat_tpr(a.C);
-  const int cw = 8 * a.tpr, ctiles = a.C / cw, rb = stat_row_blocks(a.M, a.C);
+  const int cw = 8 * a.tpr, ctiles = a.C / cw, rb = stat_row_blocks(a.M, a.C, MODE == 1 ? 1 : 2);
   if ((size_t)ctiles * rb * 2 * cw > ws_floats || ctiles > TFDE_MAX_COUNTERS) return TFDE_ERR_INVALID;
   a.partials = ws; a.counters = counters;
   const size_t smem = (size_t)2 * (ST / a.tpr) * cw * sizeof(float);      // = 32 KB
