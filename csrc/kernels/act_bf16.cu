@@ -467,13 +467,34 @@ __global__ void im2col_b2b_kernel(const __nv_bfloat16* __restrict__ x, __nv_bflo
   const unsigned lane = threadIdx.x & 31u;
   const unsigned warps = (gridDim.x * blockDim.x) >> 5;
   const unsigned Mu = (unsigned)M, Wo = (unsigned)g.Wo, Ho = (unsigned)g.Ho, Cu = (unsigned)g.C, KW = (unsigned)g.KW;
+  // a lane visits the same 16-byte groups of every row: decode the first NIP of them (kh, kw, ci) once
+  constexpr int NIP = 4;
+  int pkh[NIP], pkw[NIP]; unsigned pci[NIP];
+#pragma unroll
+  for (int it = 0; it < NIP; ++it) {
+    const unsigned k0 = (lane + 32u * it) << 3;
+    const unsigned tap = k0 / Cu;
+    pci[it] = k0 - tap * Cu; pkh[it] = (int)(tap / KW); pkw[it] = (int)(tap - (tap / KW) * KW);
+  }
   for (unsigned m = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; m < Mu; m += warps) {
     const unsigned t = m / Wo, ow = m - t * Wo;
     const unsigned b = t / Ho, oh = t - b * Ho;
     const int ih0 = (int)(oh * g.sh) - g.pt, iw0 = (int)(ow * g.sw) - g.pl;
     const __nv_bfloat16* xb = x + (size_t)b * g.H * g.W * g.C;
     __nv_bfloat16* orow = out + (size_t)m * ldo;
-    for (unsigned k8 = lane; k8 < k8n; k8 += 32u) {
+#pragma unroll
+    for (int it = 0; it < NIP; ++it) {
+      const unsigned k8 = lane + 32u * it;
+      if (k8 < k8n) {
+        const unsigned k0 = k8 << 3;
+        uint4 o = make_uint4(0u, 0u, 0u, 0u);
+        const int ih = ih0 + pkh[it], iw = iw0 + pkw[it];
+        if (k0 < (unsigned)Kc && (unsigned)ih < (unsigned)g.H && (unsigned)iw < (unsigned)g.W)
+          o = ldg16(xb + ((size_t)ih * g.W + iw) * g.C + pci[it]);
+        *reinterpret_cast<uint4*>(orow + k0) = o;
+      }
+    }
+    for (unsigned k8 = lane + 32u * NIP; k8 < k8n; k8 += 32u) {
       const unsigned k0 = k8 << 3;
       uint4 o = make_uint4(0u, 0u, 0u, 0u);
       if (k0 < (unsigned)Kc) {
@@ -496,12 +517,35 @@ __global__ void dgrad_gather_b2b_kernel(const __nv_bfloat16* __restrict__ dy, __
   const unsigned lane = threadIdx.x & 31u;
   const unsigned warps = (gridDim.x * blockDim.x) >> 5;
   const unsigned Mu = (unsigned)Min, Wd = (unsigned)g.W, Hd = (unsigned)g.H, Co = (unsigned)g.Cout, KW = (unsigned)g.KW;
+  const bool unit = g.sh == 1 && g.sw == 1;        // stride 1 (every 3x3 of ResNet): no per-element divisions
+  constexpr int NIP = 4;
+  int pkh[NIP], pkw[NIP]; unsigned pco[NIP];
+#pragma unroll
+  for (int it = 0; it < NIP; ++it) {
+    const unsigned k0 = (lane + 32u * it) << 3;
+    const unsigned tap = k0 / Co;
+    pco[it] = k0 - tap * Co; pkh[it] = (int)(tap / KW); pkw[it] = (int)(tap - (tap / KW) * KW);
+  }
   for (unsigned m = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; m < Mu; m += warps) {
     const unsigned t = m / Wd, w = m - t * Wd;
     const unsigned b = t / Hd, h = t - b * Hd;
     const __nv_bfloat16* db = dy + (size_t)b * g.Ho * g.Wo * g.Cout;
     __nv_bfloat16* orow = out + (size_t)m * ldo;
-    for (unsigned k8 = lane; k8 < k8n; k8 += 32u) {
+    if (unit) {
+#pragma unroll
+      for (int it = 0; it < NIP; ++it) {
+        const unsigned k8 = lane + 32u * it;
+        if (k8 < k8n) {
+          const unsigned k0 = k8 << 3;
+          uint4 o = make_uint4(0u, 0u, 0u, 0u);
+          const int oh = (int)h + g.pt - pkh[it], ow = (int)w + g.pl - pkw[it];
+          if (k0 < (unsigned)Kd && (unsigned)oh < (unsigned)g.Ho && (unsigned)ow < (unsigned)g.Wo)
+            o = ldg16(db + ((size_t)oh * g.Wo + ow) * g.Cout + pco[it]);
+          *reinterpret_cast<uint4*>(orow + k0) = o;
+        }
+      }
+    }
+    for (unsigned k8 = unit ? lane + 32u * NIP : lane; k8 < k8n; k8 += 32u) {
       const unsigned k0 = k8 << 3;
       uint4 o = make_uint4(0u, 0u, 0u, 0u);
       if (k0 < (unsigned)Kd) {

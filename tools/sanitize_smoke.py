@@ -31,5 +31,30 @@ if "--tc" in sys.argv:
     mixed_conv.conv2d_bwd(xc, w, yc, torch.ones_like(yc), (1, 1), (1, 1, 1, 1), True, True, False)
     torch.cuda.synchronize()
     print("tc ok", float(c.sum()), float(yc.sum()))
+if "--act16" in sys.argv:
+    # bf16-activation kernels, MN-major / untransposed-weight GEMMs, staged epilogues
+    from tfde_b200 import ops
+    from tfde_b200.ops import act16, tensorcore
+    BF = torch.bfloat16
+    dev = torch.device("cuda")
+    xb = torch.randn(8, 16, 16, 64, generator=g).to(BF).to(dev)
+    gam, bet = torch.ones(64, device=dev), torch.zeros(64, device=dev)
+    mm, mv = torch.zeros(64, device=dev), torch.ones(64, device=dev)
+    yb, sm, si, sc, sh = act16.bn_fwd(xb, gam, bet, mm, mv, 0.99, 1e-3, True, True, True)
+    act16.bn_bwd(xb, yb, gam, sm, si, sc, sh, True)
+    act16.add(xb, yb, relu=True); act16.relu_bwd(yb, xb, addend=xb); act16.colsum(xb.reshape(-1, 64))
+    p, idx = act16.maxpool_fwd(xb, (3, 3), (2, 2), (0, 1, 0, 1))
+    act16.maxpool_bwd(p, idx, tuple(xb.shape), (3, 3), (2, 2), (0, 1, 0, 1))
+    act16.global_avgpool_bwd(act16.global_avgpool_fwd(xb), tuple(xb.shape))
+    for (k, s, co) in ((1, 1, 256), (3, 1, 64), (1, 2, 128)):
+        ho, wo, pads = ops.conv_geometry(16, 16, k, k, (s, s), "same")
+        w = (torch.randn(k, k, 64, co, generator=g) * 0.05).to(dev)
+        yc = act16.conv2d_fwd(xb, w, None, (s, s), pads)
+        act16.conv2d_bwd(xb, w, torch.ones_like(yc), (s, s), pads)
+    a = torch.randn(1000, 136, generator=g).to(BF).to(dev)
+    tensorcore.gemm_bf16_nt(a, torch.randn(1000, 72, generator=g).to(BF).to(dev))
+    tensorcore.gemm_bf16_nn(a, torch.randn(130, 72, generator=g).to(BF).to(dev), None, True, BF)
+    torch.cuda.synchronize()
+    print("act16 ok")
 torch.cuda.synchronize()
 print("SANITIZE SMOKE DONE")
