@@ -11,9 +11,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "tensorflow-distributed-example_b200", "_lib", "libtfde_kernels.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
 KEEP = ("gemm_bf16_tcgen05_kernel", "allreduce_fused_kernel", "dense_skinny_fwd_kernel", "head_fwd_bwd_kernel",
-        "conv3x3c1_relu_pool", "gemm_fp32_kernel")
-MNEMONICS = ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMAPF", "SYNCS", "LDGSTS", "UCGABAR", "HMMA", "FFMA", "LDG", "STG",
-             "ATOMG", "REDG", "MEMBAR", "CCTL")
+        "conv3x3c1_relu_pool", "allreduce_nvls_kernel", "gemm_bf16_tcgen05_persistent_kernel", "colstats_bf16_kernel",
+        "bn_bwd_apply_bf16_kernel", "gemm_fp32_kernel")
+N_LISTED = 9     # kernels of KEEP[:N_LISTED] get a full listing; the rest only a row in the summary
+MNEMONICS = ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMAPF", "SYNCS", "LDGSTS", "UCGABAR", "LDGMC", "HMMA", "FFMA", "LDG",
+             "STG", "STS", "LDS", "ATOMG", "REDG", "MEMBAR", "CCTL")
 
 
 def main():
@@ -40,7 +42,7 @@ def main():
                 if ".SYS" in op or ".STRONG.SYS" in op:
                     counts["sys-scope"] += 1
         path = os.path.join(OUT, short + ".sass")
-        if any(k in name for k in KEEP[:5]):
+        if any(k in name for k in KEEP[:N_LISTED]):
             with open(path, "w") as f:
                 f.write("Function : " + part)
         rows.append((short, counts))
