@@ -202,6 +202,63 @@ int tfde_dense_wgrad_push(const float* x, const float* dy, const float* ymask, f
                           tfde_stream_t stream);
 size_t tfde_push_desc_bytes(void);
 
+/* ---- tcgen05 GEMMs with MN-major operands (gemm_tcgen05_persistent.cu) ------------------------------------ */
+/* C[M,N] = A[K,M]^T . B[K,N]: the filter-gradient GEMM with activations [rows, Cin] and output gradients
+ * [rows, Cout] as the forward pass left them (both "MN-major": a_major/b_major bits of the instruction
+ * descriptor, 64x64 TMA boxes). M % 8 == 0, N % 8 == 0, any K; lda/ldb row strides in elements. Deterministic
+ * split-K through `ws`. ref: the dW of every Conv2D/Dense (cuDNN/cuBLAS in TF): distributed_with_keras.py:34-38. */
+int tfde_gemm_bf16_nt_persistent(const void* A, const void* B, float* c_f32, void* c_bf16, long ldc, int M, int N,
+                                 int K, long lda, long ldb, float* ws, size_t ws_bytes, tfde_stream_t stream);
+/* C[M,N] = act(A[M,K] . B[kb,N] + bias): A K-major, B MN-major = the weight matrix exactly as Keras stores it
+ * (HWIO flattened / (in,out)); kb <= K valid rows of B (padded im2col columns meet zero-filled rows). */
+int tfde_gemm_bf16_nn_persistent(const void* A, const void* B, float* c_f32, void* c_bf16, long ldc,
+                                 const float* bias, int relu, int M, int N, int K, int kb, long ldb, float* ws,
+                                 size_t ws_bytes, tfde_stream_t stream);
+
+/* ---- bf16-activation layer kernels (act_bf16.cu) ----------------------------------------------------------- */
+/* Keras mixed_bfloat16 semantics: bf16 tensors between layers, fp32 variables / statistics. All tensors are
+ * channels-last with C % 8 == 0 (tfde_act16_supported_channels). `ws`/`counters`: per-stream scratch for the
+ * two-phase deterministic column reductions. ref: BatchNormalization / Activation / MaxPooling2D / Conv2D,
+ * mnist_keras_distributed.py:83-104; ResNet-50 config of BASELINE.json. */
+int tfde_act16_supported_channels(int C);
+size_t tfde_act16_ws_floats(long M, int C);
+int tfde_bn_fwd_train_bf16(const void* x, void* y, long M, int C, const float* gamma, const float* beta,
+                           float* moving_mean, float* moving_var, float momentum, float eps, int relu,
+                           int unbiased_moving, float* save_mean, float* save_invstd, float* scale, float* shift,
+                           float* ws, size_t ws_floats, unsigned* counters, tfde_stream_t stream);
+int tfde_bn_apply_bf16(const void* x, void* y, long M, int C, const float* scale, const float* shift, int relu,
+                       tfde_stream_t stream);
+/* backward; with relu != 0 the mask (y > 0) is recomputed as x*scale+shift > 0 instead of re-reading y */
+int tfde_bn_bwd_bf16(const void* x, const void* dy, void* dx, long M, int C, const float* gamma,
+                     const float* save_mean, const float* save_invstd, const float* scale, const float* shift,
+                     int relu, float* dgamma, float* dbeta, float* ws, size_t ws_floats, unsigned* counters,
+                     tfde_stream_t stream);
+int tfde_colsum_bf16(const void* x, long M, int C, float* out, float* ws, size_t ws_floats, unsigned* counters,
+                     tfde_stream_t stream);
+int tfde_add_bf16(const void* a, const void* b, void* y, long n, int relu, tfde_stream_t stream);
+int tfde_relu_bwd_bf16(const void* y, const void* dy, const void* addend, void* dx, long n, tfde_stream_t stream);
+int tfde_cast_f32_bf16(const float* x, void* y, long n, tfde_stream_t stream);
+int tfde_maxpool_fwd_bf16(const void* x, void* y, uint8_t* idx, int Bn, int H, int W, int C, int PH, int PW, int sh,
+                          int sw, int pt, int pl, int Ho, int Wo, tfde_stream_t stream);
+int tfde_maxpool_bwd_bf16(const void* dy, const uint8_t* idx, void* dx, int Bn, int H, int W, int C, int PH, int PW,
+                          int sh, int sw, int pt, int pl, int Ho, int Wo, tfde_stream_t stream);
+int tfde_gap_fwd_bf16(const void* x, float* y, int Bn, int HW, int C, tfde_stream_t stream);
+int tfde_gap_bwd_bf16(const float* dy, void* dx, int Bn, int HW, int C, tfde_stream_t stream);
+/* bf16 -> bf16 operand gathers (one warp per row, 16 bytes per lane) and the compact strided-1x1 data gradient */
+int tfde_im2col_b2b(const void* x, void* out, int B, int H, int W, int C, int KH, int KW, int Ho, int Wo, int sh,
+                    int sw, int pt, int pl, int Cout, int ldo, tfde_stream_t stream);
+int tfde_dgrad_gather_b2b(const void* dy, void* out, int B, int H, int W, int C, int KH, int KW, int Ho, int Wo,
+                          int sh, int sw, int pt, int pl, int Cout, int ldo, tfde_stream_t stream);
+int tfde_strided_scatter_b2b(const void* g, void* dx, int Bn, int H, int W, int C, int Ho, int Wo, int sh, int sw,
+                             tfde_stream_t stream);
+
+/* ---- NVLS all-reduce (allreduce_p2p.cu, mode 2 of tfde_allreduce_fused) ---------------------------------- */
+/* Bytes of the multicast-bound signal pad the NVLS variant needs ([2 phases][256 blocks] counters). The
+ * descriptor's mc_g / mc_w / mc_flags are multicast mappings (multimem.ld_reduce / multimem.st / multimem.red),
+ * nv_flags this rank's ordinary mapping of the signal pad. ref: the NCCL all-reduce behind
+ * MultiWorkerMirroredStrategy, distributed_with_keras.py:16,63. */
+size_t tfde_ar_nvls_flag_bytes(void);
+
 /* ---- diagnostics (debug_util.cu) ---------------------------------------------------------------------- */
 int tfde_capture_status(tfde_stream_t stream); /* 0 none, 1 capturing, 2 capture invalidated */
 int tfde_clear_last_error(void);

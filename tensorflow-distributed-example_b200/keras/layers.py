@@ -234,8 +234,7 @@ class Conv2D(Layer):
         """bf16-activation path (ops/act16.py): policy mixed_bfloat16 + activations='bfloat16', no fused
         activation, tensor-core-friendly shapes. The fp32 network input is accepted too (stem conv)."""
         from ..ops import mixed, act16
-        return (x.is_cuda is not None and mixed.global_policy() == "mixed_bfloat16"
-                and mixed.activation_dtype() == "bfloat16" and self.activation is None
+        return (mixed.activation_dtype() == "bfloat16" and self.activation is None
                 and act16.conv_supported(x.shape, self.kernel.shape, self.out_shape[0], self.out_shape[1],
                                          x.dtype == torch.bfloat16))
 
