@@ -168,6 +168,52 @@ def check_ps_push_pull(strategy):
     return ok
 
 
+def soak(strategy, iters):
+    """Stress / soak of the cross-GPU protocol (what a single-device race checker cannot see): `iters`
+    back-to-back fused all-reduce+SGD launches per variant with random per-rank host delays (ranks arrive at the
+    flag barriers in every order), several arena sizes, integer-valued gradients so that every partial sum is
+    exact in fp32 and the expected weights are known in closed form. Checks: exact result, bit-identical
+    replicas, no timeout status, epochs in lock-step."""
+    import random
+    comm = strategy.comm()
+    rank, world = strategy.rank, strategy.world_size
+    rnd = random.Random(1000 + rank)
+    ok = True
+    modes = ("one_shot", "two_shot") + (("nvls",) if comm.nvls else ())
+    for mode in modes:
+        for n in (257, 40_003, 347_146):
+            os.environ["TFDE_AR_MODE"] = mode
+            opt = O.SGD(1.0).bind(strategy.device, seed=1)
+            arena = Arena(n, strategy.device, comm=comm)
+            comm.prepare(arena, opt)
+            arena.w.zero_()
+            base = (torch.arange(arena.n_total, device=strategy.device) % 7).float()
+            for it in range(iters):
+                arena.g.copy_(base * float(rank + 1))          # sum over ranks = base * W(W+1)/2
+                if rnd.random() < 0.3:
+                    time.sleep(rnd.random() * 2e-3)            # skew the ranks against each other
+                comm.reduce_and_apply(arena, opt)
+                opt.iterations += 1
+                if it % 64 == 63:
+                    torch.cuda.synchronize()
+            torch.cuda.synchronize()
+            comm.check_health()
+            expect = -(base[:n].double() * (world * (world + 1) / 2) * iters)
+            err = (arena.w[:n].double() - expect).abs().max().item()
+            if err != 0.0:
+                print(f"[rank {rank}] FAIL soak mode={mode} n={n}: max err {err}", flush=True)
+                ok = False
+            ws = gather_cpu(arena.w[:n])
+            if not all(np.array_equal(ws[0], x) for x in ws[1:]):
+                print(f"[rank {rank}] FAIL soak replicas differ mode={mode} n={n}", flush=True)
+                ok = False
+            if native.hparams_get(opt.hparams)["step"] != iters:
+                print(f"[rank {rank}] FAIL soak device step counter mode={mode} n={n}", flush=True)
+                ok = False
+            del arena
+    return ok
+
+
 def sweep(strategy, out_path):
     """Fused all-reduce(+SGD) bus bandwidth: S/t * 2(N-1)/N, device-timed, max over ranks."""
     comm = strategy.comm()
@@ -251,6 +297,17 @@ def main():
         strategy.shutdown()
         dist.destroy_process_group()
         return
+    if "--soak" in sys.argv:
+        iters = int(sys.argv[sys.argv.index("--soak") + 1])
+        sok = soak(strategy, iters)
+        flag = torch.tensor([1.0 if sok else 0.0], dtype=torch.float64)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if rank == 0:
+            print(f"P2P SOAK ({iters} iterations x 3 sizes x variants)", "PASSED" if flag.item() == 1.0 else "FAILED",
+                  flush=True)
+        strategy.shutdown()
+        dist.destroy_process_group()
+        sys.exit(0 if flag.item() == 1.0 else 1)
     if rank == 0:
         print("NVLS multicast:", "available" if strategy.comm().nvls else "unavailable", flush=True)
     # small scalar all-reduce (G14)
