@@ -22,3 +22,18 @@ def test_p2p_allreduce_two_ranks():
     sys.stdout.write(r.stdout[-4000:])
     sys.stderr.write(r.stderr[-4000:])
     assert r.returncode == 0 and "P2P CHECKS PASSED" in r.stdout
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_p2p_soak_skewed_ranks():
+    """Soak of the cross-GPU flag protocol (what a single-device race checker cannot
+    see): 200 launches per variant and size with randomly delayed ranks and exact integer sums."""
+    n = min(torch.cuda.device_count(), 8)
+    n = 2 if n < 4 else (4 if n < 8 else 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+           "--master-addr", "127.0.0.1", "--master-port", "29534",
+           os.path.join(ROOT, "tests", "mp_worker_p2p.py"), "--soak", "200"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    sys.stdout.write(r.stdout[-4000:])
+    sys.stderr.write(r.stderr[-4000:])
+    assert r.returncode == 0 and "PASSED" in r.stdout
