@@ -312,7 +312,12 @@ head_fwd_bwd_kernel(const HeadParams p) {
 size_t head_smem_bytes(int K, int N, int rpb = HD_ROWS_MAX) {
   return ((size_t)rpb * (K + 1) + (size_t)K * N + (size_t)rpb * N + N + 16) * sizeof(float);
 }
-int head_rows_per_block(int M) { return M <= 256 ? 16 : HD_ROWS_MAX; }
+int head_rows_per_block(int M) {
+  static int forced = -1;      // TFDE_HEAD_RPB=16|64 overrides the heuristic (experiments)
+  if (forced < 0) { const char* e = getenv("TFDE_HEAD_RPB"); forced = e ? atoi(e) : 0; }
+  if (forced == 4 || forced == 8 || forced == 16 || forced == 32 || forced == 64) return forced;
+  return M <= 256 ? 16 : HD_ROWS_MAX;
+}
 
 }  // namespace
 
