@@ -191,6 +191,97 @@ __global__ void __launch_bounds__(ST, (MODE == 1) ? 1 : 2) colstats_bf16_kernel(
   if (threadIdx.x == 0) a.counters[blockIdx.x] = 0u;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Batch-norm statistics from the partial column sums a GEMM epilogue left behind (psum / psq: fp32 [G][C],
+// one row per 32 output rows; gemm_tcgen05_persistent.cu). Same two-phase deterministic scheme as
+// colstats_bf16_kernel, over 1/8 of the bytes of the tensor itself; finalises exactly like MODE 0.
+// block = 256 threads = (cw/4 lanes of 4 channels) x (1024/cw rows); grid = (C/cw, row blocks).
+// ---------------------------------------------------------------------------------------------------
+struct PartArgs {
+  const float* psum; const float* psq; int G; long M; int C; int cw;
+  float* partials; unsigned* counters;
+  float* mean; float* invstd; float* scale; float* shift; float* moving_mean; float* moving_var;
+  const float* gamma; const float* beta; float momentum, eps; int unbiased;
+};
+
+__global__ void __launch_bounds__(256) bn_finalize_partials_kernel(const PartArgs a) {
+  TFDE_PDL_PROLOGUE();
+  __shared__ float4 sa[256], sb[256];
+  __shared__ double dsa[1024], dsb[1024];
+  __shared__ int s_last;
+  const int cw = a.cw, lanes = cw >> 2, rows = 256 / lanes;
+  const int tx = threadIdx.x % lanes, ty = threadIdx.x / lanes;
+  const int c0 = blockIdx.x * cw + tx * 4;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = s;
+  const int stride = gridDim.y * rows;
+  int g = blockIdx.y * rows + ty;
+  for (; g + 3 * stride < a.G; g += 4 * stride) {
+    float4 vs[4], vq[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      vs[u] = __ldg(reinterpret_cast<const float4*>(a.psum + (size_t)(g + u * stride) * a.C + c0));
+      vq[u] = __ldg(reinterpret_cast<const float4*>(a.psq + (size_t)(g + u * stride) * a.C + c0));
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      s.x += vs[u].x; s.y += vs[u].y; s.z += vs[u].z; s.w += vs[u].w;
+      q.x += vq[u].x; q.y += vq[u].y; q.z += vq[u].z; q.w += vq[u].w;
+    }
+  }
+  for (; g < a.G; g += stride) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(a.psum + (size_t)g * a.C + c0));
+    const float4 w = __ldg(reinterpret_cast<const float4*>(a.psq + (size_t)g * a.C + c0));
+    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; q.x += w.x; q.y += w.y; q.z += w.z; q.w += w.w;
+  }
+  sa[threadIdx.x] = s; sb[threadIdx.x] = q;
+  __syncthreads();
+  float* part = a.partials + ((size_t)blockIdx.x * gridDim.y + blockIdx.y) * 2 * cw;
+  if (ty == 0) {
+    for (int r = 1; r < rows; ++r) {
+      const float4 v = sa[r * lanes + tx], w = sb[r * lanes + tx];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; q.x += w.x; q.y += w.y; q.z += w.z; q.w += w.w;
+    }
+    __stcg(reinterpret_cast<float4*>(part + tx * 4), s);
+    __stcg(reinterpret_cast<float4*>(part + cw + tx * 4), q);
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(a.counters + blockIdx.x, 1u) == gridDim.y - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  {
+    double ds[4] = {0.0, 0.0, 0.0, 0.0}, dq[4] = {0.0, 0.0, 0.0, 0.0};
+    const float* base = a.partials + (size_t)blockIdx.x * gridDim.y * 2 * cw;
+    for (unsigned rb = ty; rb < gridDim.y; rb += rows) {
+      const float* pp = base + (size_t)rb * 2 * cw;
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(pp + tx * 4));
+      const float4 w = __ldcg(reinterpret_cast<const float4*>(pp + cw + tx * 4));
+      ds[0] += (double)v.x; ds[1] += (double)v.y; ds[2] += (double)v.z; ds[3] += (double)v.w;
+      dq[0] += (double)w.x; dq[1] += (double)w.y; dq[2] += (double)w.z; dq[3] += (double)w.w;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { dsa[ty * cw + tx * 4 + j] = ds[j]; dsb[ty * cw + tx * 4 + j] = dq[j]; }
+    __syncthreads();
+  }
+  for (int cl = threadIdx.x; cl < cw; cl += 256) {
+    const int c = blockIdx.x * cw + cl;
+    double ds = 0.0, dq = 0.0;
+    for (int r = 0; r < rows; ++r) { ds += dsa[r * cw + cl]; dq += dsb[r * cw + cl]; }
+    const double mean = ds / (double)a.M;
+    double var = dq / (double)a.M - mean * mean;
+    if (var < 0.0) var = 0.0;
+    const float inv = rsqrtf((float)var + a.eps);
+    a.mean[c] = (float)mean; a.invstd[c] = inv;
+    const float sc = (a.gamma ? a.gamma[c] : 1.f) * inv;
+    a.scale[c] = sc; a.shift[c] = (a.beta ? a.beta[c] : 0.f) - (float)mean * sc;
+    const double vm = (a.unbiased && a.M > 1) ? var * ((double)a.M / (double)(a.M - 1)) : var;
+    a.moving_mean[c] = a.moving_mean[c] * a.momentum + (float)mean * (1.f - a.momentum);
+    a.moving_var[c] = a.moving_var[c] * a.momentum + (float)vm * (1.f - a.momentum);
+  }
+  if (threadIdx.x == 0) a.counters[blockIdx.x] = 0u;
+}
+
 // y = relu?(x * scale + shift)   (scale = gamma*invstd, shift = beta - mean*scale)
 __global__ void bn_apply_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long n8,
                                      int C, const float* __restrict__ scale, const float* __restrict__ shift,
@@ -646,6 +737,33 @@ TFDE_API int tfde_bn_fwd_train_bf16(const void* x, void* y, long M, int C, const
 }
 
 // y = relu?(x*scale + shift) with caller-provided per-channel scale/shift (inference with moving statistics).
+// Batch-norm training forward when the producing GEMM already left per-32-row partial statistics
+// (tfde_gemm_bf16_nn_stats_persistent): reduce the [G][C] partials, finalise, apply. x is read ONCE.
+TFDE_API int tfde_bn_fwd_from_partials_bf16(const void* x, void* y, long M, int C, const float* psum, const float* psq,
+                                            int G, const float* gamma, const float* beta, float* moving_mean,
+                                            float* moving_var, float momentum, float eps, int relu,
+                                            int unbiased_moving, float* save_mean, float* save_invstd, float* scale,
+                                            float* shift, float* ws, size_t ws_floats, unsigned* counters,
+                                            cudaStream_t stream) {
+  if ((C & 63) || G <= 0 || !psum || !psq) return TFDE_ERR_INVALID;
+  PartArgs a{};
+  a.psum = psum; a.psq = psq; a.G = G; a.M = M; a.C = C; a.cw = (C % 128 == 0) ? 128 : 64;
+  a.mean = save_mean; a.invstd = save_invstd; a.scale = scale; a.shift = shift;
+  a.moving_mean = moving_mean; a.moving_var = moving_var; a.gamma = gamma; a.beta = beta;
+  a.momentum = momentum; a.eps = eps; a.unbiased = unbiased_moving;
+  const int ctiles = C / a.cw, rows = 256 / (a.cw / 4);
+  int rb = (G + rows * 4 - 1) / (rows * 4);
+  if (rb > 64) rb = 64;
+  if (rb < 1) rb = 1;
+  if ((size_t)ctiles * rb * 2 * a.cw > ws_floats || ctiles > TFDE_MAX_COUNTERS) return TFDE_ERR_INVALID;
+  a.partials = ws; a.counters = counters;
+  tfde_launch(bn_finalize_partials_kernel, dim3(ctiles, rb), dim3(256), 0, stream, a);
+  const long n8 = M * C / 8;
+  tfde_launch(bn_apply_bf16_kernel, dim3(ew_blocks(n8)), dim3(256), 0, stream, (const __nv_bfloat16*)x,
+              (__nv_bfloat16*)y, n8, C, (const float*)scale, (const float*)shift, relu);
+  TFDE_RETURN_LAUNCH_STATUS();
+}
+
 TFDE_API int tfde_bn_apply_bf16(const void* x, void* y, long M, int C, const float* scale, const float* shift,
                                 int relu, cudaStream_t stream) {
   if (C & 7) return TFDE_ERR_INVALID;

@@ -85,6 +85,10 @@ struct PEpilogue {
   float* c_f32; __nv_bfloat16* c_bf16; long ldc;
   const float* bias; int relu;
   int M, N;
+  // optional fused batch-norm statistics (bf16 output, staged path, no split-K): per 32-row group partial
+  // column sums / sums of squares of the ROUNDED outputs, [ceil(M/32)][N] each -- the consumer of a
+  // convolution's output is a batch-norm whose first pass would otherwise re-read the whole tensor
+  float* stat_sum; float* stat_sq;
 };
 
 // MNMAJ is a bit mask: bit 0 = A is MN-major (stored [K, M], M contiguous), bit 1 = B is MN-major (stored
@@ -256,6 +260,25 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
             }
           }
           __syncwarp();
+          if (ep.stat_sum != nullptr && out16) {
+            // fused batch-norm statistics: lane owns columns 2*lane, 2*lane+1 of the 64-column slab and walks
+            // the 32 staged rows (4-byte conflict-free reads of the rounded bf16 pairs)
+            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+            const int nrows = min(32, ep.M - row0);
+#pragma unroll 8
+            for (int rr = 0; rr < 32; ++rr) {
+              if (rr < nrows) {
+                const uint32_t pr = *reinterpret_cast<const uint32_t*>(stg + rr * P_STG_PITCH + lane * 4);
+                const float a = __uint_as_float(pr << 16), b = __uint_as_float(pr & 0xffff0000u);
+                s0 += a; s1 += b; q0 = fmaf(a, a, q0); q1 = fmaf(b, b, q1);
+              }
+            }
+            if (nrows > 0) {
+              const size_t o = (size_t)(row0 >> 5) * ep.N + nbase + 2 * lane;
+              *reinterpret_cast<float2*>(ep.stat_sum + o) = make_float2(s0, s1);
+              *reinterpret_cast<float2*>(ep.stat_sq + o) = make_float2(q0, q1);
+            }
+          }
           uint8_t* gbase = out16 ? reinterpret_cast<uint8_t*>(ep.c_bf16 + nbase) : reinterpret_cast<uint8_t*>(ep.c_f32 + nbase);
           const size_t gpitch = (size_t)ep.ldc * (out16 ? 2 : 4);
 #pragma unroll
@@ -598,4 +621,30 @@ TFDE_API int tfde_gemm_bf16_nn_persistent(const void* A, const void* B, float* c
   if (BN == 64) return p_launch<64, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
   if (BN == 128) return p_launch<128, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
   return p_launch<256, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+}
+
+// Same GEMM with bf16 output only, plus the batch-norm statistics of that output fused into the epilogue:
+// stat_sum / stat_sq [ceil(M/32)][N] receive per-32-row-group column sums and sums of squares of the ROUNDED
+// values (what the batch-norm will read back). No split-K (partial tiles have no statistics): use it when the
+// output has enough tiles to fill the machine. N % 64 == 0, ldc % 8 == 0.
+TFDE_API int tfde_gemm_bf16_nn_stats_persistent(const void* A, const void* B, void* c_bf16, long ldc, const float* bias,
+                                                int M, int N, int K, int kb, long ldb, float* stat_sum,
+                                                float* stat_sq, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || (K & 7) || (N & 63) || (ldc & 7) || (ldb & 7) || ldb < N || kb <= 0 || kb > K ||
+      !A || !B || !c_bf16 || !stat_sum || !stat_sq)
+    return TFDE_ERR_INVALID;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15) ||
+      (reinterpret_cast<uintptr_t>(c_bf16) & 15) || (reinterpret_cast<uintptr_t>(stat_sum) & 7) ||
+      (reinterpret_cast<uintptr_t>(stat_sq) & 7))
+    return TFDE_ERR_INVALID;
+  const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+  CUtensorMap ta, tb;
+  int rc = p_make_map(&ta, A, M, K, P_BM);
+  if (rc != 0) return rc;
+  rc = p_make_map_ld(&tb, B, kb, N, ldb, P_BK, 64);
+  if (rc != 0) return rc;
+  PEpilogue ep{nullptr, (__nv_bfloat16*)c_bf16, ldc, bias, 0, M, N, stat_sum, stat_sq};
+  if (BN == 64) return p_launch<64, 2>(ta, tb, ep, M, N, K, nullptr, 0, stream);
+  if (BN == 128) return p_launch<128, 2>(ta, tb, ep, M, N, K, nullptr, 0, stream);
+  return p_launch<256, 2>(ta, tb, ep, M, N, K, nullptr, 0, stream);
 }

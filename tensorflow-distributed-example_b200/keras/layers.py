@@ -254,8 +254,15 @@ class Conv2D(Layer):
                                            self.out_shape[1], x.dtype == torch.bfloat16)
             self._a_cache = (self.buf("a16", ashape, torch.bfloat16)
                              if ashape is not None and training and _CACHE_IM2COL else None)
+            # feeding a training-mode batch-norm: the GEMM epilogue leaves its partial statistics behind
+            self._bn_partials = None
+            if training and x.is_cuda and getattr(self, "feeds_bn", False):
+                pshape = act16.bn_partials_shape(x.shape, self.kernel.shape, self.out_shape[0], self.out_shape[1])
+                if pshape is not None:
+                    self._bn_partials = (self.buf("bn_psum", pshape), self.buf("bn_psq", pshape))
             act16.conv2d_fwd(x, self.kernel.value, self.bias.value if self.bias else None, self.strides,
-                             self.pads, out=y, a_cache=self._a_cache, w16=getattr(self.kernel, "value16", None))
+                             self.pads, out=y, a_cache=self._a_cache, w16=getattr(self.kernel, "value16", None),
+                             bn_partials=self._bn_partials)
             self._y = y
             return y
         y = self.buf("y", (b,) + self.out_shape)
@@ -490,10 +497,13 @@ class BatchNormalization(Layer):
             from ..ops import act16
             y = self.buf("y16", x.shape, torch.bfloat16)
             sc, sh = self.buf("scale", (c,)), self.buf("shift", (c,))
+            src = getattr(self, "stats_source", None)      # the convolution whose GEMM already reduced x
+            partials = (src._bn_partials if training and src is not None and getattr(src, "_y", None) is x
+                        and getattr(src, "_bn_partials", None) is not None else None)
             act16.bn_fwd(x, self.gamma.value if self.gamma else None, self.beta.value if self.beta else None,
                          self.moving_mean.value, self.moving_variance.value, self.momentum, self.epsilon,
                          training, self.fused_relu, self.unbiased_moving, out=y, save_mean=sm, save_invstd=si,
-                         scale=sc, shift=sh)
+                         scale=sc, shift=sh, partials=partials)
             self._y, self._sm, self._si, self._sc, self._sh = y, sm, si, sc, sh
             return y
         y = self.buf("y", x.shape)

@@ -236,6 +236,7 @@ class Sequential:
                 # d(loss)/d(bias) of a convolution feeding a training-mode batch-norm is identically zero
                 # (batch-norm removes any per-channel shift); the bf16-activation path skips that reduction
                 cur.bias_grad_zero = True
+                cur.feeds_bn, nxt.stats_source = True, cur     # BN statistics come out of the conv GEMM's epilogue
             plan.append(cur)
             i += 1
         self.exec_plan = plan

@@ -44,6 +44,8 @@ class Bottleneck(L.Layer):
         self.b3 = self._mk(L.BatchNormalization(epsilon=1.001e-5), "3_bn")
         self.b1.fused_relu = self.b2.fused_relu = True
         self.c1.bias_grad_zero = self.c2.bias_grad_zero = self.c3.bias_grad_zero = True   # each feeds a batch-norm
+        for conv, bn in ((self.c1, self.b1), (self.c2, self.b2), (self.c3, self.b3)):
+            conv.feeds_bn, bn.stats_source = True, conv       # BN statistics come out of the conv GEMM's epilogue
         shape = tuple(in_shape)
         for l in (self.c1, self.b1, self.c2, self.b2, self.c3, self.b3):
             shape = l.build(shape)
@@ -51,6 +53,7 @@ class Bottleneck(L.Layer):
             self.c0 = self._mk(L.Conv2D(f * e, 1, strides=self.stride), "0_conv")
             self.b0 = self._mk(L.BatchNormalization(epsilon=1.001e-5), "0_bn")
             self.c0.bias_grad_zero = True
+            self.c0.feeds_bn, self.b0.stats_source = True, self.c0
             s0 = self.b0.build(self.c0.build(tuple(in_shape)))
             if s0 != shape:
                 raise ValueError(f"{self.name}: shortcut {s0} != main {shape}")

@@ -24,12 +24,15 @@ c_p, c_i, c_l, c_f, c_z = native.c_p, native.c_i, native.c_l, native.c_f, native
 BF = torch.bfloat16
 _WGRAD_NT = __import__("os").environ.get("TFDE_WGRAD_NT", "1") == "1"   # MN-major filter-gradient GEMM
 _FWD_NN = __import__("os").environ.get("TFDE_FWD_NN", "1") == "1"       # forward GEMM on untransposed weights
+_FUSE_BN_STATS = __import__("os").environ.get("TFDE_FUSE_BN_STATS", "1") == "1"   # BN statistics in the GEMM epilogue
 
 for _n, _a in [
     ("tfde_act16_supported_channels", [c_i]),
     ("tfde_bn_fwd_train_bf16", [c_p, c_p, c_l, c_i, c_p, c_p, c_p, c_p, c_f, c_f, c_i, c_i, c_p, c_p, c_p, c_p,
                                 c_p, c_z, c_p, c_p]),
     ("tfde_bn_apply_bf16", [c_p, c_p, c_l, c_i, c_p, c_p, c_i, c_p]),
+    ("tfde_bn_fwd_from_partials_bf16", [c_p, c_p, c_l, c_i, c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_f, c_f, c_i, c_i,
+                                        c_p, c_p, c_p, c_p, c_p, c_z, c_p, c_p]),
     ("tfde_bn_bwd_bf16", [c_p, c_p, c_p, c_l, c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_p, c_p, c_p, c_z, c_p, c_p]),
     ("tfde_colsum_bf16", [c_p, c_l, c_i, c_p, c_p, c_z, c_p, c_p]),
     ("tfde_add_bf16", [c_p, c_p, c_p, c_l, c_i, c_p]),
@@ -69,8 +72,9 @@ def _empty_like_bf(t, out):
 # batch normalisation
 # ----------------------------------------------------------------------------------------------
 def bn_fwd(x, gamma, beta, moving_mean, moving_var, momentum, eps, training, relu, unbiased_moving,
-           out=None, save_mean=None, save_invstd=None, scale=None, shift=None):
-    """x, out: bf16 [..., C]. Updates the moving statistics in place when training. Returns
+           out=None, save_mean=None, save_invstd=None, scale=None, shift=None, partials=None):
+    """x, out: bf16 [..., C]. Updates the moving statistics in place when training. ``partials`` = (psum, psq)
+    per-32-row partial statistics left by the producing GEMM (CUDA): x is then read once. Returns
     (y, save_mean, save_invstd, scale, shift); scale/shift are the folded per-channel affine that the
     backward uses to recompute the fused-ReLU mask from x."""
     C = x.shape[-1]
@@ -99,7 +103,17 @@ def bn_fwd(x, gamma, beta, moving_mean, moving_var, momentum, eps, training, rel
         return y, save_mean, save_invstd, scale, shift
     L = native.load()
     y = _empty_like_bf(x, out)
-    if training:
+    if training and partials is not None:
+        psum, psq = partials
+        _, ws, wsn, cnt = _ws(dev)
+        native.check(L.tfde_bn_fwd_from_partials_bf16(x.data_ptr(), y.data_ptr(), M, C, psum.data_ptr(), psq.data_ptr(),
+                                                      psum.shape[0], native.ptr(gamma), native.ptr(beta),
+                                                      moving_mean.data_ptr(), moving_var.data_ptr(), momentum, eps,
+                                                      1 if relu else 0, 1 if unbiased_moving else 0,
+                                                      save_mean.data_ptr(), save_invstd.data_ptr(), scale.data_ptr(),
+                                                      shift.data_ptr(), ws, wsn, cnt, native.stream_ptr()),
+                     "bn_fwd_from_partials_bf16")
+    elif training:
         _, ws, wsn, cnt = _ws(dev)
         native.check(L.tfde_bn_fwd_train_bf16(x.data_ptr(), y.data_ptr(), M, C, native.ptr(gamma), native.ptr(beta),
                                               moving_mean.data_ptr(), moving_var.data_ptr(), momentum, eps,
@@ -319,8 +333,19 @@ def _a_operand(x, w_shape, stride, pads, ho, wo, tag, cache=None, reuse=False):
     return a, kp
 
 
-def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None, a_cache=None, w16=None):
-    """x: bf16 NHWC (or the fp32 network input); w: fp32 HWIO; returns bf16 NHWC."""
+def bn_partials_shape(x_shape, w_shape, ho, wo):
+    """[G, cout] of the partial-statistics buffers conv2d_fwd can fill for a following batch-norm, or None when
+    the fused-statistics GEMM does not apply (small outputs keep split-K and the separate statistics kernel)."""
+    M, cout = x_shape[0] * ho * wo, w_shape[3]
+    if not (_FWD_NN and _FUSE_BN_STATS and tensorcore.nn_stats_eligible(M, cout)):
+        return None
+    return ((M + 31) // 32, cout)
+
+
+def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None, a_cache=None, w16=None,
+               bn_partials=None):
+    """x: bf16 NHWC (or the fp32 network input); w: fp32 HWIO; returns bf16 NHWC.
+    ``bn_partials`` = (psum, psq) fp32 [G, cout] buffers (see bn_partials_shape): CUDA only, filled by the GEMM."""
     b, h, wd, c = x.shape
     kh, kw, _, cout = w.shape
     ho = (h + pads[0] + pads[1] - kh) // stride[0] + 1
@@ -340,7 +365,11 @@ def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None, a_ca
         # only per-step weight work is a flat fp32 -> bf16 cast (padded im2col columns meet zero-filled rows)
         wb = w16 if w16 is not None else cast_bf16_masked(w.reshape(kc, cout), None,
                                                           out=_scratch(x.device, "B", kc * cout).view(kc, cout))
-        tensorcore.gemm_bf16_nn(a, wb.reshape(kc, cout), bias, False, BF, out=y.view(M, cout))
+        if bn_partials is not None:
+            # the consumer is a training-mode batch-norm: leave its per-32-row partial statistics behind
+            tensorcore.gemm_bf16_nn_stats(a, wb.reshape(kc, cout), bias, y.view(M, cout), bn_partials[0], bn_partials[1])
+        else:
+            tensorcore.gemm_bf16_nn(a, wb.reshape(kc, cout), bias, False, BF, out=y.view(M, cout))
         return y
     wt = _scratch(x.device, "B", cout * kp).view(cout, kp)
     native.check(L.tfde_cast_transpose_pad_bf16(w.data_ptr(), None, wt.data_ptr(), kc, cout, kp, native.stream_ptr()),

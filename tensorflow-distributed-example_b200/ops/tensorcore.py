@@ -108,3 +108,31 @@ def gemm_bf16_nn(a, b, bias=None, relu=False, out_dtype=torch.float32, out=None)
                                                 1 if relu else 0, M, N, K, Kb, b.stride(0), wsp.ws.data_ptr(),
                                                 wsp.ws_bytes, native.stream_ptr()), "gemm_bf16_nn[persistent]")
     return c
+
+
+native.register_optional("tfde_gemm_bf16_nn_stats_persistent",
+                         [c_p, c_p, c_p, c_l, c_p, c_i, c_i, c_i, c_i, c_l, c_p, c_p, c_p])
+
+
+def nn_stats_eligible(M: int, N: int) -> bool:
+    """The fused-statistics GEMM runs without split-K: worth it only when the output alone fills the machine."""
+    bn = 64 if N <= 64 else (128 if N <= 128 else 256)
+    return N % 64 == 0 and ((M + 127) // 128) * ((N + bn - 1) // bn) >= 148
+
+
+def gemm_bf16_nn_stats(a, b, bias, out, stat_sum, stat_sq):
+    """gemm_bf16_nn with bf16 output whose epilogue also leaves per-32-row partial column sums / sums of squares
+    of the rounded output in ``stat_sum`` / ``stat_sq`` (fp32 [ceil(M/32), N]): the batch-norm that consumes the
+    output finalises its statistics from those instead of re-reading the tensor."""
+    L = native.load()
+    M, K = a.shape
+    Kb, N = b.shape
+    G = (M + 31) // 32
+    if (out.dtype != torch.bfloat16 or stat_sum.shape != (G, N) or stat_sq.shape != (G, N)
+            or stat_sum.dtype != torch.float32 or not a.is_contiguous() or b.stride(1) != 1):
+        raise ValueError("gemm_bf16_nn_stats: bad operands")
+    native.check(L.tfde_gemm_bf16_nn_stats_persistent(a.data_ptr(), b.data_ptr(), out.data_ptr(), out.stride(0),
+                                                      native.ptr(bias), M, N, K, Kb, b.stride(0), stat_sum.data_ptr(),
+                                                      stat_sq.data_ptr(), native.stream_ptr()),
+                 "gemm_bf16_nn_stats[persistent]")
+    return out

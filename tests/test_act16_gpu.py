@@ -204,3 +204,34 @@ def test_gemm_nn_weights_as_stored(M, K, Kb, N):
     ref = torch.relu(a[:, :Kb].float() @ b.float() + bias)
     torch.cuda.synchronize()
     _close(c, ref, 2e-2, 2e-2 * (K ** 0.5) / 8)
+
+
+@pytest.mark.parametrize("B,H,C,Co", [(16, 56, 64, 256), (13, 40, 64, 64)])
+def test_bn_statistics_fused_into_conv_gemm(B, H, C, Co):
+    """conv (1x1) -> training batch-norm with the statistics taken from the GEMM epilogue's partial sums equals the
+    two-pass batch-norm on the same convolution output (same rounded tensor, fp32/fp64 reductions both ways)."""
+    from tfde_b200.ops import act16
+    dev = _dev()
+    g = torch.Generator().manual_seed(B + Co)
+    x = torch.randn(B, H, H, C, generator=g).to(BF).to(dev)
+    w = (torch.randn(1, 1, C, Co, generator=g) * 0.1).to(dev)
+    bias = (torch.randn(Co, generator=g) * 0.1).to(dev)
+    gamma, beta = (torch.rand(Co, generator=g) + 0.5).to(dev), (torch.randn(Co, generator=g) * 0.1).to(dev)
+    pshape = act16.bn_partials_shape(tuple(x.shape), tuple(w.shape), H, H)
+    assert pshape is not None and pshape == ((B * H * H + 31) // 32, Co)
+    psum, psq = torch.zeros(pshape, device=dev), torch.zeros(pshape, device=dev)
+    y1 = act16.conv2d_fwd(x, w, bias, (1, 1), (0, 0, 0, 0), bn_partials=(psum, psq))
+    y2 = act16.conv2d_fwd(x, w, bias, (1, 1), (0, 0, 0, 0))
+    assert torch.equal(y1, y2)
+    mm1, mv1 = torch.zeros(Co, device=dev), torch.ones(Co, device=dev)
+    mm2, mv2 = torch.zeros(Co, device=dev), torch.ones(Co, device=dev)
+    o1 = act16.bn_fwd(y1, gamma, beta, mm1, mv1, 0.99, 1e-3, True, True, True, partials=(psum, psq))
+    o2 = act16.bn_fwd(y2, gamma, beta, mm2, mv2, 0.99, 1e-3, True, True, True)
+    torch.cuda.synchronize()
+    ref_sum = y1.float().reshape(-1, Co).sum(0)
+    _close(psum.sum(0), ref_sum, 1e-4, 1e-2)
+    for a, b in zip(o1[1:], o2[1:]):          # save_mean, save_invstd, scale, shift
+        _close(a, b, 1e-5, 1e-6)
+    _close(mm1, mm2, 1e-5, 1e-7)
+    _close(mv1, mv2, 1e-5, 1e-7)
+    _close(o1[0], o2[0], 1e-2, 1e-2)
