@@ -28,15 +28,15 @@ conv3x3c1_relu_pool_fwd_kernel(const void* __restrict__ xin, const float* __rest
 #pragma unroll
   for (int i = 0; i < 9; ++i) wr[i] = __ldg(w + i * 32 + lane);
   const float b = bias ? __ldg(bias + lane) : 0.f;
-  const long total = (long)Bn * PH * PW;
-  for (long p = (long)blockIdx.x * WARPS + warp; p < total; p += (long)gridDim.x * WARPS) {
-    const int pw = (int)(p % PW);
-    const long t = p / PW;
-    const int ph = (int)(t % PH);
-    const long bi = t / PH;
+  // 32-bit index arithmetic (the host rejects Bn*PH*PW >= 2^31): emulated 64-bit div/mod was most of the
+  // instruction count of this loop at large batch
+  const unsigned total = (unsigned)Bn * (unsigned)PH * (unsigned)PW, uPW = (unsigned)PW, uPH = (unsigned)PH;
+  for (unsigned p = blockIdx.x * WARPS + warp; p < total; p += gridDim.x * WARPS) {
+    const unsigned t = p / uPW, pw = p - t * uPW;
+    const unsigned bi = t / uPH, ph = t - bi * uPH;
     float v = 0.f;
     if (lane < 16) {
-      const long off = (bi * H + (2 * ph + (lane >> 2))) * W + (2 * pw + (lane & 3));
+      const size_t off = ((size_t)bi * H + (2 * ph + (lane >> 2))) * W + (2 * pw + (lane & 3));
       if (U8) v = (float)__ldg(reinterpret_cast<const uint8_t*>(xin) + off) * in_scale;
       else    v = __ldg(reinterpret_cast<const float*>(xin) + off);
     }
@@ -57,8 +57,8 @@ conv3x3c1_relu_pool_fwd_kernel(const void* __restrict__ xin, const float* __rest
         o = fmaxf(o, 0.f);
         if (o > best) { best = o; besti = dy * 2 + dx; }
       }
-    pooled[p * 32 + lane] = best;
-    idx[p * 32 + lane] = (uint8_t)besti;
+    pooled[(size_t)p * 32 + lane] = best;
+    idx[(size_t)p * 32 + lane] = (uint8_t)besti;
   }
 }
 
@@ -78,27 +78,25 @@ conv3x3c1_relu_pool_bwd_kernel(const void* __restrict__ xin, const float* __rest
   float acc[10];
 #pragma unroll
   for (int i = 0; i < 10; ++i) acc[i] = 0.f;
-  const long total = (long)Bn * PH * PW;
-  const long stride = (long)gridDim.x * WARPS;
-  // Software-pipelined: the loads of pixel p+stride are issued before pixel p is consumed.
-  auto fetch = [&](long p, float& xv, float& g, int& bsel) {
+  const unsigned total = (unsigned)Bn * (unsigned)PH * (unsigned)PW, uPW = (unsigned)PW, uPH = (unsigned)PH;
+  const unsigned stride = gridDim.x * WARPS;
+  // Software-pipelined: the loads of pixel p+stride are issued before pixel p is consumed. 32-bit indices.
+  auto fetch = [&](unsigned p, float& xv, float& g, int& bsel) {
     xv = 0.f; g = 0.f; bsel = 0;
     if (p >= total) return;
-    const int pw = (int)(p % PW);
-    const long t = p / PW;
-    const int ph = (int)(t % PH);
-    const long bi = t / PH;
+    const unsigned t = p / uPW, pw = p - t * uPW;
+    const unsigned bi = t / uPH, ph = t - bi * uPH;
     if (lane < 16) {
-      const long off = (bi * H + (2 * ph + (lane >> 2))) * W + (2 * pw + (lane & 3));
+      const size_t off = ((size_t)bi * H + (2 * ph + (lane >> 2))) * W + (2 * pw + (lane & 3));
       if (U8) xv = (float)__ldg(reinterpret_cast<const uint8_t*>(xin) + off) * in_scale;
       else    xv = __ldg(reinterpret_cast<const float*>(xin) + off);
     }
-    g = __ldg(dpooled + p * 32 + lane);
-    if (!(__ldg(pooled + p * 32 + lane) > 0.f)) g = 0.f;
-    bsel = idx[p * 32 + lane];
+    g = __ldg(dpooled + (size_t)p * 32 + lane);
+    if (!(__ldg(pooled + (size_t)p * 32 + lane) > 0.f)) g = 0.f;
+    bsel = idx[(size_t)p * 32 + lane];
   };
   float xv_n, g_n; int b_n;
-  long p = (long)blockIdx.x * WARPS + warp;
+  unsigned p = blockIdx.x * WARPS + warp;
   fetch(p, xv_n, g_n, b_n);
   for (; p < total; p += stride) {
     const float xv = xv_n, g = g_n; const int bsel = b_n;
@@ -177,6 +175,7 @@ TFDE_API int tfde_conv3x3c1_relu_pool_fwd(const void* x, int x_is_u8, float in_s
                                           cudaStream_t stream) {
   if (Cout != 32 || H < 4 || W < 4) return TFDE_ERR_INVALID;
   const int PH = (H - 2) / 2, PW = (W - 2) / 2;
+  if ((long)Bn * PH * PW >= (1L << 31) - 148L * 64 * WARPS) return TFDE_ERR_INVALID;           // 32-bit pixel index
   const int grid = grid_for((long)Bn * PH * PW);
   if (x_is_u8)
     tfde_launch(conv3x3c1_relu_pool_fwd_kernel<true>, dim3(grid), dim3(WARPS * 32), 0, stream, x, w, bias, pooled, idx, Bn, H, W, PH, PW, in_scale);
@@ -197,7 +196,11 @@ TFDE_API int tfde_conv3x3c1_relu_pool_bwd(const void* x, int x_is_u8, float in_s
   const int PH = (H - 2) / 2, PW = (W - 2) / 2;
   long blocks = ((long)Bn * PH * PW + WARPS * 4 - 1) / (WARPS * 4);  // >= 4 pixels per warp
   if (blocks < 1) blocks = 1;
-  if (blocks > 148L * 2) blocks = 148L * 2;
+  // latency-bound streaming reduction: large batches get 4 resident blocks per SM (the partials buffer holds
+  // 592 rows); the batch-64 operating point keeps 2 (shorter last-block finalise)
+  const long cap = ((long)Bn * PH * PW > 200000L) ? 148L * 4 : 148L * 2;
+  if (blocks > cap) blocks = cap;
+  if ((long)Bn * PH * PW >= (1L << 31) - 148L * 4 * WARPS) return TFDE_ERR_INVALID;   // 32-bit pixel index
   const int grid = (int)blocks;
   if (x_is_u8)
     tfde_launch(conv3x3c1_relu_pool_bwd_kernel<true>, dim3(grid), dim3(WARPS * 32), 0, stream, x, pooled, idx, dpooled, dw, db, partials, counter, Bn, H, W, PH, PW, in_scale);
