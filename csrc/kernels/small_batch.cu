@@ -319,6 +319,121 @@ int head_rows_per_block(int M) {
   return M <= 256 ? 16 : HD_ROWS_MAX;
 }
 
+// ================================================================================================
+// 3. skinny dense backward: dx, dW and db of Dense(K -> 64) at batch <= 64 in ONE launch
+// ================================================================================================
+// The batch-64 operating point of the reference (distributed_with_keras.py:37: Dense(64) on 5408 features).
+// The generic GEMM path runs the filter gradient and the data gradient as two 85-block kernels of ~17 us each
+// (forked); both are one 64x64x64 tile per block and pure latency. Here block b owns input features
+// [64b, 64b+64): it stages g = dy * (y > 0) [64 x 64] once, then
+//   dx[m, k] = sum_n g[m, n] * W[k, n]   (W rows k are contiguous: the Keras (in, out) layout)
+//   dW[k, n] = sum_m x[m, k] * g[m, n]
+// with the second operand tile re-using the same shared memory, and block 0 also writes db = sum_m g.
+// Thread (ty, tx) of 16x16 owns the 4x4 outputs {ty+16i} x {tx+16j}: conflict-free shared reads, coalesced
+// 64-byte global segments. Deterministic (no split, fixed order).
+constexpr int SB_T = 64;
+__global__ void __launch_bounds__(256)
+dense_bwd_skinny_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ dy,
+                        const float* __restrict__ ymask, float* __restrict__ dx, float* __restrict__ dw,
+                        float* __restrict__ db, int M, int K) {
+  TFDE_PDL_PROLOGUE();
+  __shared__ float gs[SB_T][SB_T + 1];      // g[m][n]
+  __shared__ float ts[SB_T][SB_T + 1];      // W tile [k][n], then x tile [m][k]
+  const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+  const int k0 = blockIdx.x * SB_T;
+  // stage g and the W tile (float4 global loads, scalar shared stores because of the +1 padding)
+  for (int e = t; e < SB_T * SB_T / 4; e += 256) {
+    const int r = e >> 4, c4 = (e & 15) << 2;
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < M) {
+      g = __ldg(reinterpret_cast<const float4*>(dy + (size_t)r * SB_T + c4));
+      if (ymask != nullptr) {
+        const float4 y = __ldg(reinterpret_cast<const float4*>(ymask + (size_t)r * SB_T + c4));
+        if (!(y.x > 0.f)) g.x = 0.f; if (!(y.y > 0.f)) g.y = 0.f; if (!(y.z > 0.f)) g.z = 0.f; if (!(y.w > 0.f)) g.w = 0.f;
+      }
+    }
+    gs[r][c4] = g.x; gs[r][c4 + 1] = g.y; gs[r][c4 + 2] = g.z; gs[r][c4 + 3] = g.w;
+    float4 wv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (k0 + r < K) wv = __ldg(reinterpret_cast<const float4*>(w + (size_t)(k0 + r) * SB_T + c4));
+    ts[r][c4] = wv.x; ts[r][c4 + 1] = wv.y; ts[r][c4 + 2] = wv.z; ts[r][c4 + 3] = wv.w;
+  }
+  // prefetch this thread's part of the x tile into registers while the data gradient is computed
+  float4 xr[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int e = t + u * 256, r = e >> 4, c4 = (e & 15) << 2;
+    xr[u] = (r < M && k0 + c4 < K) ? __ldg(reinterpret_cast<const float4*>(x + (size_t)r * K + k0 + c4))
+                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  __syncthreads();
+  if (blockIdx.x == 0 && db != nullptr && t < SB_T) {
+    float s = 0.f;
+    for (int m = 0; m < SB_T; ++m) s += gs[m][t];
+    db[t] = s;
+  }
+  float acc[4][4];
+  if (dx != nullptr) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+#pragma unroll 8
+    for (int n = 0; n < SB_T; ++n) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = gs[ty + 16 * i][n];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = ts[tx + 16 * j][n];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int m = ty + 16 * i;
+      if (m < M) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int k = k0 + tx + 16 * j;
+          if (k < K) dx[(size_t)m * K + k] = acc[i][j];
+        }
+      }
+    }
+  }
+  __syncthreads();                           // every thread is done with the W tile
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int e = t + u * 256, r = e >> 4, c4 = (e & 15) << 2;
+    ts[r][c4] = xr[u].x; ts[r][c4 + 1] = xr[u].y; ts[r][c4 + 2] = xr[u].z; ts[r][c4 + 3] = xr[u].w;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+#pragma unroll 8
+  for (int m = 0; m < SB_T; ++m) {
+    float a[4], b[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) a[i] = ts[m][ty + 16 * i];      // x[m][k], k = ty + 16 i
+#pragma unroll
+    for (int j = 0; j < 4; ++j) b[j] = gs[m][tx + 16 * j];      // g[m][n], n = tx + 16 j
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int k = k0 + ty + 16 * i;
+    if (k < K) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) dw[(size_t)k * SB_T + tx + 16 * j] = acc[i][j];
+    }
+  }
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
@@ -386,5 +501,21 @@ TFDE_API int tfde_head_fwd_bwd(const float* h, const float* w, const float* bias
   HeadParams p{h, w, bias, labels, label_is_i64, out, dh, dw, db, out4, M, K, N, relu_mask, from_probs, rpb, scale,
                partials, counter};
   tfde_launch(head_fwd_bwd_kernel, dim3((M + rpb - 1) / rpb), dim3(HD_THREADS), smem, stream, p);
+  TFDE_RETURN_LAUNCH_STATUS();
+}
+
+// 1 if tfde_dense_bwd_skinny handles this shape: batch <= 64 rows, exactly 64 units, K % 4 == 0.
+TFDE_API int tfde_dense_bwd_skinny_supported(int M, int K, int N) {
+  return (M >= 1 && M <= SB_T && N == SB_T && K >= 4 && (K & 3) == 0) ? 1 : 0;
+}
+
+// Backward of Dense(K -> 64) at batch <= 64 in one launch: dx [M,K] (may be NULL), dw [K,64], db [64] (may be
+// NULL); ymask = the layer's own output when it had a fused ReLU (gradient masked by y > 0), else NULL.
+// ref: the Dense(64, relu) of distributed_with_keras.py:37 (cuBLAS GEMMs + Eigen reduce in TF).
+TFDE_API int tfde_dense_bwd_skinny(const float* x, const float* w, const float* dy, const float* ymask, float* dx,
+                                   float* dw, float* db, int M, int K, int N, cudaStream_t stream) {
+  if (!tfde_dense_bwd_skinny_supported(M, K, N) || !x || !w || !dy || !dw) return TFDE_ERR_INVALID;
+  tfde_launch(dense_bwd_skinny_kernel, dim3((K + SB_T - 1) / SB_T), dim3(256), 0, stream, x, w, dy, ymask, dx, dw, db,
+              M, K);
   TFDE_RETURN_LAUNCH_STATUS();
 }

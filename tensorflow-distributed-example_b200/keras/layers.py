@@ -453,7 +453,7 @@ class Dense(Layer):
         scratch = self.buf("dz", dy.shape) if self.activation == "softmax" else None
         ops.dense_bwd(self._x, self.kernel.value, self._y, dy, self.activation, self.need_dx, self.use_bias,
                       out_dx=dx, out_dw=self.kernel.grad, out_db=self.bias.grad if self.bias else None,
-                      scratch=scratch, side_stream=self.model.fork_stream() if dy.is_cuda else None)
+                      scratch=scratch, side_stream=self.model.fork_stream if dy.is_cuda else None)
         return dx
 
 

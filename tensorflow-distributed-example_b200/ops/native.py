@@ -256,6 +256,11 @@ def dense_fwd(x, w, bias=None, act="none", out=None):
     return y
 
 
+_SKINNY_BWD = os.environ.get("TFDE_SKINNY_BWD", "1") == "1"
+register_optional("tfde_dense_bwd_skinny_supported", [c_i, c_i, c_i])
+register_optional("tfde_dense_bwd_skinny", [c_p] * 7 + [c_i] * 3 + [c_p])
+
+
 def dense_bwd(x, w, y, dy, act="none", need_dx=True, has_bias=True, out_dx=None, out_dw=None,
               out_db=None, scratch=None, side_stream=None):
     """``side_stream``: when given (and a data gradient is needed) the filter-gradient GEMM is forked onto
@@ -281,6 +286,14 @@ def dense_bwd(x, w, y, dy, act="none", need_dx=True, has_bias=True, out_dx=None,
         db = out_db if out_db is not None else torch.empty((N,), dtype=torch.float32, device=dev)
     from . import push as _push
     pd = _push.lookup(dw.data_ptr())
+    if (pd is None and _SKINNY_BWD and hasattr(L, "tfde_dense_bwd_skinny")
+            and L.tfde_dense_bwd_skinny_supported(M, K, N)):
+        # batch <= 64, 64 units: dx, dW and db in ONE launch (csrc/kernels/small_batch.cu) instead of two forked
+        # 85-block GEMMs -- the data gradient is on the critical path of the step
+        dx = (out_dx if out_dx is not None else torch.empty((M, K), dtype=torch.float32, device=dev)) if need_dx else None
+        check(L.tfde_dense_bwd_skinny(x.data_ptr(), w.data_ptr(), dy.data_ptr(), ptr(mask), ptr(dx), dw.data_ptr(),
+                                      ptr(db), M, K, N, stream_ptr()), "dense_bwd_skinny")
+        return dx, dw, db
 
     def launch_wgrad(ws_):
         if pd is not None:
@@ -293,6 +306,8 @@ def dense_bwd(x, w, y, dy, act="none", need_dx=True, has_bias=True, out_dx=None,
             check(L.tfde_dense_wgrad(x.data_ptr(), dy.data_ptr(), ptr(mask), dw.data_ptr(), ptr(db), M, K, N,
                                      *_gemm_tail(ws_)), "dense_wgrad")
 
+    if callable(side_stream):      # lazily created: the one-launch path above never needs it
+        side_stream = side_stream() if need_dx else None
     if side_stream is not None and need_dx:
         side_stream.wait_stream(torch.cuda.current_stream(dev))      # fork: inputs are ready
         with torch.cuda.stream(side_stream):

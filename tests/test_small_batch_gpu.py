@@ -67,3 +67,27 @@ def test_fused_head(M, K, N, probs, bias, lab):
     # relu_mask variant
     _, _, dh2, _, _ = ops.head_fwd_bwd(h.to(DEV), w.to(DEV), b.to(DEV) if bias else None, ld, scale, probs, True, True)
     _close(dh2, dx_ref * (h.double() > 0), what="head dh masked", rtol=5e-4)
+
+
+@pytest.mark.parametrize("M,K,relu,need_dx,bias", [(64, 5408, True, True, True), (33, 5408, False, True, True),
+                                                   (64, 100, True, False, False), (1, 64, True, True, True)])
+def test_dense_bwd_skinny_one_launch(M, K, relu, need_dx, bias):
+    """dx, dW, db of Dense(K -> 64) at batch <= 64 in one launch vs the fp32 PyTorch restatement (partial last
+    feature tile: 5408 = 84 * 64 + 32; partial batch; no data gradient; no bias)."""
+    L = native.load()
+    N = 64
+    assert L.tfde_dense_bwd_skinny_supported(M, K, N) == 1
+    assert L.tfde_dense_bwd_skinny_supported(65, K, N) == 0 and L.tfde_dense_bwd_skinny_supported(M, K, 32) == 0
+    x, w, dy = _rand(M, K, seed=1), _rand(K, N, seed=2) * 0.05, _rand(M, N, seed=3)
+    y = torch.relu(x @ w) if relu else x @ w
+    act = "relu" if relu else "none"
+    rdx, rdw, rdb = ref.dense_bwd(x, w, y, dy, act, need_dx, bias)
+    dx, dw, db = ops.dense_bwd(x.to(DEV), w.to(DEV), y.to(DEV), dy.to(DEV), act, need_dx, bias)
+    torch.cuda.synchronize()
+    _close(dw, rdw, what="dw")
+    if bias:
+        _close(db, rdb, what="db")
+    if need_dx:
+        _close(dx, rdx, what="dx")
+    else:
+        assert dx is None
