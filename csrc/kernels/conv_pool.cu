@@ -206,7 +206,12 @@ TFDE_API int tfde_conv3x3c1_relu_pool_bwd(const void* x, int x_is_u8, float in_s
   if (blocks < 1) blocks = 1;
   // latency-bound streaming reduction: large batches get 4 resident blocks per SM (the partials buffer holds
   // 592 rows); the batch-64 operating point keeps 2 (shorter last-block finalise)
-  const long cap = ((long)Bn * PH * PW > 200000L) ? 148L * 4 : 148L * 2;
+  long cap = ((long)Bn * PH * PW > 200000L) ? 148L * 4 : 148L * 2;
+  {
+    static long forced = -1;     // TFDE_CONVBWD_BLOCKS=<n> (1..592) overrides the cap (tuning experiments)
+    if (forced < 0) { const char* e = getenv("TFDE_CONVBWD_BLOCKS"); forced = e ? atol(e) : 0; }
+    if (forced >= 1 && forced <= 148L * 4) cap = forced;
+  }
   if (blocks > cap) blocks = cap;
   if ((long)Bn * PH * PW >= (1L << 31) - 148L * 4 * WARPS) return TFDE_ERR_INVALID;   // 32-bit pixel index
   const int grid = (int)blocks;
