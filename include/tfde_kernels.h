@@ -155,6 +155,12 @@ int tfde_head_fwd_bwd(const float* h, const float* w, const float* bias, const v
                       float* out, float* dh, float* dw, float* db, float* out4, int M, int K, int N,
                       int relu_mask, int from_probs, float scale, float* partials, unsigned* counter,
                       tfde_stream_t stream);
+/* Backward of Dense(K -> 64) at batch <= 64 in ONE launch: dx [M,K] (may be NULL), dw [K,64], db [64] (may be
+ * NULL); ymask = the layer's own output when it had a fused ReLU, else NULL. Replaces two forked 85-block
+ * GEMMs on the critical path of the batch-64 step. ref: Dense(64, relu), distributed_with_keras.py:37. */
+int tfde_dense_bwd_skinny_supported(int M, int K, int N);
+int tfde_dense_bwd_skinny(const float* x, const float* w, const float* dy, const float* ymask, float* dx, float* dw,
+                          float* db, int M, int K, int N, tfde_stream_t stream);
 
 /* ---- bf16 tensor-core GEMMs: tcgen05.mma + TMEM + TMA (gemm_tcgen05.cu, gemm_tcgen05_persistent.cu) -- */
 /* C[M,N] = act(A[M,K] . B[N,K]^T + bias); A, B bf16 with K contiguous (K % 8 == 0, 16-byte aligned);
@@ -215,6 +221,13 @@ int tfde_gemm_bf16_nn_persistent(const void* A, const void* B, float* c_f32, voi
                                  const float* bias, int relu, int M, int N, int K, int kb, long ldb, float* ws,
                                  size_t ws_bytes, tfde_stream_t stream);
 
+/* tfde_gemm_bf16_nn_persistent with bf16 output only, whose epilogue also leaves per-32-row partial column sums /
+ * sums of squares of the rounded output in stat_sum / stat_sq (fp32 [ceil(M/32)][N]) for the batch-norm that
+ * consumes it (tfde_bn_fwd_from_partials_bf16). No split-K; N % 64 == 0. */
+int tfde_gemm_bf16_nn_stats_persistent(const void* A, const void* B, void* c_bf16, long ldc, const float* bias, int M,
+                                       int N, int K, int kb, long ldb, float* stat_sum, float* stat_sq,
+                                       tfde_stream_t stream);
+
 /* ---- bf16-activation layer kernels (act_bf16.cu) ----------------------------------------------------------- */
 /* Keras mixed_bfloat16 semantics: bf16 tensors between layers, fp32 variables / statistics. All tensors are
  * channels-last with C % 8 == 0 (tfde_act16_supported_channels). `ws`/`counters`: per-stream scratch for the
@@ -228,6 +241,12 @@ int tfde_bn_fwd_train_bf16(const void* x, void* y, long M, int C, const float* g
                            float* ws, size_t ws_floats, unsigned* counters, tfde_stream_t stream);
 int tfde_bn_apply_bf16(const void* x, void* y, long M, int C, const float* scale, const float* shift, int relu,
                        tfde_stream_t stream);
+/* training forward from the partial statistics a GEMM epilogue left behind (psum / psq: fp32 [G][C]) */
+int tfde_bn_fwd_from_partials_bf16(const void* x, void* y, long M, int C, const float* psum, const float* psq, int G,
+                                   const float* gamma, const float* beta, float* moving_mean, float* moving_var,
+                                   float momentum, float eps, int relu, int unbiased_moving, float* save_mean,
+                                   float* save_invstd, float* scale, float* shift, float* ws, size_t ws_floats,
+                                   unsigned* counters, tfde_stream_t stream);
 /* backward; with relu != 0 the mask (y > 0) is recomputed as x*scale+shift > 0 instead of re-reading y */
 int tfde_bn_bwd_bf16(const void* x, const void* dy, void* dx, long M, int C, const float* gamma,
                      const float* save_mean, const float* save_invstd, const float* scale, const float* shift,
