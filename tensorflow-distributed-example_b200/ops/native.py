@@ -257,6 +257,8 @@ def dense_fwd(x, w, bias=None, act="none", out=None):
 
 
 _SKINNY_BWD = os.environ.get("TFDE_SKINNY_BWD", "1") == "1"
+_SKINNY_BWD_PUSH = os.environ.get("TFDE_SKINNY_BWD_PUSH", "0") == "1"     # experimental, see ROADMAP.md item 2
+register_optional("tfde_dense_bwd_skinny_push", [c_p] * 7 + [c_i] * 3 + [c_p, c_p])
 register_optional("tfde_dense_bwd_skinny_supported", [c_i, c_i, c_i])
 register_optional("tfde_dense_bwd_skinny", [c_p] * 7 + [c_i] * 3 + [c_p])
 
@@ -293,6 +295,15 @@ def dense_bwd(x, w, y, dy, act="none", need_dx=True, has_bias=True, out_dx=None,
         dx = (out_dx if out_dx is not None else torch.empty((M, K), dtype=torch.float32, device=dev)) if need_dx else None
         check(L.tfde_dense_bwd_skinny(x.data_ptr(), w.data_ptr(), dy.data_ptr(), ptr(mask), ptr(dx), dw.data_ptr(),
                                       ptr(db), M, K, N, stream_ptr()), "dense_bwd_skinny")
+        return dx, dw, db
+
+    if (pd is not None and _SKINNY_BWD_PUSH and hasattr(L, "tfde_dense_bwd_skinny_push")
+            and L.tfde_dense_bwd_skinny_supported(M, K, N)):
+        # EXPERIMENTAL (off by default, not yet validated on >= 2 GPUs): one-launch backward that also pushes dW
+        dx = (out_dx if out_dx is not None else torch.empty((M, K), dtype=torch.float32, device=dev)) if need_dx else None
+        check(L.tfde_dense_bwd_skinny_push(x.data_ptr(), w.data_ptr(), dy.data_ptr(), ptr(mask), ptr(dx), dw.data_ptr(),
+                                           ptr(db), M, K, N, ctypes.byref(pd), stream_ptr()), "dense_bwd_skinny_push")
+        _push.stats["pushed_launches"] += 1
         return dx, dw, db
 
     def launch_wgrad(ws_):
