@@ -1,0 +1,816 @@
+// Whole training step of "Model A" in ONE persistent cooperative kernel (optionally K steps per launch).
+//
+// Model (distributed_with_keras.py:33-43): Conv2D(32,3,relu) -> MaxPooling2D() -> Flatten -> Dense(64,relu)
+// -> Dense(ncls) ; SparseCategoricalCrossentropy(from_logits=True) ; SGD (momentum / Adam as extras);
+// per-replica batch <= 64 (distributed_with_keras.py:13). The reference runs this step as ~25 TensorFlow ops
+// plus an NCCL all-reduce (distributed_with_keras.py:16,63); round 1 of this repository ran it as 6 dependent
+// kernels (68 us, every one of them latency-bound). Here the step is one launch:
+//
+//   grid = 169 CTAs = one per pooled pixel (13x13); CTA p owns input features [32p, 32p+32) of the Dense(64)
+//   layer, i.e. rows [32p, 32p+32) of its (5408, 64) kernel -- 8 KB of weights that only this CTA ever reads
+//   or writes. The 1.38 MB activation tensor and its gradient never exist in global memory.
+//
+//   P1  conv3x3+bias+ReLU+maxpool for pixel p, all rows of the batch (kept in shared memory for the backward
+//       pass), then the split-K partial  h_p[64,64] = act_p[64,32] . W_p[32,64]        -> global partials
+//   B1  grid barrier
+//   P2  CTAs 0..127 reduce 8 float4 columns each over the 169 partials (fixed order), + bias, ReLU -> h
+//   B2  grid barrier
+//   P3  every CTA (redundantly, 16 KB of L2 reads instead of a third barrier): head logits, softmax-CE,
+//       d(logits), dh = d(logits).Wh^T * (h>0); then its own slice:  dW_p = act_p^T . dh,
+//       dx_p = dh . W_p^T, pool routing + ReLU mask + conv filter-gradient partial for pixel p.
+//       CTA 0 also produces the head / bias gradients and the loss / accuracy scalars.
+//   T   ticket: the last CTA to arrive reduces the 169 conv partials and applies the optimizer to the small
+//       tensors (conv kernel+bias, dense bias, head kernel+bias), writes the metrics tail, advances the
+//       step counter and releases the next step.
+//
+// Multi-GPU (MirroredStrategy / MultiWorkerMirroredStrategy, G12): the gradient all-reduce is part of the SAME
+// kernel, slice by slice, over peer memory (NVLink 5 / NVSwitch) -- GEMM -> reduce-scatter -> all-gather with
+// no NCCL call and no separate launch:
+//   * slice p is owned by rank p % W. Right after computing dW_p a non-owner stores it into the owner's
+//     receive buffer and raises a per-(rank, slice) flag (st.release.sys); it then carries on with dx / the
+//     conv backward while the bytes fly.
+//   * the owner sums the W contributions in rank order (bit-identical replicas), stores the reduced slice
+//     into every peer's `gsum` buffer and raises the per-slice "reduced" flag; every rank applies the
+//     optimizer to its own copy of slice p (optimizer state stays replicated: checkpoints need no gather).
+//   * the small tensors + the 4 metric scalars (G14) are exchanged one-shot by the ticket winner
+//     (double-buffered by step parity).
+// All waits are bounded (status word + abort), flags carry a monotonically increasing epoch kept in device
+// memory, so the kernel can be replayed from a CUDA graph.
+//
+// Numerics: exact fp32 FFMA everywhere (the reference trains in fp32), fixed summation orders.
+#include "common.cuh"
+#include <mutex>
+
+namespace {
+
+constexpr int FS_PIX = 169;       // pooled pixels = CTAs
+constexpr int FS_PW = 13;
+constexpr int FS_HW = 28;         // input height/width
+constexpr int FS_THREADS = 256;
+constexpr int FS_B = 64;          // max rows of the per-replica batch
+constexpr int FS_C = 32;          // conv channels
+constexpr int FS_U = 64;          // dense units
+constexpr int FS_NC = 16;         // max classes (padded head width)
+constexpr int FS_SLICE = FS_C * FS_U;        // 2048 floats of the dense kernel per CTA
+constexpr int FS_ND = FS_PIX * FS_SLICE;     // 346112 floats
+constexpr int FS_MAX_RANKS = 8;
+constexpr int FS_SMALL_MAX = 2048;           // floats of the packed small-tensor block (>= 288+32+64+64*16+16+4)
+constexpr int FS_FLAG_STRIDE = 176;          // >= FS_PIX, multiple of 16
+
+// state words (each on its own 128-byte line)
+constexpr int ST_BAR = 0, ST_TICKET = 32, ST_DONE = 64, ST_BAR0 = 96, ST_TICKET0 = 97, ST_EPOCH0 = 98;
+constexpr int FS_STATE_WORDS = 128;
+
+// shared memory layout (floats)
+constexpr int PATCH_LD = 17, ACT_LD = 68, WS_LD = 68, HS_LD = 65, ZS_LD = 17, DH_LD = 68, DX_LD = 33;
+constexpr int SM_PATCH = 0;
+constexpr int SM_ACT = SM_PATCH + FS_B * PATCH_LD;      // actT [32][68]
+constexpr int SM_ARG = SM_ACT + FS_C * ACT_LD;          // argw [64][4] u32
+constexpr int SM_WS = SM_ARG + FS_B * 4;                // ws   [32][68]
+constexpr int SM_HS = SM_WS + FS_C * WS_LD;             // hs   [64][65]
+constexpr int SM_WH = SM_HS + FS_B * HS_LD;             // wh   [64][16] + bh [16]
+constexpr int SM_ZS = SM_WH + FS_U * FS_NC + FS_NC;     // zs   [64][17]
+constexpr int SM_DH = SM_ZS + FS_B * ZS_LD;             // dh   [64][68]
+constexpr int SM_DX = SM_DH + FS_B * DH_LD;             // dxs  [64][33]
+constexpr int SM_CW = SM_DX + FS_B * DX_LD;             // cw   [10][32]
+constexpr int SM_RED = SM_CW + 10 * FS_C;               // red  [8][10][32]
+constexpr int SM_MISC = SM_RED + 8 * 10 * FS_C;         // misc [64]: labels (int) ; [64..96): loss/correct per warp
+constexpr int SM_TOTAL = SM_MISC + 96;
+static_assert(SM_ACT % 4 == 0 && SM_WS % 4 == 0 && SM_DH % 4 == 0 && SM_WH % 4 == 0 && SM_RED % 4 == 0, "align");
+
+struct Hyper { float lr, mu, b1, b2, eps, gs, lr_t; };
+
+struct FsParams {
+  const void* x; const long long* y;
+  int x_is_u8; float in_scale; long x_step_bytes;
+  int B, nsteps, ncls, opt;
+  float* w; float* g; float* s1; float* s2;
+  long off_ck, off_cb, off_dk, off_db, off_hk, off_hb, n;
+  float loss_scale;
+  TfdeHParams* hp; float* metrics; float* tails;
+  float* part; float* hbuf; float* cpart; float* small;
+  uint32_t* state; int* status;
+  unsigned long long timeout_ns;
+  int rank, world;
+  float* rs[FS_MAX_RANKS];        // rs[o]: owner o's receive buffer [world][FS_ND]
+  float* gsum[FS_MAX_RANKS];      // gsum[r]: rank r's reduced dense-kernel gradient [FS_ND]
+  float* srecv[FS_MAX_RANKS];     // srecv[r]: rank r's small-block receive slots [2][world][FS_SMALL_MAX]
+  uint32_t* flags[FS_MAX_RANKS];  // flags[r]: RS [world][176] | AG [176] | S [world]
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Bounded spin until *flag >= target (wrap-safe). SYS: the flag is written by a peer GPU. Returns false on
+// timeout or when another CTA already recorded a failure (the whole grid then drains quickly).
+template <bool SYS>
+__device__ __forceinline__ bool wait_flag(const FsParams& p, const uint32_t* flag, uint32_t target, int code,
+                                          int who, int where) {
+  const unsigned long long t0 = globaltimer_ns();
+  unsigned spins = 0;
+  while ((int)((SYS ? ld_acquire_sys(flag) : ld_acquire_gpu(flag)) - target) < 0) {
+    if ((++spins & 0xff) == 0) {
+      if (*reinterpret_cast<volatile int*>(p.status) != 0) return false;
+      if (globaltimer_ns() - t0 > p.timeout_ns) {
+        if (atomicCAS(p.status, 0, code) == 0) { p.status[1] = (int)target; p.status[2] = who; p.status[3] = where; }
+        return false;
+      }
+    }
+  }
+  return true;
+}
+
+// Grid-wide barrier on a monotonically increasing arrival counter (all CTAs are co-resident: cooperative launch).
+__device__ __forceinline__ void grid_barrier(const FsParams& p, uint32_t target, int where) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(p.state + ST_BAR, 1u);
+    wait_flag<false>(p, p.state + ST_BAR, target, 10, (int)blockIdx.x, where);
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float update_one(int opt, float w, float g, float* s1, float* s2, long i, const Hyper& h) {
+  g *= h.gs;
+  if (opt == 0) return w - h.lr * g;
+  if (opt == 1 || opt == 2) {
+    const float v = h.mu * s1[i] - h.lr * g;
+    s1[i] = v;
+    return w + (opt == 2 ? (h.mu * v - h.lr * g) : v);
+  }
+  const float m = h.b1 * s1[i] + (1.f - h.b1) * g;
+  const float v = h.b2 * s2[i] + (1.f - h.b2) * g * g;
+  s1[i] = m; s2[i] = v;
+  return w - h.lr_t * m / (sqrtf(v) + h.eps);
+}
+
+__device__ __forceinline__ float4 update_four(int opt, float4 w, float4 g, float* s1, float* s2, long i, const Hyper& h) {
+  float4 o;
+  if (opt == 0) {
+    o.x = w.x - h.lr * (g.x * h.gs); o.y = w.y - h.lr * (g.y * h.gs);
+    o.z = w.z - h.lr * (g.z * h.gs); o.w = w.w - h.lr * (g.w * h.gs);
+    return o;
+  }
+  o.x = update_one(opt, w.x, g.x, s1, s2, i, h);     o.y = update_one(opt, w.y, g.y, s1, s2, i + 1, h);
+  o.z = update_one(opt, w.z, g.z, s1, s2, i + 2, h); o.w = update_one(opt, w.w, g.w, s1, s2, i + 3, h);
+  return o;
+}
+
+// packed small block: [ck 288][cb 32][db 64][hk 64*ncls][hb ncls][tail 4]
+__device__ __forceinline__ int small_len(int ncls) { return 288 + 32 + 64 + 64 * ncls + ncls + 4; }
+__device__ __forceinline__ long small_to_arena(const FsParams& p, int i) {
+  if (i < 288) return p.off_ck + i;
+  i -= 288; if (i < 32) return p.off_cb + i;
+  i -= 32;  if (i < 64) return p.off_db + i;
+  i -= 64;  if (i < 64 * p.ncls) return p.off_hk + i;
+  i -= 64 * p.ncls; if (i < p.ncls) return p.off_hb + i;
+  return p.n + (i - p.ncls);
+}
+
+__global__ void __launch_bounds__(FS_THREADS, 2)
+fused_step_kernel(const FsParams p) {
+  extern __shared__ __align__(16) float sm[];
+  float* patch = sm + SM_PATCH;
+  float* actT = sm + SM_ACT;
+  uint32_t* argw = reinterpret_cast<uint32_t*>(sm + SM_ARG);
+  float* ws = sm + SM_WS;
+  float* hs = sm + SM_HS;
+  float* wh = sm + SM_WH;
+  float* bh = wh + FS_U * FS_NC;
+  float* zs = sm + SM_ZS;
+  float* dh = sm + SM_DH;
+  float* dxs = sm + SM_DX;
+  float* cw = sm + SM_CW;
+  float* red = sm + SM_RED;
+  int* ylab = reinterpret_cast<int*>(sm + SM_MISC);
+  float* wred = sm + SM_MISC + 64;          // [0..8) loss, [8..16) correct
+  __shared__ int s_last;
+
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int pix = blockIdx.x, py = pix / FS_PW, px = pix - py * FS_PW;
+  const int grid = gridDim.x;
+  const int W = p.world, R = p.rank;
+  const int owner = pix % W;
+  const uint32_t bar0 = p.state[ST_BAR0], ticket0 = p.state[ST_TICKET0], epoch0 = p.state[ST_EPOCH0];
+  float* gslice = p.g + p.off_dk + (long)pix * FS_SLICE;
+  float* wslice = p.w + p.off_dk + (long)pix * FS_SLICE;
+  const long aslice = p.off_dk + (long)pix * FS_SLICE;        // arena index of the slice (optimizer slots)
+  const int nsmall = small_len(p.ncls);
+
+  for (int s = 0; s < p.nsteps; ++s) {
+    const uint32_t e = epoch0 + (uint32_t)s + 1u;
+    // hyper-parameters of this step (the ticket winner of the previous step advanced them before releasing us)
+    Hyper h;
+    {
+      const volatile TfdeHParams* hp = p.hp;
+      h.lr = hp->lr; h.mu = hp->momentum; h.b1 = hp->beta1; h.b2 = hp->beta2; h.eps = hp->eps; h.gs = hp->grad_scale;
+      const float b1p = hp->beta1_pow * h.b1, b2p = hp->beta2_pow * h.b2;
+      h.lr_t = (p.opt == 3) ? h.lr * sqrtf(1.f - b2p) / (1.f - b1p) : h.lr;
+    }
+    // ================================ P1: conv + pool + split-K dense partial =========================
+    {
+      // dense kernel slice (8 KB) -> registers now, shared memory after the conv weights are staged
+      float4 wreg[2];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) wreg[i] = __ldcg(reinterpret_cast<const float4*>(wslice) + t + i * FS_THREADS);
+      for (int i = t; i < 320; i += FS_THREADS)
+        cw[i] = __ldcg(i < 288 ? p.w + p.off_ck + i : p.w + p.off_cb + (i - 288));
+      int yv = -1;
+      if (t < FS_B && t < p.B) yv = (int)p.y[(long)s * p.B + t];
+      {
+        const int b = t >> 2, row = t & 3;
+        float v[4] = {0.f, 0.f, 0.f, 0.f};
+        if (b < p.B) {
+          const long off = ((long)b * FS_HW + (2 * py + row)) * FS_HW + 2 * px;
+          if (p.x_is_u8) {
+            const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x) + (long)s * p.x_step_bytes + off;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = (float)__ldg(xb + j) * p.in_scale;
+          } else {
+            const float* xf = reinterpret_cast<const float*>(reinterpret_cast<const char*>(p.x) + (long)s * p.x_step_bytes) + off;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = __ldg(xf + j) * p.in_scale;
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) patch[b * PATCH_LD + row * 4 + j] = v[j];
+      }
+      if (t < FS_B) ylab[t] = yv;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int idx4 = t + i * FS_THREADS, c = idx4 >> 4, n4 = idx4 & 15;
+        *reinterpret_cast<float4*>(ws + c * WS_LD + n4 * 4) = wreg[i];
+      }
+    }
+    __syncthreads();
+    {
+      // conv: thread = (row b, 8 channels); weights broadcast from shared memory
+      const int b = t & 63, cg = t >> 6;
+      float pr[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) pr[i] = patch[b * PATCH_LD + i];
+      uint32_t bits = 0;
+#pragma unroll
+      for (int cc = 0; cc < 8; ++cc) {
+        const int c = cg * 8 + cc;
+        float wr[9];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) wr[i] = cw[i * FS_C + c];
+        const float bias = cw[9 * FS_C + c];
+        float best = -1.f; int besti = 0;
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+          for (int dx = 0; dx < 2; ++dx) {
+            float o = bias;
+#pragma unroll
+            for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+              for (int kw = 0; kw < 3; ++kw) o = fmaf(wr[kh * 3 + kw], pr[(dy + kh) * 4 + dx + kw], o);
+            o = fmaxf(o, 0.f);
+            if (o > best) { best = o; besti = dy * 2 + dx; }
+          }
+        actT[c * ACT_LD + b] = best;
+        bits |= (uint32_t)besti << (2 * cc);
+      }
+      argw[b * 4 + cg] = bits;
+    }
+    __syncthreads();
+    {
+      // split-K partial: h_p[b, n] = sum_c act[b, c] * W_p[c, n]; thread tile 4 rows x 4 units
+      const int tb = t >> 4, tn = t & 15;
+      float acc[4][4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+#pragma unroll 8
+      for (int c = 0; c < FS_C; ++c) {
+        const float4 a = *reinterpret_cast<const float4*>(actT + c * ACT_LD + tb * 4);
+        const float4 wv = *reinterpret_cast<const float4*>(ws + c * WS_LD + tn * 4);
+        const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          acc[i][0] = fmaf(av[i], wv.x, acc[i][0]); acc[i][1] = fmaf(av[i], wv.y, acc[i][1]);
+          acc[i][2] = fmaf(av[i], wv.z, acc[i][2]); acc[i][3] = fmaf(av[i], wv.w, acc[i][3]);
+        }
+      }
+      float4* dst = reinterpret_cast<float4*>(p.part + (long)pix * (FS_B * FS_U));
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        __stcg(dst + (tb * 4 + i) * (FS_U / 4) + tn, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
+    }
+    grid_barrier(p, bar0 + (uint32_t)(2 * s + 1) * (uint32_t)grid, 1);
+
+    // ================================ P2: reduce the partials -> h =====================================
+    if (pix < 128) {
+      const int f4 = pix * 8 + warp;        // float4 column of h (1024 in all)
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 v[6];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        const int q = lane + 32 * j;
+        v[j] = q < FS_PIX ? __ldcg(reinterpret_cast<const float4*>(p.part) + (long)q * 1024 + f4)
+                          : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int j = 0; j < 6; ++j) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        a.x += __shfl_xor_sync(0xffffffffu, a.x, o); a.y += __shfl_xor_sync(0xffffffffu, a.y, o);
+        a.z += __shfl_xor_sync(0xffffffffu, a.z, o); a.w += __shfl_xor_sync(0xffffffffu, a.w, o);
+      }
+      if (lane == 0) {
+        const float4 bv = __ldcg(reinterpret_cast<const float4*>(p.w + p.off_db) + (f4 & 15));
+        a.x = fmaxf(a.x + bv.x, 0.f); a.y = fmaxf(a.y + bv.y, 0.f);
+        a.z = fmaxf(a.z + bv.z, 0.f); a.w = fmaxf(a.w + bv.w, 0.f);
+        __stcg(reinterpret_cast<float4*>(p.hbuf) + f4, a);
+      }
+    }
+    grid_barrier(p, bar0 + (uint32_t)(2 * s + 2) * (uint32_t)grid, 2);
+
+    // ================================ P3: head + loss + backward =======================================
+    {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int f4 = t + i * FS_THREADS, b = f4 >> 4, k4 = f4 & 15;
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(p.hbuf) + f4);
+        float* d = hs + b * HS_LD + k4 * 4;
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+      }
+      for (int i = t; i < FS_U * FS_NC + FS_NC; i += FS_THREADS) {
+        float v = 0.f;
+        if (i < FS_U * FS_NC) { const int k = i >> 4, c = i & 15; if (c < p.ncls) v = __ldcg(p.w + p.off_hk + k * p.ncls + c); }
+        else { const int c = i - FS_U * FS_NC; if (c < p.ncls) v = __ldcg(p.w + p.off_hb + c); }
+        wh[i] = v;
+      }
+    }
+    __syncthreads();
+    {
+      // logits: thread = (row b, classes cg, cg+4, cg+8, cg+12)
+      const int b = t & 63, cg = t >> 6;
+      float a0 = bh[cg], a1 = bh[cg + 4], a2 = bh[cg + 8], a3 = bh[cg + 12];
+#pragma unroll 8
+      for (int k = 0; k < FS_U; ++k) {
+        const float hv = hs[b * HS_LD + k];
+        const float* wr = wh + k * FS_NC + cg;
+        a0 = fmaf(hv, wr[0], a0); a1 = fmaf(hv, wr[4], a1); a2 = fmaf(hv, wr[8], a2); a3 = fmaf(hv, wr[12], a3);
+      }
+      float* z = zs + b * ZS_LD + cg;
+      z[0] = a0; z[4] = a1; z[8] = a2; z[12] = a3;
+    }
+    __syncthreads();
+    {
+      // softmax cross-entropy: warp per row, lane = class
+      float loss = 0.f, correct = 0.f;
+      const int N = p.ncls;
+      for (int r = warp * 8; r < warp * 8 + 8; ++r) {
+        const int y = ylab[r];
+        const float z = lane < N ? zs[r * ZS_LD + lane] : -INFINITY;
+        float mx = z; int am = lane < N ? lane : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const float ov = __shfl_xor_sync(0xffffffffu, mx, o);
+          const int oa = __shfl_xor_sync(0xffffffffu, am, o);
+          if (ov > mx || (ov == mx && oa < am)) { mx = ov; am = oa; }
+        }
+        const float ex = lane < N ? expf(z - mx) : 0.f;
+        const float sum = warp_sum(ex);
+        const float prob = ex / sum;
+        const bool live = r < p.B;
+        const bool valid = live && (unsigned)y < (unsigned)N;
+        const float zy = __shfl_sync(0xffffffffu, z, valid ? y : 0);
+        float dz = 0.f;
+        if (valid) dz = (prob - (lane == y ? 1.f : 0.f)) * p.loss_scale;
+        if (lane == 0 && live) {
+          // a label outside [0, ncls) poisons the loss (TensorFlow's GPU kernel returns NaN for it) and
+          // contributes no gradient
+          loss += valid ? (mx + logf(sum)) - zy : __int_as_float(0x7fc00000);
+          if (valid && am == y) correct += 1.f;
+        }
+        if (lane < FS_NC) zs[r * ZS_LD + lane] = (lane < N) ? dz : 0.f;
+      }
+      if (lane == 0) { wred[warp] = loss; wred[8 + warp] = correct; }
+    }
+    __syncthreads();
+    {
+      // dh[b, n] = (sum_c dz[b, c] * Wh[n, c]) * (h[b, n] > 0)
+      const int b = t & 63, ng = t >> 6;
+      float zr[FS_NC];
+#pragma unroll
+      for (int c = 0; c < FS_NC; ++c) zr[c] = zs[b * ZS_LD + c];
+#pragma unroll 4
+      for (int j = 0; j < 16; ++j) {
+        const int n = ng * 16 + j;
+        const float* wr = wh + n * FS_NC;
+        float a = 0.f;
+#pragma unroll
+        for (int c = 0; c < FS_NC; ++c) a = fmaf(zr[c], wr[c], a);
+        dh[b * DH_LD + n] = hs[b * HS_LD + n] > 0.f ? a : 0.f;
+      }
+    }
+    __syncthreads();
+    if (pix == 0) {
+      // head kernel/bias gradient, dense bias gradient, loss / accuracy scalars -> packed small block
+      float* sp = p.small;
+      const int N = p.ncls;
+      for (int i = t; i < FS_U * N; i += FS_THREADS) {       // dWh[k, c] = sum_b h[b, k] * dz[b, c]
+        const int k = i / N, c = i - k * N;
+        float a = 0.f;
+        for (int b = 0; b < FS_B; ++b) a = fmaf(hs[b * HS_LD + k], zs[b * ZS_LD + c], a);
+        __stcg(sp + 384 + i, a);
+      }
+      if (t < FS_U) {                                        // db[n] = sum_b dh[b, n]
+        float a = 0.f;
+        for (int b = 0; b < FS_B; ++b) a += dh[b * DH_LD + t];
+        __stcg(sp + 320 + t, a);
+      } else if (t < FS_U + N) {                             // dbh[c] = sum_b dz[b, c]
+        const int c = t - FS_U;
+        float a = 0.f;
+        for (int b = 0; b < FS_B; ++b) a += zs[b * ZS_LD + c];
+        __stcg(sp + 384 + FS_U * N + c, a);
+      } else if (t == 128) {
+        float l = 0.f, c = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { l += wred[i]; c += wred[8 + i]; }
+        float* tl = sp + 384 + FS_U * N + N;
+        __stcg(tl + 0, l * p.loss_scale); __stcg(tl + 1, c); __stcg(tl + 2, (float)p.B); __stcg(tl + 3, 0.f);
+      }
+    }
+    // dW_p[c, n] = sum_b act[b, c] * dh[b, n] ; thread tile 2 channels x 4 units (kept in registers until the
+    // optimizer / the reduction consumes it)
+    float gacc[2][4];
+    const int tc = t >> 4, tn = t & 15;
+    {
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) gacc[i][j] = 0.f;
+#pragma unroll 8
+      for (int b = 0; b < FS_B; ++b) {
+        const float a0 = actT[(tc * 2) * ACT_LD + b], a1 = actT[(tc * 2 + 1) * ACT_LD + b];
+        const float4 d = *reinterpret_cast<const float4*>(dh + b * DH_LD + tn * 4);
+        gacc[0][0] = fmaf(a0, d.x, gacc[0][0]); gacc[0][1] = fmaf(a0, d.y, gacc[0][1]);
+        gacc[0][2] = fmaf(a0, d.z, gacc[0][2]); gacc[0][3] = fmaf(a0, d.w, gacc[0][3]);
+        gacc[1][0] = fmaf(a1, d.x, gacc[1][0]); gacc[1][1] = fmaf(a1, d.y, gacc[1][1]);
+        gacc[1][2] = fmaf(a1, d.z, gacc[1][2]); gacc[1][3] = fmaf(a1, d.w, gacc[1][3]);
+      }
+    }
+    if (W == 1) {
+      // single replica: the optimizer is the epilogue of the filter-gradient tile
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int c = tc * 2 + i, off = c * FS_U + tn * 4;
+        const float4 gv = make_float4(gacc[i][0], gacc[i][1], gacc[i][2], gacc[i][3]);
+        const float4 wv = *reinterpret_cast<const float4*>(ws + c * WS_LD + tn * 4);
+        *reinterpret_cast<float4*>(gslice + off) = gv;
+        *reinterpret_cast<float4*>(wslice + off) = update_four(p.opt, wv, gv, p.s1, p.s2, aslice + off, h);
+      }
+    } else if (owner != R) {
+      // GEMM -> reduce-scatter: the tile goes straight into the owner's receive buffer over NVLink
+      float* dst = p.rs[owner] + (long)R * FS_ND + (long)pix * FS_SLICE;
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+        __stcg(reinterpret_cast<float4*>(dst + (tc * 2 + i) * FS_U + tn * 4),
+               make_float4(gacc[i][0], gacc[i][1], gacc[i][2], gacc[i][3]));
+      __syncthreads();
+      if (t == 0) st_release_sys(p.flags[owner] + R * FS_FLAG_STRIDE + pix, e);
+    }
+    {
+      // dx_p[b, c] = sum_n dh[b, n] * W_p[c, n], masked by ReLU; thread tile 4 rows x 2 channels
+      const int tb = t >> 4, tq = t & 15;
+      float acc[4][2];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = 0.f;
+#pragma unroll 4
+      for (int n4 = 0; n4 < FS_U / 4; ++n4) {
+        const float4 w0 = *reinterpret_cast<const float4*>(ws + (tq * 2) * WS_LD + n4 * 4);
+        const float4 w1 = *reinterpret_cast<const float4*>(ws + (tq * 2 + 1) * WS_LD + n4 * 4);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 d = *reinterpret_cast<const float4*>(dh + (tb * 4 + i) * DH_LD + n4 * 4);
+          acc[i][0] = fmaf(d.x, w0.x, acc[i][0]); acc[i][0] = fmaf(d.y, w0.y, acc[i][0]);
+          acc[i][0] = fmaf(d.z, w0.z, acc[i][0]); acc[i][0] = fmaf(d.w, w0.w, acc[i][0]);
+          acc[i][1] = fmaf(d.x, w1.x, acc[i][1]); acc[i][1] = fmaf(d.y, w1.y, acc[i][1]);
+          acc[i][1] = fmaf(d.z, w1.z, acc[i][1]); acc[i][1] = fmaf(d.w, w1.w, acc[i][1]);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int b = tb * 4 + i;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int c = tq * 2 + j;
+          dxs[b * DX_LD + c] = actT[c * ACT_LD + b] > 0.f ? acc[i][j] : 0.f;
+        }
+      }
+    }
+    __syncthreads();
+    {
+      // conv filter/bias gradient partial of this pixel: lane = channel, warp strides over the rows
+      float acc[10];
+#pragma unroll
+      for (int i = 0; i < 10; ++i) acc[i] = 0.f;
+      for (int b = warp; b < FS_B; b += 8) {
+        const float gv = dxs[b * DX_LD + lane];
+        const int sel = (argw[b * 4 + (lane >> 3)] >> (2 * (lane & 7))) & 3;
+        const int dy = sel >> 1, dx = sel & 1;
+        const float* pb = patch + b * PATCH_LD + dy * 4 + dx;
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+          for (int kw = 0; kw < 3; ++kw) acc[kh * 3 + kw] = fmaf(gv, pb[kh * 4 + kw], acc[kh * 3 + kw]);
+        acc[9] += gv;
+      }
+#pragma unroll
+      for (int i = 0; i < 10; ++i) red[(warp * 10 + i) * FS_C + lane] = acc[i];
+    }
+    __syncthreads();
+    for (int i = t; i < 320; i += FS_THREADS) {
+      float a = 0.f;
+#pragma unroll
+      for (int wv = 0; wv < 8; ++wv) a += red[wv * 320 + i];
+      __stcg(p.cpart + (long)pix * 320 + i, a);
+    }
+    // ================================ T: ticket; the last CTA finishes the small tensors ===============
+    __threadfence();
+    __syncthreads();
+    if (t == 0) s_last = (atomicAdd(p.state + ST_TICKET, 1u) + 1u == ticket0 + (uint32_t)(s + 1) * (uint32_t)grid);
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      // conv partials: 80 float4 columns x 3 interleaved groups, 8 independent loads in flight per thread
+      float4* sgrp = reinterpret_cast<float4*>(red);      // [3][80]
+      if (t < 240) {
+        const int grp = t / 80, c4 = t - grp * 80;
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int q0 = grp; q0 < FS_PIX; q0 += 24) {
+          float4 v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int q = q0 + 3 * j;
+            v[j] = q < FS_PIX ? __ldcg(reinterpret_cast<const float4*>(p.cpart + (long)q * 320) + c4)
+                              : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
+        }
+        sgrp[grp * 80 + c4] = a;
+      }
+      __syncthreads();
+      float* sp = p.small;
+      if (t < 80) {
+        const float4 a = sgrp[t], b = sgrp[80 + t], c = sgrp[160 + t];
+        __stcg(reinterpret_cast<float4*>(sp) + t,
+               make_float4((a.x + b.x) + c.x, (a.y + b.y) + c.y, (a.z + b.z) + c.z, (a.w + b.w) + c.w));
+      }
+      __syncthreads();
+      // `sp` now holds this replica's packed small gradients + [loss*scale, correct, rows, 0]
+      float* stage = dh;                                   // reduced block (shared memory, dead by now)
+      if (W == 1) {
+        for (int i = t; i < nsmall; i += FS_THREADS) stage[i] = __ldcg(sp + i);
+      } else {
+        const int parity = (int)(e & 1u);
+        for (int k = 1; k < W; ++k) {
+          const int peer = (R + k) % W;
+          float* dst = p.srecv[peer] + ((long)parity * W + R) * FS_SMALL_MAX;
+          for (int i = t; i < nsmall; i += FS_THREADS) __stcg(dst + i, __ldcg(sp + i));
+        }
+        __syncthreads();
+        if (t < W && t != R) {
+          st_release_sys(p.flags[t] + (W + 1) * FS_FLAG_STRIDE + R, e);
+          wait_flag<true>(p, p.flags[R] + (W + 1) * FS_FLAG_STRIDE + t, e, 21, t, pix);
+        }
+        __syncthreads();
+        const float* base = p.srecv[R] + (long)parity * W * FS_SMALL_MAX;
+        for (int i = t; i < nsmall; i += FS_THREADS) {
+          float a = 0.f;
+          for (int r = 0; r < W; ++r) a += (r == R) ? __ldcg(sp + i) : __ldcg(base + (long)r * FS_SMALL_MAX + i);
+          stage[i] = a;
+        }
+      }
+      __syncthreads();
+      const int ntrain = nsmall - 4;
+      for (int i = t; i < ntrain; i += FS_THREADS) {
+        const long ai = small_to_arena(p, i);
+        const float gv = stage[i];
+        p.g[ai] = gv;
+        p.w[ai] = update_one(p.opt, __ldcg(p.w + ai), gv, p.s1, p.s2, ai, h);
+      }
+      if (t < 4) {
+        const float v = stage[ntrain + t];
+        p.g[p.n + t] = v;
+        p.w[p.n + t] = v;
+        if (p.metrics) p.metrics[t] += v;
+        if (p.tails) p.tails[(long)s * 4 + t] = v;
+      }
+      __syncthreads();
+      if (t == 0) {
+        TfdeHParams* hp = p.hp;
+        hp->beta1_pow *= hp->beta1; hp->beta2_pow *= hp->beta2; hp->step += 1u;
+        if (s == p.nsteps - 1) {
+          p.state[ST_BAR0] = bar0 + (uint32_t)(2 * p.nsteps) * (uint32_t)grid;
+          p.state[ST_TICKET0] = ticket0 + (uint32_t)p.nsteps * (uint32_t)grid;
+          p.state[ST_EPOCH0] = epoch0 + (uint32_t)p.nsteps;
+          if (p.tails) __threadfence_system();
+        }
+        __threadfence();
+        st_release_gpu(p.state + ST_DONE, e);
+      }
+    }
+    // ================================ dense-kernel slice: reduce across replicas, update ================
+    if (W > 1) {
+      float4 sum[2];
+      if (owner == R) {
+        if (t < W && t != R) wait_flag<true>(p, p.flags[R] + t * FS_FLAG_STRIDE + pix, e, 22, t, pix);
+        __syncthreads();
+        const float* base = p.rs[R] + (long)pix * FS_SLICE;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int off = (tc * 2 + i) * FS_U + tn * 4;
+          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int r = 0; r < W; ++r) {
+            const float4 v = (r == R) ? make_float4(gacc[i][0], gacc[i][1], gacc[i][2], gacc[i][3])
+                                      : __ldcg(reinterpret_cast<const float4*>(base + (long)r * FS_ND + off));
+            a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+          }
+          sum[i] = a;
+          for (int k = 1; k < W; ++k) {
+            const int peer = (R + k) % W;
+            __stcg(reinterpret_cast<float4*>(p.gsum[peer] + (long)pix * FS_SLICE + off), a);
+          }
+        }
+        __syncthreads();
+        if (t < W && t != R) st_release_sys(p.flags[t] + W * FS_FLAG_STRIDE + pix, e);
+      } else {
+        if (t == 0) wait_flag<true>(p, p.flags[R] + W * FS_FLAG_STRIDE + pix, e, 23, owner, pix);
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+          sum[i] = __ldcg(reinterpret_cast<const float4*>(p.gsum[R] + (long)pix * FS_SLICE + (tc * 2 + i) * FS_U + tn * 4));
+      }
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int c = tc * 2 + i, off = c * FS_U + tn * 4;
+        const float4 wv = *reinterpret_cast<const float4*>(ws + c * WS_LD + tn * 4);
+        *reinterpret_cast<float4*>(gslice + off) = sum[i];
+        *reinterpret_cast<float4*>(wslice + off) = update_four(p.opt, wv, sum[i], p.s1, p.s2, aslice + off, h);
+      }
+    }
+    // ================================ wait for the step to be complete ==================================
+    if (s + 1 < p.nsteps) {
+      if (t == 0) wait_flag<false>(p, p.state + ST_DONE, e, 11, pix, 3);
+      __syncthreads();
+    }
+    if (*reinterpret_cast<volatile int*>(p.status) != 0) break;    // a wait timed out somewhere: drain
+  }
+}
+
+struct DeviceInit { bool done = false; int max_blocks = 0; };
+DeviceInit g_init[64];
+std::mutex g_init_mu;
+
+}  // namespace
+
+// Launch descriptor (mirrored by ops/fused_step.py::_FusedStepDesc).
+struct TfdeFusedStepDesc {
+  const void* x; const void* y;
+  int x_is_u8; float in_scale; long x_step_bytes;
+  int B, nsteps, ncls, opt;
+  float* w; float* g; float* s1; float* s2;
+  long off_ck, off_cb, off_dk, off_db, off_hk, off_hb, n;
+  float loss_scale; int rank; int world; int reserved;
+  void* hp; float* metrics; float* tails;
+  float* part; float* hbuf; float* cpart; float* small_block;
+  void* state; void* status;
+  unsigned long long timeout_ns;
+  void* rs[FS_MAX_RANKS]; void* gsum[FS_MAX_RANKS]; void* srecv[FS_MAX_RANKS]; void* flags[FS_MAX_RANKS];
+};
+
+TFDE_API size_t tfde_fused_step_desc_bytes() { return sizeof(TfdeFusedStepDesc); }
+// scratch sizes (floats / words) so that the Python side never hard-codes them
+TFDE_API size_t tfde_fused_step_part_floats() { return (size_t)FS_PIX * FS_B * FS_U; }
+TFDE_API size_t tfde_fused_step_hbuf_floats() { return (size_t)FS_B * FS_U; }
+TFDE_API size_t tfde_fused_step_cpart_floats() { return (size_t)FS_PIX * 320; }
+TFDE_API size_t tfde_fused_step_small_floats() { return (size_t)FS_SMALL_MAX; }
+TFDE_API size_t tfde_fused_step_state_words() { return (size_t)FS_STATE_WORDS; }
+TFDE_API size_t tfde_fused_step_rs_floats(int world) { return (size_t)world * FS_ND; }
+TFDE_API size_t tfde_fused_step_gsum_floats() { return (size_t)FS_ND; }
+TFDE_API size_t tfde_fused_step_srecv_floats(int world) { return (size_t)2 * world * FS_SMALL_MAX; }
+TFDE_API size_t tfde_fused_step_flag_words(int world) { return (size_t)(world + 1) * FS_FLAG_STRIDE + 16; }
+TFDE_API int tfde_fused_step_blocks() { return FS_PIX; }
+
+// One training step x nsteps of Model A on `stream`. Returns 0, a cudaError_t, or TFDE_ERR_INVALID for shapes the
+// kernel does not cover (the caller then uses the layer-by-layer path).
+TFDE_API int tfde_fused_step(const TfdeFusedStepDesc* d, cudaStream_t stream) {
+  if (d->B < 1 || d->B > FS_B || d->nsteps < 1 || d->ncls < 1 || d->ncls > FS_NC) return TFDE_ERR_INVALID;
+  if (d->world < 1 || d->world > FS_MAX_RANKS || d->rank < 0 || d->rank >= d->world) return TFDE_ERR_INVALID;
+  if (d->opt < 0 || d->opt > 3 || (d->opt >= 1 && !d->s1) || (d->opt == 3 && !d->s2)) return TFDE_ERR_INVALID;
+  if ((d->off_dk & 3) || (d->off_db & 3) || ((uintptr_t)d->w & 15) || ((uintptr_t)d->g & 15)) return TFDE_ERR_INVALID;
+  int dev = 0;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return (int)err;
+  const size_t smem = (size_t)SM_TOTAL * sizeof(float);
+  {
+    std::lock_guard<std::mutex> lk(g_init_mu);
+    DeviceInit& di = g_init[dev & 63];
+    if (!di.done) {
+      err = cudaFuncSetAttribute(fused_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (err != cudaSuccess) return (int)err;
+      int per_sm = 0, sms = 0;
+      err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_step_kernel, FS_THREADS, smem);
+      if (err != cudaSuccess) return (int)err;
+      err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      if (err != cudaSuccess) return (int)err;
+      di.max_blocks = per_sm * sms;
+      di.done = true;
+    }
+    if (di.max_blocks < FS_PIX) return TFDE_ERR_INVALID;     // the grid could not be co-resident on this GPU
+  }
+  FsParams p{};
+  p.x = d->x; p.y = (const long long*)d->y; p.x_is_u8 = d->x_is_u8; p.in_scale = d->in_scale;
+  p.x_step_bytes = d->x_step_bytes; p.B = d->B; p.nsteps = d->nsteps; p.ncls = d->ncls; p.opt = d->opt;
+  p.w = d->w; p.g = d->g; p.s1 = d->s1; p.s2 = d->s2;
+  p.off_ck = d->off_ck; p.off_cb = d->off_cb; p.off_dk = d->off_dk; p.off_db = d->off_db;
+  p.off_hk = d->off_hk; p.off_hb = d->off_hb; p.n = d->n;
+  p.loss_scale = d->loss_scale; p.hp = (TfdeHParams*)d->hp; p.metrics = d->metrics; p.tails = d->tails;
+  p.part = d->part; p.hbuf = d->hbuf; p.cpart = d->cpart; p.small = d->small_block;
+  p.state = (uint32_t*)d->state; p.status = (int*)d->status;
+  p.timeout_ns = d->timeout_ns ? d->timeout_ns : 5000000000ULL;
+  p.rank = d->rank; p.world = d->world;
+  for (int i = 0; i < FS_MAX_RANKS; ++i) {
+    p.rs[i] = (float*)d->rs[i]; p.gsum[i] = (float*)d->gsum[i];
+    p.srecv[i] = (float*)d->srecv[i]; p.flags[i] = (uint32_t*)d->flags[i];
+  }
+  if (d->world > 1)
+    for (int i = 0; i < d->world; ++i)
+      if (!p.rs[i] || !p.gsum[i] || !p.srecv[i] || !p.flags[i]) return TFDE_ERR_INVALID;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(FS_PIX); cfg.blockDim = dim3(FS_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  err = cudaLaunchKernelEx(&cfg, fused_step_kernel, p);
+  if (err != cudaSuccess) return (int)err;
+  TFDE_RETURN_LAUNCH_STATUS();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Host launcher for the end-to-end path (Keras `steps_per_execution`): ONE call stages the inputs of `nsteps`
+// steps and launches them. Per step it issues that step's own host->device copies (images, labels) from the
+// caller's pinned memory on `copy_stream`, so the copies of execution i+1 run under the kernel of execution i;
+// the kernel is ordered after the copies by an event and is followed by `ev_done` (the host waits on it before
+// it reuses this staging slot or reads the losses the kernel wrote into mapped pinned memory).
+// ---------------------------------------------------------------------------------------------
+TFDE_API int tfde_event_create(void** out) {
+  cudaEvent_t e;
+  cudaError_t err = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+  *out = (void*)e;
+  return (int)err;
+}
+TFDE_API int tfde_event_destroy(void* e) { return (int)cudaEventDestroy((cudaEvent_t)e); }
+TFDE_API int tfde_event_synchronize(void* e) { return (int)cudaEventSynchronize((cudaEvent_t)e); }
+TFDE_API int tfde_event_query(void* e) { return (int)cudaEventQuery((cudaEvent_t)e); }
+
+TFDE_API int tfde_fused_exec(const TfdeFusedStepDesc* d, const void* host_x, const void* host_y,
+                             size_t x_bytes_per_step, size_t y_bytes_per_step, cudaStream_t copy_stream,
+                             void* ev_copied, void* ev_done, cudaStream_t stream) {
+  cudaError_t err;
+  char* dx = (char*)d->x; char* dy = (char*)d->y;
+  for (int s = 0; s < d->nsteps; ++s) {
+    err = cudaMemcpyAsync(dx + (size_t)s * x_bytes_per_step, (const char*)host_x + (size_t)s * x_bytes_per_step,
+                          x_bytes_per_step, cudaMemcpyHostToDevice, copy_stream);
+    if (err != cudaSuccess) return (int)err;
+    err = cudaMemcpyAsync(dy + (size_t)s * y_bytes_per_step, (const char*)host_y + (size_t)s * y_bytes_per_step,
+                          y_bytes_per_step, cudaMemcpyHostToDevice, copy_stream);
+    if (err != cudaSuccess) return (int)err;
+  }
+  err = cudaEventRecord((cudaEvent_t)ev_copied, copy_stream);
+  if (err != cudaSuccess) return (int)err;
+  err = cudaStreamWaitEvent(stream, (cudaEvent_t)ev_copied, 0);
+  if (err != cudaSuccess) return (int)err;
+  int rc = tfde_fused_step(d, stream);
+  if (rc != 0) return rc;
+  return (int)cudaEventRecord((cudaEvent_t)ev_done, stream);
+}

@@ -115,6 +115,9 @@ class Sequential:
         self._type_counts: Dict[str, int] = {}
         self.stop_training = False
         self.gpu_launches_per_step = 0
+        self.steps_per_execution = 1
+        self._fused = None           # ops.fused_step.FusedStepPlan once the whole-step kernel is in use
+        self._fused_checked = False
         for l in layers or []:
             self.add(l)
 
@@ -244,7 +247,10 @@ class Sequential:
     # ------------------------------------------------------------------------------------------
     # compile
     # ------------------------------------------------------------------------------------------
-    def compile(self, optimizer="sgd", loss=None, metrics=None, **_ignored):
+    def compile(self, optimizer="sgd", loss=None, metrics=None, steps_per_execution=1, **_ignored):
+        """``steps_per_execution`` (Keras): how many optimizer steps ``fit`` hands to the device per launch. The
+        whole-step kernel runs them back to back inside one launch, each step with its own input batch."""
+        self.steps_per_execution = max(1, int(steps_per_execution or 1))
         self.loss = losses_mod.get(loss)
         self.optimizer = opt_mod.get(optimizer)
         self.metrics_names = ["loss"]
@@ -342,6 +348,12 @@ class Sequential:
     def _step_body(self, x, y, global_batch: int):
         """forward -> fused loss/grad/accuracy -> backward -> (cross-replica reduce +) optimizer."""
         st = self.strategy
+        plan = self.fused_plan(x)
+        if plan is not None:
+            # the whole step -- forward, loss, backward, cross-replica reduction, optimizer -- is ONE kernel
+            plan.launch(x, y, int(x.shape[0]), 1, global_batch)
+            self.optimizer.iterations += 1
+            return
         asynchronous = not st.synchronous
         if asynchronous:
             st.pull(self)              # parameter-server mode: fetch the current weights (N4)
@@ -379,6 +391,80 @@ class Sequential:
             self.optimizer.iterations += 1
         else:
             self.optimizer.apply_local(a)
+
+    def fused_plan(self, x=None):
+        """The whole-step kernel's plan when this model/strategy/policy is covered by it (Model A topology, fp32,
+        synchronous strategy, CUDA) and -- if ``x`` is given -- this batch is (<= 64 rows, uint8/float32)."""
+        if not self._fused_checked:
+            self._fused_checked = True
+            from ..ops import fused_step, mixed
+            if (self.device.type == "cuda" and fused_step.enabled() and self.built and self.compiled
+                    and mixed.global_policy() == "float32" and self.strategy.synchronous
+                    and os.environ.get("TFDE_FUSION", "1") == "1" and not self.loss.from_probs):
+                m = fused_step.match(self)
+                if m is not None:
+                    self._fused = fused_step.FusedStepPlan(self, *m)
+        plan = self._fused
+        if plan is None or x is None:
+            return plan
+        if not isinstance(x, torch.Tensor):
+            return None
+        return plan if plan.supports(x, int(x.shape[0])) else None
+
+    def train_on_batches(self, x, y, steps: Optional[int] = None, global_batch: Optional[int] = None):
+        """``steps`` optimizer steps in ONE device launch (Keras ``steps_per_execution``): ``x`` holds the
+        per-replica batches of all steps stacked along axis 0 (``[steps*B, ...]`` or ``[steps, B, ...]``), ``y``
+        likewise. Each step consumes its own batch and produces its own loss (``last_losses()``). Models the
+        whole-step kernel does not cover run the steps one after the other through ``train_on_batch``."""
+        if isinstance(x, np.ndarray):
+            x = torch.from_numpy(x)
+        if isinstance(y, np.ndarray):
+            y = torch.from_numpy(y)
+        if steps is None:
+            if y.dim() != 2:
+                raise ValueError("train_on_batches: pass steps=K, or x shaped [K, B, ...] with y shaped [K, B]")
+            steps = int(y.shape[0])
+            x = x.reshape((-1,) + tuple(x.shape[2:]))
+        K = int(steps)
+        rows = int(x.shape[0])
+        if rows % K:
+            raise ValueError(f"{rows} rows do not split into {K} equal steps")
+        B = rows // K
+        yy = y.reshape(-1)
+        if not self.built:
+            self.build(tuple(x.shape[1:]))
+        if getattr(self.optimizer, "_bound_to", None) is not self:
+            self._bind_optimizer()
+        gb = global_batch if global_batch is not None else B * self.strategy.num_replicas_in_sync
+        plan = self.fused_plan(x) if self.device.type == "cuda" else None
+        if plan is None or not plan.supports(x, B):
+            for k in range(K):
+                self.train_on_batch(x[k * B:(k + 1) * B], yy[k * B:(k + 1) * B], global_batch=gb)
+            return
+        if self._stream is None:
+            self._stream = torch.cuda.Stream(device=self.device)
+        if x.is_cuda:
+            with torch.cuda.stream(self._stream):
+                self._stream.wait_stream(torch.cuda.current_stream(self.device))
+                plan.launch(x.contiguous(), yy.contiguous().long(), B, K, gb)
+            self._host_tail = None
+        else:
+            plan.execute(x, yy, B, K, gb, self._stream)
+            self._host_tail = "fused"
+        self.optimizer.iterations += K
+
+    def last_losses(self, lag: int = 0):
+        """Per-step losses (global mean) of the most recent ``train_on_batches`` / ``train_on_batch`` execution from
+        host batches (``lag=1``: of the one before it, so a loop can read every loss while the next execution is
+        already running). Waits for that execution only."""
+        plan = self._fused
+        if plan is not None and getattr(self, "_host_tail", None) == "fused":
+            slot = plan.last_slot if lag == 0 else plan.prev_slot
+            if slot is None:
+                return []
+            slot.wait()
+            return slot.host_tails[:slot.nsteps, 0].tolist()
+        return [self.last_step_loss(lag)]
 
     def fork_stream(self):
         """Side stream on which layers may run work that only the optimizer consumes (filter gradients)
@@ -427,6 +513,25 @@ class Sequential:
         if self._stream is None:
             self._stream = torch.cuda.Stream(device=self.device)
             ops.native.Workspace.current(self.device)
+        if isinstance(x, np.ndarray):
+            x = torch.from_numpy(x)
+        if isinstance(y, np.ndarray):
+            y = torch.from_numpy(y)
+        plan = self.fused_plan(x)
+        if plan is not None and os.environ.get("TFDE_FUSED_DIRECT", "1") == "1":
+            # one kernel per step: no CUDA graph needed. Host batches go through the staging ring (H2D on the copy
+            # stream, loss written into mapped pinned memory); device batches are consumed in place.
+            yy = y.reshape(-1)
+            if x.is_cuda:
+                with torch.cuda.stream(self._stream):
+                    self._stream.wait_stream(torch.cuda.current_stream(self.device))
+                    plan.launch(x.contiguous(), yy.contiguous().long(), b, 1, gb)
+                self._host_tail = None
+            else:
+                plan.execute(x, yy, b, 1, gb, self._stream)
+                self._host_tail = "fused"
+            self.optimizer.iterations += 1
+            return
         key = (b, tuple(x.shape[1:]), str(x.dtype), gb)
         st = self._graphs.get(key)
         if st is None:
@@ -529,6 +634,14 @@ class Sequential:
             st.graph = g
         return st.graph
 
+    def record_event(self, event):
+        """Records ``event`` on the stream this model launches its steps on (device-side timing of a training loop)."""
+        if self.device.type == "cuda":
+            if self._stream is None:
+                self._stream = torch.cuda.Stream(device=self.device)
+            event.record(self._stream)
+        return event
+
     def sync(self):
         if self.device.type == "cuda":
             if self._stream is not None:
@@ -542,6 +655,8 @@ class Sequential:
         m = self.arena.metrics.detach().cpu().tolist()
         if self.strategy.num_replicas_in_sync > 1:
             self.strategy.comm().check_health()
+        if self._fused is not None:
+            self._fused.check()
         out = {"loss": m[0] / max(steps, 1)}
         if "accuracy" in self.metrics_names:
             out["accuracy"] = m[1] / max(m[2], 1.0)
@@ -556,7 +671,11 @@ class Sequential:
     def last_step_loss(self, lag: int = 0) -> float:
         """Loss (global mean) of the most recent step, or -- ``lag=1`` -- of the step before it, which lets a
         loop read EVERY step's loss one step late while the next step is already running on the GPU."""
-        if getattr(self, "_host_tail", None) is not None:
+        if getattr(self, "_host_tail", None) == "fused":
+            ls = self.last_losses(lag)
+            if ls:
+                return float(ls[-1])
+        elif getattr(self, "_host_tail", None) is not None:
             # already on the host: the graph's last node copied it into the slot's pinned tail
             slot = self._last_slot if lag == 0 else self._prev_slot
             if slot is not None:
@@ -607,10 +726,35 @@ class Sequential:
                     log.warning("input ran out of data after %d steps of epoch %d", steps, epoch + 1)
                     self.stop_training = True
                     break
+                group = [(xb, yb)]
+                want = self.steps_per_execution
+                if steps_per_epoch is not None:
+                    want = min(want, steps_per_epoch - steps)
+                pending = None
+                while len(group) < want:
+                    # steps_per_execution: hand several batches to the device at once (same shape only)
+                    try:
+                        xn, yn, gn = next(it)
+                    except StopIteration:
+                        break
+                    if gn != gb or tuple(xn.shape) != tuple(xb.shape):
+                        pending = (xn, yn, gn)
+                        break
+                    group.append((xn, yn))
                 cbs.on_train_batch_begin(steps)
-                self.train_on_batch(xb, yb, global_batch=gb)
-                steps += 1
+                if len(group) == 1:
+                    self.train_on_batch(xb, yb, global_batch=gb)
+                else:
+                    as_t = lambda a: a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
+                    xs = torch.cat([as_t(g[0]) for g in group], 0)
+                    ys = torch.cat([as_t(g[1]).reshape(-1) for g in group], 0)
+                    self.train_on_batches(xs, ys, steps=len(group), global_batch=gb)
+                steps += len(group)
                 cbs.on_train_batch_end(steps - 1)
+                if pending is not None:
+                    # a batch of another shape ended the group: it is its own step
+                    self.train_on_batch(pending[0], pending[1], global_batch=pending[2])
+                    steps += 1
             logs = self.read_metrics(steps)
             dt = time.time() - t0
             if validation_data is not None:

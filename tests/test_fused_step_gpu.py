@@ -1,0 +1,136 @@
+"""The whole-step kernel (csrc/kernels/fused_step.cu: forward + loss + backward + optimizer of the reference's Keras
+MNIST CNN in one cooperative launch) against two independent oracles: the PyTorch CPU restatement of the model
+(ops/reference.py, driven layer by layer) and the layer-by-layer GPU kernels of round 1."""
+import numpy as np
+import pytest
+import torch
+
+import tfde_b200 as tf
+from tfde_b200.parallel.strategy import Strategy
+
+pytestmark = pytest.mark.gpu
+
+
+def _data(n, seed=0, u8=True):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randint(0, 256, (n, 28, 28, 1), generator=g, dtype=torch.uint8)
+    y = torch.randint(0, 10, (n,), generator=g)
+    return (x if u8 else x.float() / 255.0), y
+
+
+def _opt(kind):
+    return {"sgd": lambda: tf.keras.optimizers.SGD(0.05),
+            "momentum": lambda: tf.keras.optimizers.SGD(0.05, momentum=0.9),
+            "nesterov": lambda: tf.keras.optimizers.SGD(0.05, momentum=0.9, nesterov=True),
+            "adam": lambda: tf.keras.optimizers.Adam(0.002)}[kind]()
+
+
+def _train(device, kind, steps, x, y, bs, seed=7):
+    with Strategy(device=device).scope():
+        m = tf.models.build_and_compile_cnn_model(optimizer=_opt(kind), seed=seed)
+    losses = []
+    for i in range(steps):
+        lo = (i * bs) % (len(x) - bs + 1)
+        m.train_on_batch(x[lo:lo + bs], y[lo:lo + bs])
+        losses.append(m.last_step_loss())
+    return m, losses
+
+
+@pytest.mark.parametrize("kind", ["sgd", "momentum", "nesterov", "adam"])
+def test_whole_step_matches_cpu_reference(kind):
+    x, y = _data(512)
+    mc, lc = _train("cpu", kind, 8, x, y, 64)
+    mg, lg = _train("cuda", kind, 8, x, y, 64)
+    assert mg._fused is not None, "the whole-step kernel must be the path that ran"
+    np.testing.assert_allclose(lg, lc, rtol=2e-4, atol=2e-5)
+    for a, b in zip(mg.get_weights(), mc.get_weights()):
+        np.testing.assert_allclose(a, b, rtol=2e-3, atol=5e-5)
+
+
+@pytest.mark.parametrize("bs", [1, 7, 37, 64])
+def test_whole_step_batch_sizes_and_float_input(bs):
+    x, y = _data(256, seed=3, u8=False)
+    mc, lc = _train("cpu", "sgd", 4, x, y, bs)
+    mg, lg = _train("cuda", "sgd", 4, x, y, bs)
+    assert mg._fused is not None
+    np.testing.assert_allclose(lg, lc, rtol=2e-4, atol=2e-5)
+    for a, b in zip(mg.get_weights(), mc.get_weights()):
+        np.testing.assert_allclose(a, b, rtol=2e-3, atol=5e-5)
+
+
+def test_whole_step_matches_layerwise_kernels(monkeypatch):
+    x, y = _data(512, seed=5)
+    mf, lf = _train("cuda", "sgd", 10, x, y, 64)
+    monkeypatch.setenv("TFDE_FUSED_STEP", "0")
+    ml, ll = _train("cuda", "sgd", 10, x, y, 64)
+    assert mf._fused is not None and ml._fused is None
+    np.testing.assert_allclose(lf, ll, rtol=1e-4, atol=1e-5)
+    for a, b in zip(mf.get_weights(), ml.get_weights()):
+        np.testing.assert_allclose(a, b, rtol=1e-3, atol=2e-5)
+    # gradients of the last step are left in the gradient arena by both paths
+    np.testing.assert_allclose(mf.arena.g.cpu().numpy(), ml.arena.g.cpu().numpy(), rtol=1e-3, atol=1e-5)
+
+
+def test_steps_per_execution_equals_single_steps():
+    """K steps in one launch (each with its own batch) == K launches of one step, bit for bit."""
+    x, y = _data(64 * 6, seed=9)
+    m1, l1 = _train("cuda", "adam", 6, x, y, 64)
+    with Strategy(device="cuda").scope():
+        m2 = tf.models.build_and_compile_cnn_model(optimizer=_opt("adam"), seed=7)
+    m2.train_on_batches(x[:64 * 2], y[:64 * 2], steps=2)
+    la = m2.last_losses()
+    m2.train_on_batches(x[64 * 2:].reshape(4, 64, 28, 28, 1), y[64 * 2:].reshape(4, 64))
+    lb = m2.last_losses()
+    assert m2.optimizer.iterations == 6
+    assert la + lb == l1
+    for a, b in zip(m1.get_weights(), m2.get_weights()):
+        assert np.array_equal(a, b)
+    # device-resident inputs take the same kernel
+    with Strategy(device="cuda").scope():
+        m3 = tf.models.build_and_compile_cnn_model(optimizer=_opt("adam"), seed=7)
+    m3.train_on_batches(x.cuda(), y.cuda(), steps=6)
+    for a, b in zip(m1.get_weights(), m3.get_weights()):
+        assert np.array_equal(a, b)
+
+
+def test_fit_with_steps_per_execution_learns():
+    (xtr, ytr), (xte, yte) = tf.data.mnist.load_data(n_train=2048, n_test=512)
+    m = tf.models.build_and_compile_cnn_model(learning_rate=0.05, seed=1)
+    m.compile(optimizer=tf.keras.optimizers.SGD(0.05),
+              loss=tf.keras.losses.SparseCategoricalCrossentropy(from_logits=True), metrics=["accuracy"],
+              steps_per_execution=8)
+    ds = tf.data.Dataset.from_tensor_slices((xtr[..., None], ytr.astype(np.int64))).shuffle(2048, seed=1).repeat().batch(64)
+    h = m.fit(ds, epochs=3, steps_per_epoch=36, verbose=0)     # 36 = 4 full groups of 8 + one of 4
+    assert m._fused is not None
+    assert m.optimizer.iterations == 108
+    assert h.history["loss"][-1] < h.history["loss"][0]
+    loss, acc = m.evaluate(xte[..., None], yte.astype(np.int64), batch_size=128)
+    assert acc > 0.9, (loss, acc)
+
+
+def test_out_of_range_label_poisons_the_loss_not_the_weights():
+    x, y = _data(64, seed=11)
+    y = y.clone()
+    y[5] = 12
+    with Strategy(device="cuda").scope():
+        m = tf.models.build_and_compile_cnn_model(learning_rate=0.05, seed=2)
+    m.train_on_batch(x, y)
+    assert np.isnan(m.last_step_loss())
+    for w in m.get_weights():
+        assert np.isfinite(w).all()
+
+
+def test_metrics_and_learning_rate_change_between_launches():
+    x, y = _data(256, seed=13)
+    with Strategy(device="cuda").scope():
+        m = tf.models.build_and_compile_cnn_model(learning_rate=0.05, seed=4)
+    m.train_on_batches(x, y, steps=4)
+    met = m.read_metrics(4)
+    ls = m.last_losses()
+    assert met["loss"] == pytest.approx(sum(ls) / 4, rel=1e-5)
+    assert 0.0 <= met["accuracy"] <= 1.0
+    w0 = [w.copy() for w in m.get_weights()]
+    m.optimizer.set_learning_rate(0.0)
+    m.train_on_batches(x, y, steps=4)
+    for a, b in zip(w0, m.get_weights()):
+        assert np.array_equal(a, b), "lr = 0 must leave the weights untouched"

@@ -41,7 +41,8 @@ def test_model_a_matches_cpu_reference(opt):
         np.testing.assert_allclose(a, b, rtol=5e-3, atol=2e-4)
 
 
-def test_model_a_graph_equals_eager():
+def test_model_a_graph_equals_eager(monkeypatch):
+    monkeypatch.setenv("TFDE_FUSED_STEP", "0")     # the layer-by-layer path (the whole-step kernel needs no graph)
     builder = lambda: tf.models.build_and_compile_cnn_model(learning_rate=0.05, seed=3)
     x, y = _data(256)
     m1, l1 = _train(builder, "cuda", 10, x, y, 64, graph=True)
