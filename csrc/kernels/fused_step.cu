@@ -57,26 +57,32 @@ constexpr int FS_MAX_RANKS = 8;
 constexpr int FS_SMALL_MAX = 2048;           // floats of the packed small-tensor block (>= 288+32+64+64*16+16+4)
 constexpr int FS_FLAG_STRIDE = 176;          // >= FS_PIX, multiple of 16
 
-// state words (each on its own 128-byte line)
-constexpr int ST_BAR = 0, ST_TICKET = 32, ST_DONE = 64, ST_BAR0 = 96, ST_TICKET0 = 97, ST_EPOCH0 = 98;
-constexpr int FS_STATE_WORDS = 128;
+// state words (each counter on its own 128-byte line)
+constexpr int ST_BAR = 0, ST_TICKET = 32, ST_DONE = 64, ST_EPOCH0 = 96, ST_GROUP = 128;   // ST_GROUP + 32*g, g < 13
+constexpr int FS_GROUPS = 13;                // two-level ticket: 13 groups of 13 CTAs
+constexpr int FS_STATE_WORDS = ST_GROUP + 32 * FS_GROUPS;
+constexpr int FS_PROF_STAMPS = 16;
+// global scratch: hbuf = h [64][64] | dh [64][64] | dz [64][16] | per-row loss, correct [64][2]
+constexpr int HB_H = 0, HB_DH = FS_B * FS_U, HB_DZ = 2 * FS_B * FS_U, HB_STAT = HB_DZ + FS_B * FS_NC;
+constexpr int FS_HBUF_FLOATS = HB_STAT + 2 * FS_B;
+// cpart = per-CTA conv partials [169][320] | per-group partials [13][320]
+constexpr int FS_CPART_FLOATS = (FS_PIX + FS_GROUPS) * 320;
 
 // shared memory layout (floats)
-constexpr int PATCH_LD = 17, ACT_LD = 68, WS_LD = 68, HS_LD = 65, ZS_LD = 17, DH_LD = 68, DX_LD = 33;
+constexpr int PATCH_LD = 17, ACT_LD = 68, WS_LD = 68, WH_LD = 17, DH_LD = 68, DX_LD = 33, DZ_LD = 17;
 constexpr int SM_PATCH = 0;
 constexpr int SM_ACT = SM_PATCH + FS_B * PATCH_LD;      // actT [32][68]
 constexpr int SM_ARG = SM_ACT + FS_C * ACT_LD;          // argw [64][4] u32
 constexpr int SM_WS = SM_ARG + FS_B * 4;                // ws   [32][68]
-constexpr int SM_HS = SM_WS + FS_C * WS_LD;             // hs   [64][65]
-constexpr int SM_WH = SM_HS + FS_B * HS_LD;             // wh   [64][16] + bh [16]
-constexpr int SM_ZS = SM_WH + FS_U * FS_NC + FS_NC;     // zs   [64][17]
-constexpr int SM_DH = SM_ZS + FS_B * ZS_LD;             // dh   [64][68]
+constexpr int SM_DH = SM_WS + FS_C * WS_LD;             // dh   [64][68]  (tail: staging of the reduced small block)
 constexpr int SM_DX = SM_DH + FS_B * DH_LD;             // dxs  [64][33]
 constexpr int SM_CW = SM_DX + FS_B * DX_LD;             // cw   [10][32]
-constexpr int SM_RED = SM_CW + 10 * FS_C;               // red  [8][10][32]
-constexpr int SM_MISC = SM_RED + 8 * 10 * FS_C;         // misc [64]: labels (int) ; [64..96): loss/correct per warp
-constexpr int SM_TOTAL = SM_MISC + 96;
-static_assert(SM_ACT % 4 == 0 && SM_WS % 4 == 0 && SM_DH % 4 == 0 && SM_WH % 4 == 0 && SM_RED % 4 == 0, "align");
+constexpr int SM_RED = SM_CW + 10 * FS_C;               // red  [8][10][32] (P2: [16][16] float4 ; tail: [80] float4)
+constexpr int SM_WH = SM_RED + 8 * 10 * FS_C;           // whs  [64][17] + bh [16]      (row CTAs only)
+constexpr int SM_ROW = SM_WH + FS_U * WH_LD + FS_NC;    // hrow [64]
+constexpr int SM_HG = SM_ROW + FS_U;                    // hcol [64][4] + dzs [64][17]  (head-gradient CTAs only)
+constexpr int SM_TOTAL = SM_HG + FS_B * 4 + FS_B * DZ_LD;
+static_assert(SM_ACT % 4 == 0 && SM_WS % 4 == 0 && SM_DH % 4 == 0 && SM_RED % 4 == 0 && SM_HG % 4 == 0, "align");
 
 struct Hyper { float lr, mu, b1, b2, eps, gs, lr_t; };
 
@@ -96,6 +102,7 @@ struct FsParams {
   float* gsum[FS_MAX_RANKS];      // gsum[r]: rank r's reduced dense-kernel gradient [FS_ND]
   float* srecv[FS_MAX_RANKS];     // srecv[r]: rank r's small-block receive slots [2][world][FS_SMALL_MAX]
   uint32_t* flags[FS_MAX_RANKS];  // flags[r]: RS [world][176] | AG [176] | S [world]
+  unsigned long long* prof;       // optional [FS_PIX][FS_PROF_STAMPS] globaltimer stamps of the LAST step of a launch
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -122,6 +129,9 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 
 // Bounded spin until *flag >= target (wrap-safe). SYS: the flag is written by a peer GPU. Returns false on
 // timeout or when another CTA already recorded a failure (the whole grid then drains quickly).
+#define FS_STAMP(i) do { if (p.prof && threadIdx.x == 0 && s == p.nsteps - 1) \
+    p.prof[(long)blockIdx.x * FS_PROF_STAMPS + (i)] = globaltimer_ns(); } while (0)
+
 template <bool SYS>
 __device__ __forceinline__ bool wait_flag(const FsParams& p, const uint32_t* flag, uint32_t target, int code,
                                           int who, int where) {
@@ -194,16 +204,15 @@ fused_step_kernel(const FsParams p) {
   float* actT = sm + SM_ACT;
   uint32_t* argw = reinterpret_cast<uint32_t*>(sm + SM_ARG);
   float* ws = sm + SM_WS;
-  float* hs = sm + SM_HS;
-  float* wh = sm + SM_WH;
-  float* bh = wh + FS_U * FS_NC;
-  float* zs = sm + SM_ZS;
   float* dh = sm + SM_DH;
   float* dxs = sm + SM_DX;
   float* cw = sm + SM_CW;
   float* red = sm + SM_RED;
-  int* ylab = reinterpret_cast<int*>(sm + SM_MISC);
-  float* wred = sm + SM_MISC + 64;          // [0..8) loss, [8..16) correct
+  float* whs = sm + SM_WH;
+  float* bh = whs + FS_U * WH_LD;
+  float* hrow = sm + SM_ROW;
+  float* hcol = sm + SM_HG;
+  float* dzs = hcol + FS_B * 4;
   __shared__ int s_last;
 
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -211,14 +220,19 @@ fused_step_kernel(const FsParams p) {
   const int grid = gridDim.x;
   const int W = p.world, R = p.rank;
   const int owner = pix % W;
-  const uint32_t bar0 = p.state[ST_BAR0], ticket0 = p.state[ST_TICKET0], epoch0 = p.state[ST_EPOCH0];
+  const int N = p.ncls;
+  const uint32_t epoch0 = p.state[ST_EPOCH0];
   float* gslice = p.g + p.off_dk + (long)pix * FS_SLICE;
   float* wslice = p.w + p.off_dk + (long)pix * FS_SLICE;
   const long aslice = p.off_dk + (long)pix * FS_SLICE;        // arena index of the slice (optimizer slots)
-  const int nsmall = small_len(p.ncls);
+  const int nsmall = small_len(N);
+  const bool row_cta = pix < FS_B;          // reduces row `pix` of h and runs the classifier head for it
+  const bool hg_cta = pix < 16;             // computes 4 rows of the head kernel gradient
+  const int grp = pix / FS_GROUPS;          // two-level ticket group
 
   for (int s = 0; s < p.nsteps; ++s) {
     const uint32_t e = epoch0 + (uint32_t)s + 1u;
+    const uint32_t bar_base = (e - 1u) * 2u * (uint32_t)grid;
     // hyper-parameters of this step (the ticket winner of the previous step advanced them before releasing us)
     Hyper h;
     {
@@ -227,7 +241,9 @@ fused_step_kernel(const FsParams p) {
       const float b1p = hp->beta1_pow * h.b1, b2p = hp->beta2_pow * h.b2;
       h.lr_t = (p.opt == 3) ? h.lr * sqrtf(1.f - b2p) / (1.f - b1p) : h.lr;
     }
+    FS_STAMP(0);
     // ================================ P1: conv + pool + split-K dense partial =========================
+    int ylab = -1;
     {
       // dense kernel slice (8 KB) -> registers now, shared memory after the conv weights are staged
       float4 wreg[2];
@@ -235,8 +251,14 @@ fused_step_kernel(const FsParams p) {
       for (int i = 0; i < 2; ++i) wreg[i] = __ldcg(reinterpret_cast<const float4*>(wslice) + t + i * FS_THREADS);
       for (int i = t; i < 320; i += FS_THREADS)
         cw[i] = __ldcg(i < 288 ? p.w + p.off_ck + i : p.w + p.off_cb + (i - 288));
-      int yv = -1;
-      if (t < FS_B && t < p.B) yv = (int)p.y[(long)s * p.B + t];
+      if (row_cta) {
+        if (t == 0 && pix < p.B) ylab = (int)p.y[(long)s * p.B + pix];
+        for (int i = t; i < FS_U * FS_NC + FS_NC; i += FS_THREADS) {   // head kernel [64][ncls] -> [64][17], bias
+          float v = 0.f;
+          if (i < FS_U * FS_NC) { const int k = i >> 4, c = i & 15; if (c < N) v = __ldcg(p.w + p.off_hk + k * N + c); whs[k * WH_LD + c] = v; }
+          else { const int c = i - FS_U * FS_NC; if (c < N) v = __ldcg(p.w + p.off_hb + c); bh[c] = v; }
+        }
+      }
       {
         const int b = t >> 2, row = t & 3;
         float v[4] = {0.f, 0.f, 0.f, 0.f};
@@ -255,7 +277,6 @@ fused_step_kernel(const FsParams p) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) patch[b * PATCH_LD + row * 4 + j] = v[j];
       }
-      if (t < FS_B) ylab[t] = yv;
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         const int idx4 = t + i * FS_THREADS, c = idx4 >> 4, n4 = idx4 & 15;
@@ -320,73 +341,53 @@ fused_step_kernel(const FsParams p) {
       for (int i = 0; i < 4; ++i)
         __stcg(dst + (tb * 4 + i) * (FS_U / 4) + tn, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
     }
-    grid_barrier(p, bar0 + (uint32_t)(2 * s + 1) * (uint32_t)grid, 1);
+    FS_STAMP(1);
+    grid_barrier(p, bar_base + (uint32_t)grid, 1);
+    FS_STAMP(2);
 
-    // ================================ P2: reduce the partials -> h =====================================
-    if (pix < 128) {
-      const int f4 = pix * 8 + warp;        // float4 column of h (1024 in all)
-      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-      float4 v[6];
+    // ================================ P2: CTA b < 64 reduces row b of h and runs the head for it ==========
+    if (row_cta) {
+      const int b = pix;
+      {
+        const int f4 = t & 15, g16 = t >> 4;
+        float4 v[11];
 #pragma unroll
-      for (int j = 0; j < 6; ++j) {
-        const int q = lane + 32 * j;
-        v[j] = q < FS_PIX ? __ldcg(reinterpret_cast<const float4*>(p.part) + (long)q * 1024 + f4)
-                          : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < 11; ++j) {
+          const int q = g16 + 16 * j;
+          v[j] = q < FS_PIX ? __ldcg(reinterpret_cast<const float4*>(p.part) + (long)q * 1024 + b * 16 + f4)
+                            : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        float4 a = v[0];
+#pragma unroll
+        for (int j = 1; j < 11; ++j) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
+        reinterpret_cast<float4*>(red)[g16 * 16 + f4] = a;
       }
+      __syncthreads();
+      if (t < 16) {
+        float4 a = reinterpret_cast<const float4*>(red)[t];
 #pragma unroll
-      for (int j = 0; j < 6; ++j) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        a.x += __shfl_xor_sync(0xffffffffu, a.x, o); a.y += __shfl_xor_sync(0xffffffffu, a.y, o);
-        a.z += __shfl_xor_sync(0xffffffffu, a.z, o); a.w += __shfl_xor_sync(0xffffffffu, a.w, o);
-      }
-      if (lane == 0) {
-        const float4 bv = __ldcg(reinterpret_cast<const float4*>(p.w + p.off_db) + (f4 & 15));
+        for (int g16 = 1; g16 < 16; ++g16) {
+          const float4 v = reinterpret_cast<const float4*>(red)[g16 * 16 + t];
+          a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+        }
+        const float4 bv = __ldcg(reinterpret_cast<const float4*>(p.w + p.off_db) + t);
         a.x = fmaxf(a.x + bv.x, 0.f); a.y = fmaxf(a.y + bv.y, 0.f);
         a.z = fmaxf(a.z + bv.z, 0.f); a.w = fmaxf(a.w + bv.w, 0.f);
-        __stcg(reinterpret_cast<float4*>(p.hbuf) + f4, a);
+        *reinterpret_cast<float4*>(hrow + t * 4) = a;
+        __stcg(reinterpret_cast<float4*>(p.hbuf + HB_H) + b * 16 + t, a);
       }
-    }
-    grid_barrier(p, bar0 + (uint32_t)(2 * s + 2) * (uint32_t)grid, 2);
-
-    // ================================ P3: head + loss + backward =======================================
-    {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int f4 = t + i * FS_THREADS, b = f4 >> 4, k4 = f4 & 15;
-        const float4 v = __ldcg(reinterpret_cast<const float4*>(p.hbuf) + f4);
-        float* d = hs + b * HS_LD + k4 * 4;
-        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
-      }
-      for (int i = t; i < FS_U * FS_NC + FS_NC; i += FS_THREADS) {
-        float v = 0.f;
-        if (i < FS_U * FS_NC) { const int k = i >> 4, c = i & 15; if (c < p.ncls) v = __ldcg(p.w + p.off_hk + k * p.ncls + c); }
-        else { const int c = i - FS_U * FS_NC; if (c < p.ncls) v = __ldcg(p.w + p.off_hb + c); }
-        wh[i] = v;
-      }
-    }
-    __syncthreads();
-    {
-      // logits: thread = (row b, classes cg, cg+4, cg+8, cg+12)
-      const int b = t & 63, cg = t >> 6;
-      float a0 = bh[cg], a1 = bh[cg + 4], a2 = bh[cg + 8], a3 = bh[cg + 12];
-#pragma unroll 8
-      for (int k = 0; k < FS_U; ++k) {
-        const float hv = hs[b * HS_LD + k];
-        const float* wr = wh + k * FS_NC + cg;
-        a0 = fmaf(hv, wr[0], a0); a1 = fmaf(hv, wr[4], a1); a2 = fmaf(hv, wr[8], a2); a3 = fmaf(hv, wr[12], a3);
-      }
-      float* z = zs + b * ZS_LD + cg;
-      z[0] = a0; z[4] = a1; z[8] = a2; z[12] = a3;
-    }
-    __syncthreads();
-    {
-      // softmax cross-entropy: warp per row, lane = class
-      float loss = 0.f, correct = 0.f;
-      const int N = p.ncls;
-      for (int r = warp * 8; r < warp * 8 + 8; ++r) {
-        const int y = ylab[r];
-        const float z = lane < N ? zs[r * ZS_LD + lane] : -INFINITY;
+      __syncthreads();
+      if (warp == 0) {
+        // logits (lane = class), softmax cross-entropy, d(logits), dh row
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll 4
+        for (int k = 0; k < FS_U; k += 4) {
+          const float4 hv = *reinterpret_cast<const float4*>(hrow + k);
+          a0 = fmaf(hv.x, whs[(k + 0) * WH_LD + lane], a0); a1 = fmaf(hv.y, whs[(k + 1) * WH_LD + lane], a1);
+          a2 = fmaf(hv.z, whs[(k + 2) * WH_LD + lane], a2); a3 = fmaf(hv.w, whs[(k + 3) * WH_LD + lane], a3);
+        }
+        const int y = __shfl_sync(0xffffffffu, ylab, 0);
+        const float z = lane < N ? ((a0 + a1) + (a2 + a3)) + bh[lane & 15] : -INFINITY;
         float mx = z; int am = lane < N ? lane : 0x7fffffff;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -397,66 +398,84 @@ fused_step_kernel(const FsParams p) {
         const float ex = lane < N ? expf(z - mx) : 0.f;
         const float sum = warp_sum(ex);
         const float prob = ex / sum;
-        const bool live = r < p.B;
+        const bool live = b < p.B;
         const bool valid = live && (unsigned)y < (unsigned)N;
         const float zy = __shfl_sync(0xffffffffu, z, valid ? y : 0);
-        float dz = 0.f;
-        if (valid) dz = (prob - (lane == y ? 1.f : 0.f)) * p.loss_scale;
-        if (lane == 0 && live) {
+        const float dz = valid ? (prob - (lane == y ? 1.f : 0.f)) * p.loss_scale : 0.f;
+        if (lane == 0) {
           // a label outside [0, ncls) poisons the loss (TensorFlow's GPU kernel returns NaN for it) and
           // contributes no gradient
-          loss += valid ? (mx + logf(sum)) - zy : __int_as_float(0x7fc00000);
-          if (valid && am == y) correct += 1.f;
+          const float l = !live ? 0.f : (valid ? (mx + logf(sum)) - zy : __int_as_float(0x7fc00000));
+          __stcg(p.hbuf + HB_STAT + 2 * b, l);
+          __stcg(p.hbuf + HB_STAT + 2 * b + 1, (valid && am == y) ? 1.f : 0.f);
         }
-        if (lane < FS_NC) zs[r * ZS_LD + lane] = (lane < N) ? dz : 0.f;
+        if (lane < FS_NC) __stcg(p.hbuf + HB_DZ + b * FS_NC + lane, dz);
+        // dh[b, n] = (sum_c dz[c] * Wh[n, c]) * (h[b, n] > 0), n = lane and lane + 32
+        float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+        for (int c = 0; c < FS_NC; ++c) {
+          const float dzc = __shfl_sync(0xffffffffu, dz, c);
+          d0 = fmaf(dzc, whs[lane * WH_LD + c], d0);
+          d1 = fmaf(dzc, whs[(lane + 32) * WH_LD + c], d1);
+        }
+        __stcg(p.hbuf + HB_DH + b * FS_U + lane, hrow[lane] > 0.f ? d0 : 0.f);
+        __stcg(p.hbuf + HB_DH + b * FS_U + lane + 32, hrow[lane + 32] > 0.f ? d1 : 0.f);
       }
-      if (lane == 0) { wred[warp] = loss; wred[8 + warp] = correct; }
     }
-    __syncthreads();
+    FS_STAMP(3);
+    grid_barrier(p, bar_base + 2u * (uint32_t)grid, 2);
+    FS_STAMP(4);
+
+    // ================================ P3: backward of this CTA's slice ================================
     {
-      // dh[b, n] = (sum_c dz[b, c] * Wh[n, c]) * (h[b, n] > 0)
-      const int b = t & 63, ng = t >> 6;
-      float zr[FS_NC];
 #pragma unroll
-      for (int c = 0; c < FS_NC; ++c) zr[c] = zs[b * ZS_LD + c];
-#pragma unroll 4
-      for (int j = 0; j < 16; ++j) {
-        const int n = ng * 16 + j;
-        const float* wr = wh + n * FS_NC;
-        float a = 0.f;
-#pragma unroll
-        for (int c = 0; c < FS_NC; ++c) a = fmaf(zr[c], wr[c], a);
-        dh[b * DH_LD + n] = hs[b * HS_LD + n] > 0.f ? a : 0.f;
+      for (int i = 0; i < 4; ++i) {
+        const int f4 = t + i * FS_THREADS, b = f4 >> 4, k4 = f4 & 15;
+        *reinterpret_cast<float4*>(dh + b * DH_LD + k4 * 4) = __ldcg(reinterpret_cast<const float4*>(p.hbuf + HB_DH) + f4);
+      }
+      if (hg_cta) {
+        if (t < FS_B) *reinterpret_cast<float4*>(hcol + t * 4) = __ldcg(reinterpret_cast<const float4*>(p.hbuf + HB_H) + t * 16 + pix);
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(p.hbuf + HB_DZ) + t);
+        float* d = dzs + (t >> 2) * DZ_LD + (t & 3) * 4;
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
       }
     }
     __syncthreads();
-    if (pix == 0) {
-      // head kernel/bias gradient, dense bias gradient, loss / accuracy scalars -> packed small block
+    FS_STAMP(5);
+    if (hg_cta) {
+      // head kernel gradient rows [4*pix, 4*pix+4): dWh[k, c] = sum_b h[b, k] * dz[b, c]   -> packed small block
       float* sp = p.small;
-      const int N = p.ncls;
-      for (int i = t; i < FS_U * N; i += FS_THREADS) {       // dWh[k, c] = sum_b h[b, k] * dz[b, c]
-        const int k = i / N, c = i - k * N;
-        float a = 0.f;
-        for (int b = 0; b < FS_B; ++b) a = fmaf(hs[b * HS_LD + k], zs[b * ZS_LD + c], a);
-        __stcg(sp + 384 + i, a);
-      }
-      if (t < FS_U) {                                        // db[n] = sum_b dh[b, n]
-        float a = 0.f;
-        for (int b = 0; b < FS_B; ++b) a += dh[b * DH_LD + t];
-        __stcg(sp + 320 + t, a);
-      } else if (t < FS_U + N) {                             // dbh[c] = sum_b dz[b, c]
-        const int c = t - FS_U;
-        float a = 0.f;
-        for (int b = 0; b < FS_B; ++b) a += zs[b * ZS_LD + c];
-        __stcg(sp + 384 + FS_U * N + c, a);
-      } else if (t == 128) {
-        float l = 0.f, c = 0.f;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) { l += wred[i]; c += wred[8 + i]; }
-        float* tl = sp + 384 + FS_U * N + N;
-        __stcg(tl + 0, l * p.loss_scale); __stcg(tl + 1, c); __stcg(tl + 2, (float)p.B); __stcg(tl + 3, 0.f);
+      if (t < 64) {
+        const int kk = t >> 4, c = t & 15;
+        if (c < N) {
+          float a = 0.f;
+#pragma unroll 8
+          for (int b = 0; b < FS_B; ++b) a = fmaf(hcol[b * 4 + kk], dzs[b * DZ_LD + c], a);
+          __stcg(sp + 384 + (4 * pix + kk) * N + c, a);
+        }
+      } else if (pix == 0) {
+        if (t < 128) {                                         // dense bias: db[n] = sum_b dh[b, n]
+          const int n = t - 64;
+          float a = 0.f;
+#pragma unroll 8
+          for (int b = 0; b < FS_B; ++b) a += dh[b * DH_LD + n];
+          __stcg(sp + 320 + n, a);
+        } else if (t < 128 + FS_NC) {                          // head bias: dbh[c] = sum_b dz[b, c]
+          const int c = t - 128;
+          if (c < N) {
+            float a = 0.f;
+            for (int b = 0; b < FS_B; ++b) a += dzs[b * DZ_LD + c];
+            __stcg(sp + 384 + FS_U * N + c, a);
+          }
+        } else if (t == 160) {
+          float l = 0.f, c = 0.f;
+          for (int b = 0; b < FS_B; ++b) { l += __ldcg(p.hbuf + HB_STAT + 2 * b); c += __ldcg(p.hbuf + HB_STAT + 2 * b + 1); }
+          float* tl = sp + 384 + FS_U * N + N;
+          __stcg(tl + 0, l * p.loss_scale); __stcg(tl + 1, c); __stcg(tl + 2, (float)p.B); __stcg(tl + 3, 0.f);
+        }
       }
     }
+    FS_STAMP(6);
     // dW_p[c, n] = sum_b act[b, c] * dh[b, n] ; thread tile 2 channels x 4 units (kept in registers until the
     // optimizer / the reduction consumes it)
     float gacc[2][4];
@@ -466,14 +485,19 @@ fused_step_kernel(const FsParams p) {
       for (int i = 0; i < 2; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) gacc[i][j] = 0.f;
-#pragma unroll 8
-      for (int b = 0; b < FS_B; ++b) {
-        const float a0 = actT[(tc * 2) * ACT_LD + b], a1 = actT[(tc * 2 + 1) * ACT_LD + b];
-        const float4 d = *reinterpret_cast<const float4*>(dh + b * DH_LD + tn * 4);
-        gacc[0][0] = fmaf(a0, d.x, gacc[0][0]); gacc[0][1] = fmaf(a0, d.y, gacc[0][1]);
-        gacc[0][2] = fmaf(a0, d.z, gacc[0][2]); gacc[0][3] = fmaf(a0, d.w, gacc[0][3]);
-        gacc[1][0] = fmaf(a1, d.x, gacc[1][0]); gacc[1][1] = fmaf(a1, d.y, gacc[1][1]);
-        gacc[1][2] = fmaf(a1, d.z, gacc[1][2]); gacc[1][3] = fmaf(a1, d.w, gacc[1][3]);
+#pragma unroll 4
+      for (int b = 0; b < FS_B; b += 4) {
+        const float4 a0 = *reinterpret_cast<const float4*>(actT + (tc * 2) * ACT_LD + b);
+        const float4 a1 = *reinterpret_cast<const float4*>(actT + (tc * 2 + 1) * ACT_LD + b);
+        const float av0[4] = {a0.x, a0.y, a0.z, a0.w}, av1[4] = {a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 d = *reinterpret_cast<const float4*>(dh + (b + i) * DH_LD + tn * 4);
+          gacc[0][0] = fmaf(av0[i], d.x, gacc[0][0]); gacc[0][1] = fmaf(av0[i], d.y, gacc[0][1]);
+          gacc[0][2] = fmaf(av0[i], d.z, gacc[0][2]); gacc[0][3] = fmaf(av0[i], d.w, gacc[0][3]);
+          gacc[1][0] = fmaf(av1[i], d.x, gacc[1][0]); gacc[1][1] = fmaf(av1[i], d.y, gacc[1][1]);
+          gacc[1][2] = fmaf(av1[i], d.z, gacc[1][2]); gacc[1][3] = fmaf(av1[i], d.w, gacc[1][3]);
+        }
       }
     }
     if (W == 1) {
@@ -531,6 +555,7 @@ fused_step_kernel(const FsParams p) {
       float acc[10];
 #pragma unroll
       for (int i = 0; i < 10; ++i) acc[i] = 0.f;
+#pragma unroll 2
       for (int b = warp; b < FS_B; b += 8) {
         const float gv = dxs[b * DX_LD + lane];
         const int sel = (argw[b * 4 + (lane >> 3)] >> (2 * (lane & 7))) & 3;
@@ -552,37 +577,43 @@ fused_step_kernel(const FsParams p) {
       for (int wv = 0; wv < 8; ++wv) a += red[wv * 320 + i];
       __stcg(p.cpart + (long)pix * 320 + i, a);
     }
-    // ================================ T: ticket; the last CTA finishes the small tensors ===============
+    // ================================ T: two-level ticket; the last CTA finishes the small tensors ===========
+    FS_STAMP(7);
     __threadfence();
     __syncthreads();
-    if (t == 0) s_last = (atomicAdd(p.state + ST_TICKET, 1u) + 1u == ticket0 + (uint32_t)(s + 1) * (uint32_t)grid);
+    if (t == 0) s_last = (atomicAdd(p.state + ST_GROUP + 32 * grp, 1u) + 1u == e * (uint32_t)FS_GROUPS);
     __syncthreads();
     if (s_last) {
+      // last CTA of its group of 13: reduce the group's conv partials (fixed order)
       __threadfence();
-      // conv partials: 80 float4 columns x 3 interleaved groups, 8 independent loads in flight per thread
-      float4* sgrp = reinterpret_cast<float4*>(red);      // [3][80]
-      if (t < 240) {
-        const int grp = t / 80, c4 = t - grp * 80;
-        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int q0 = grp; q0 < FS_PIX; q0 += 24) {
-          float4 v[8];
+      if (t < 80) {
+        float4 v[FS_GROUPS];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const int q = q0 + 3 * j;
-            v[j] = q < FS_PIX ? __ldcg(reinterpret_cast<const float4*>(p.cpart + (long)q * 320) + c4)
-                              : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
+        for (int j = 0; j < FS_GROUPS; ++j)
+          v[j] = __ldcg(reinterpret_cast<const float4*>(p.cpart + (long)(grp * FS_GROUPS + j) * 320) + t);
+        float4 a = v[0];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
-        }
-        sgrp[grp * 80 + c4] = a;
+        for (int j = 1; j < FS_GROUPS; ++j) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
+        __stcg(reinterpret_cast<float4*>(p.cpart + (long)(FS_PIX + grp) * 320) + t, a);
       }
+      __threadfence();
       __syncthreads();
+      if (t == 0) s_last = (atomicAdd(p.state + ST_TICKET, 1u) + 1u == e * (uint32_t)FS_GROUPS);
+      __syncthreads();
+    }
+    FS_STAMP(8);
+    if (s_last) {
+      __threadfence();
       float* sp = p.small;
       if (t < 80) {
-        const float4 a = sgrp[t], b = sgrp[80 + t], c = sgrp[160 + t];
-        __stcg(reinterpret_cast<float4*>(sp) + t,
-               make_float4((a.x + b.x) + c.x, (a.y + b.y) + c.y, (a.z + b.z) + c.z, (a.w + b.w) + c.w));
+        float4 v[FS_GROUPS];
+#pragma unroll
+        for (int j = 0; j < FS_GROUPS; ++j)
+          v[j] = __ldcg(reinterpret_cast<const float4*>(p.cpart + (long)(FS_PIX + j) * 320) + t);
+        float4 a = v[0];
+#pragma unroll
+        for (int j = 1; j < FS_GROUPS; ++j) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
+        __stcg(reinterpret_cast<float4*>(sp) + t, a);
       }
       __syncthreads();
       // `sp` now holds this replica's packed small gradients + [loss*scale, correct, rows, 0]
@@ -591,10 +622,13 @@ fused_step_kernel(const FsParams p) {
         for (int i = t; i < nsmall; i += FS_THREADS) stage[i] = __ldcg(sp + i);
       } else {
         const int parity = (int)(e & 1u);
-        for (int k = 1; k < W; ++k) {
-          const int peer = (R + k) % W;
-          float* dst = p.srecv[peer] + ((long)parity * W + R) * FS_SMALL_MAX;
-          for (int i = t; i < nsmall; i += FS_THREADS) __stcg(dst + i, __ldcg(sp + i));
+        for (int i = t; i < nsmall; i += FS_THREADS) {
+          const float v = __ldcg(sp + i);
+          stage[i] = v;
+          for (int k = 1; k < W; ++k) {
+            const int peer = (R + k) % W;
+            __stcg(p.srecv[peer] + ((long)parity * W + R) * FS_SMALL_MAX + i, v);
+          }
         }
         __syncthreads();
         if (t < W && t != R) {
@@ -604,18 +638,31 @@ fused_step_kernel(const FsParams p) {
         __syncthreads();
         const float* base = p.srecv[R] + (long)parity * W * FS_SMALL_MAX;
         for (int i = t; i < nsmall; i += FS_THREADS) {
+          const float own = stage[i];
           float a = 0.f;
-          for (int r = 0; r < W; ++r) a += (r == R) ? __ldcg(sp + i) : __ldcg(base + (long)r * FS_SMALL_MAX + i);
+          for (int r = 0; r < W; ++r) a += (r == R) ? own : __ldcg(base + (long)r * FS_SMALL_MAX + i);
           stage[i] = a;
         }
       }
       __syncthreads();
       const int ntrain = nsmall - 4;
-      for (int i = t; i < ntrain; i += FS_THREADS) {
-        const long ai = small_to_arena(p, i);
-        const float gv = stage[i];
-        p.g[ai] = gv;
-        p.w[ai] = update_one(p.opt, __ldcg(p.w + ai), gv, p.s1, p.s2, ai, h);
+      {
+        // up to 8 parameters per thread: all loads first, then the updates (one L2 round trip, not eight)
+        long ai[8]; float wv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int i = t + j * FS_THREADS;
+          ai[j] = i < ntrain ? small_to_arena(p, i) : -1;
+          wv[j] = ai[j] >= 0 ? __ldcg(p.w + ai[j]) : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (ai[j] >= 0) {
+            const float gv = stage[t + j * FS_THREADS];
+            p.g[ai[j]] = gv;
+            p.w[ai[j]] = update_one(p.opt, wv[j], gv, p.s1, p.s2, ai[j], h);
+          }
+        }
       }
       if (t < 4) {
         const float v = stage[ntrain + t];
@@ -629,8 +676,6 @@ fused_step_kernel(const FsParams p) {
         TfdeHParams* hp = p.hp;
         hp->beta1_pow *= hp->beta1; hp->beta2_pow *= hp->beta2; hp->step += 1u;
         if (s == p.nsteps - 1) {
-          p.state[ST_BAR0] = bar0 + (uint32_t)(2 * p.nsteps) * (uint32_t)grid;
-          p.state[ST_TICKET0] = ticket0 + (uint32_t)p.nsteps * (uint32_t)grid;
           p.state[ST_EPOCH0] = epoch0 + (uint32_t)p.nsteps;
           if (p.tails) __threadfence_system();
         }
@@ -638,6 +683,7 @@ fused_step_kernel(const FsParams p) {
         st_release_gpu(p.state + ST_DONE, e);
       }
     }
+    FS_STAMP(9);
     // ================================ dense-kernel slice: reduce across replicas, update ================
     if (W > 1) {
       float4 sum[2];
@@ -678,10 +724,12 @@ fused_step_kernel(const FsParams p) {
       }
     }
     // ================================ wait for the step to be complete ==================================
+    FS_STAMP(10);
     if (s + 1 < p.nsteps) {
       if (t == 0) wait_flag<false>(p, p.state + ST_DONE, e, 11, pix, 3);
       __syncthreads();
     }
+    FS_STAMP(11);
     if (*reinterpret_cast<volatile int*>(p.status) != 0) break;    // a wait timed out somewhere: drain
   }
 }
@@ -705,13 +753,14 @@ struct TfdeFusedStepDesc {
   void* state; void* status;
   unsigned long long timeout_ns;
   void* rs[FS_MAX_RANKS]; void* gsum[FS_MAX_RANKS]; void* srecv[FS_MAX_RANKS]; void* flags[FS_MAX_RANKS];
+  void* prof;
 };
 
 TFDE_API size_t tfde_fused_step_desc_bytes() { return sizeof(TfdeFusedStepDesc); }
 // scratch sizes (floats / words) so that the Python side never hard-codes them
 TFDE_API size_t tfde_fused_step_part_floats() { return (size_t)FS_PIX * FS_B * FS_U; }
-TFDE_API size_t tfde_fused_step_hbuf_floats() { return (size_t)FS_B * FS_U; }
-TFDE_API size_t tfde_fused_step_cpart_floats() { return (size_t)FS_PIX * 320; }
+TFDE_API size_t tfde_fused_step_hbuf_floats() { return (size_t)FS_HBUF_FLOATS; }
+TFDE_API size_t tfde_fused_step_cpart_floats() { return (size_t)FS_CPART_FLOATS; }
 TFDE_API size_t tfde_fused_step_small_floats() { return (size_t)FS_SMALL_MAX; }
 TFDE_API size_t tfde_fused_step_state_words() { return (size_t)FS_STATE_WORDS; }
 TFDE_API size_t tfde_fused_step_rs_floats(int world) { return (size_t)world * FS_ND; }
@@ -719,6 +768,7 @@ TFDE_API size_t tfde_fused_step_gsum_floats() { return (size_t)FS_ND; }
 TFDE_API size_t tfde_fused_step_srecv_floats(int world) { return (size_t)2 * world * FS_SMALL_MAX; }
 TFDE_API size_t tfde_fused_step_flag_words(int world) { return (size_t)(world + 1) * FS_FLAG_STRIDE + 16; }
 TFDE_API int tfde_fused_step_blocks() { return FS_PIX; }
+TFDE_API int tfde_fused_step_prof_stamps() { return FS_PROF_STAMPS; }
 
 // One training step x nsteps of Model A on `stream`. Returns 0, a cudaError_t, or TFDE_ERR_INVALID for shapes the
 // kernel does not cover (the caller then uses the layer-by-layer path).
@@ -762,6 +812,7 @@ TFDE_API int tfde_fused_step(const TfdeFusedStepDesc* d, cudaStream_t stream) {
     p.rs[i] = (float*)d->rs[i]; p.gsum[i] = (float*)d->gsum[i];
     p.srecv[i] = (float*)d->srecv[i]; p.flags[i] = (uint32_t*)d->flags[i];
   }
+  p.prof = (unsigned long long*)d->prof;
   if (d->world > 1)
     for (int i = 0; i < d->world; ++i)
       if (!p.rs[i] || !p.gsum[i] || !p.srecv[i] || !p.flags[i]) return TFDE_ERR_INVALID;

@@ -436,7 +436,7 @@ class Sequential:
         if getattr(self.optimizer, "_bound_to", None) is not self:
             self._bind_optimizer()
         gb = global_batch if global_batch is not None else B * self.strategy.num_replicas_in_sync
-        plan = self.fused_plan(x) if self.device.type == "cuda" else None
+        plan = self.fused_plan() if self.device.type == "cuda" else None
         if plan is None or not plan.supports(x, B):
             for k in range(K):
                 self.train_on_batch(x[k * B:(k + 1) * B], yy[k * B:(k + 1) * B], global_batch=gb)

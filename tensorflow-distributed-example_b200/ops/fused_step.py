@@ -41,6 +41,7 @@ class _FusedStepDesc(ctypes.Structure):
         ("timeout_ns", ctypes.c_ulonglong),
         ("rs", ctypes.c_void_p * MAX_RANKS), ("gsum", ctypes.c_void_p * MAX_RANKS),
         ("srecv", ctypes.c_void_p * MAX_RANKS), ("flags", ctypes.c_void_p * MAX_RANKS),
+        ("prof", ctypes.c_void_p),
     ]
 
 
@@ -51,7 +52,7 @@ for _n, _a, _r in [
     ("tfde_fused_step_small_floats", [], _sz), ("tfde_fused_step_state_words", [], _sz),
     ("tfde_fused_step_rs_floats", [ctypes.c_int], _sz), ("tfde_fused_step_gsum_floats", [], _sz),
     ("tfde_fused_step_srecv_floats", [ctypes.c_int], _sz), ("tfde_fused_step_flag_words", [ctypes.c_int], _sz),
-    ("tfde_fused_step_blocks", [], ctypes.c_int),
+    ("tfde_fused_step_blocks", [], ctypes.c_int), ("tfde_fused_step_prof_stamps", [], ctypes.c_int),
     ("tfde_fused_step", [ctypes.POINTER(_FusedStepDesc), ctypes.c_void_p], ctypes.c_int),
     ("tfde_fused_exec", [ctypes.POINTER(_FusedStepDesc), ctypes.c_void_p, ctypes.c_void_p, _sz, _sz,
                          ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p], ctypes.c_int),
@@ -236,6 +237,32 @@ class FusedStepPlan:
         slot.src = (x, y)                              # keep the pinned sources alive until the copies ran
         self.prev_slot, self.last_slot = self.last_slot, slot
         return slot
+
+    PHASES = ["P1 conv+pool+split-K partial", "B1 grid barrier", "P2 row reduce + head (64 CTAs)", "B2 grid barrier",
+              "P3 load dh (+h, dz)", "P3 head grads (16 CTAs)", "P3 dW/dx/conv partial", "fence + two-level ticket",
+              "tail (winner CTA)", "slice exchange/update", "wait step done"]
+
+    def profile(self, x, y, B, nsteps, global_batch):
+        """Per-phase device time of the LAST step of one launch: globaltimer stamps taken by thread 0 of every CTA.
+        Returns {phase: (mean_us, max_us over CTAs)} plus the step's span. Debug/profiling aid (tools/fused_step_phases.py)."""
+        L = native.load()
+        ns = L.tfde_fused_step_prof_stamps()
+        nb = L.tfde_fused_step_blocks()
+        prof = torch.zeros((nb, ns), dtype=torch.int64, device=self.device)
+        self.desc.prof = prof.data_ptr()
+        try:
+            self.launch(x, y, B, nsteps, global_batch)
+            torch.cuda.synchronize(self.device)
+        finally:
+            self.desc.prof = None
+        t = prof.cpu().double()
+        out = {}
+        for i, name in enumerate(self.PHASES):
+            d = (t[:, i + 1] - t[:, i]) / 1e3
+            out[name] = (float(d.mean()), float(d.max()))
+        out["step span (first start -> last end)"] = (float((t[:, 10].max() - t[:, 0].min()) / 1e3),) * 2
+        out["P1..P3 critical path (max end - min start)"] = (float((t[:, 7].max() - t[:, 0].min()) / 1e3),) * 2
+        return out
 
     def check(self):
         st = self.status.cpu().tolist()
