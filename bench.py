@@ -59,7 +59,7 @@ def parse_args():
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--repeats", type=int, default=5, help="timed regions of K steps each; the median is reported")
     ap.add_argument("--steps-per-execution", type=int, default=0,
-                    help="steps handed to the device per launch (Keras steps_per_execution); 0 = min(steps, 32)")
+                    help="steps handed to the device per launch (Keras steps_per_execution); 0 = min(16, steps/4), so that the copies of one execution overlap the kernel of the previous one")
     ap.add_argument("--no-check", action="store_true", help="skip the replica / CPU-oracle correctness check")
     ap.add_argument("--l2", default="inputs", choices=["inputs", "flush"],
                     help="timing protocol for `value`: distinct inputs from a pool larger than L2 (default) or "
@@ -292,7 +292,7 @@ def run_ours(args):
     K = args.steps
     W = max(args.warmup, 3)
     R = max(1, args.repeats)
-    spe = args.steps_per_execution if args.steps_per_execution > 0 else min(K, 32)
+    spe = args.steps_per_execution if args.steps_per_execution > 0 else max(1, min(16, K // 4))
     if args.dtype == "bf16":
         tf.keras.mixed_precision.set_global_policy("mixed_bfloat16")
     check = correctness_check(tf, strategy, args, rank, world) if not args.no_check else None

@@ -235,10 +235,11 @@ fused_step_kernel(const FsParams p) {
     const uint32_t bar_base = (e - 1u) * 2u * (uint32_t)grid;
     // hyper-parameters of this step (the ticket winner of the previous step advanced them before releasing us)
     Hyper h;
+    float b1p, b2p; uint32_t hp_step;
     {
       const volatile TfdeHParams* hp = p.hp;
       h.lr = hp->lr; h.mu = hp->momentum; h.b1 = hp->beta1; h.b2 = hp->beta2; h.eps = hp->eps; h.gs = hp->grad_scale;
-      const float b1p = hp->beta1_pow * h.b1, b2p = hp->beta2_pow * h.b2;
+      b1p = hp->beta1_pow * h.b1; b2p = hp->beta2_pow * h.b2; hp_step = hp->step;
       h.lr_t = (p.opt == 3) ? h.lr * sqrtf(1.f - b2p) / (1.f - b1p) : h.lr;
     }
     FS_STAMP(0);
@@ -467,11 +468,15 @@ fused_step_kernel(const FsParams p) {
             for (int b = 0; b < FS_B; ++b) a += dzs[b * DZ_LD + c];
             __stcg(sp + 384 + FS_U * N + c, a);
           }
-        } else if (t == 160) {
-          float l = 0.f, c = 0.f;
-          for (int b = 0; b < FS_B; ++b) { l += __ldcg(p.hbuf + HB_STAT + 2 * b); c += __ldcg(p.hbuf + HB_STAT + 2 * b + 1); }
-          float* tl = sp + 384 + FS_U * N + N;
-          __stcg(tl + 0, l * p.loss_scale); __stcg(tl + 1, c); __stcg(tl + 2, (float)p.B); __stcg(tl + 3, 0.f);
+        } else if (t >= 160 && t < 192) {
+          // loss / correct: fixed-order tree over the 64 per-row values (warp 5)
+          float l = __ldcg(p.hbuf + HB_STAT + 2 * lane) + __ldcg(p.hbuf + HB_STAT + 2 * (lane + 32));
+          float c = __ldcg(p.hbuf + HB_STAT + 2 * lane + 1) + __ldcg(p.hbuf + HB_STAT + 2 * (lane + 32) + 1);
+          l = warp_sum(l); c = warp_sum(c);
+          if (lane == 0) {
+            float* tl = sp + 384 + FS_U * N + N;
+            __stcg(tl + 0, l * p.loss_scale); __stcg(tl + 1, c); __stcg(tl + 2, (float)p.B); __stcg(tl + 3, 0.f);
+          }
         }
       }
     }
@@ -673,8 +678,8 @@ fused_step_kernel(const FsParams p) {
       }
       __syncthreads();
       if (t == 0) {
-        TfdeHParams* hp = p.hp;
-        hp->beta1_pow *= hp->beta1; hp->beta2_pow *= hp->beta2; hp->step += 1u;
+        TfdeHParams* hp = p.hp;                 // advance the device-side step state (values read at step start)
+        hp->beta1_pow = b1p; hp->beta2_pow = b2p; hp->step = hp_step + 1u;
         if (s == p.nsteps - 1) {
           p.state[ST_EPOCH0] = epoch0 + (uint32_t)p.nsteps;
           if (p.tails) __threadfence_system();

@@ -37,3 +37,18 @@ def test_p2p_soak_skewed_ranks():
     sys.stdout.write(r.stdout[-4000:])
     sys.stderr.write(r.stderr[-4000:])
     assert r.returncode == 0 and "PASSED" in r.stdout
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_whole_step_kernel_in_kernel_allreduce():
+    """The whole-step kernel's reduce-scatter / all-gather over peer memory: bit-identical replicas, match with a
+    single CPU process on the global batch, and a soak with skewed ranks."""
+    n = min(torch.cuda.device_count(), 8)
+    n = 2 if n < 4 else (4 if n < 8 else 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+           "--master-addr", "127.0.0.1", "--master-port", "29535",
+           os.path.join(ROOT, "tests", "mp_worker_fused.py"), "--soak", "2000"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    sys.stdout.write(r.stdout[-4000:])
+    sys.stderr.write(r.stderr[-4000:])
+    assert r.returncode == 0 and "FUSED STEP CHECKS PASSED" in r.stdout
