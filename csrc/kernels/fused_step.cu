@@ -13,27 +13,30 @@
 //   P1  conv3x3+bias+ReLU+maxpool for pixel p, all rows of the batch (kept in shared memory for the backward
 //       pass), then the split-K partial  h_p[64,64] = act_p[64,32] . W_p[32,64]        -> global partials
 //   B1  grid barrier
-//   P2  CTAs 0..127 reduce 8 float4 columns each over the 169 partials (fixed order), + bias, ReLU -> h
+//   P2  CTA b < 64 reduces row b of h over the 169 partials (fixed order), + bias, ReLU, and runs the classifier
+//       head for that row: logits, softmax-CE, d(logits), dh[b] = d(logits).Wh^T * (h>0)    -> global (20 KB)
 //   B2  grid barrier
-//   P3  every CTA (redundantly, 16 KB of L2 reads instead of a third barrier): head logits, softmax-CE,
-//       d(logits), dh = d(logits).Wh^T * (h>0); then its own slice:  dW_p = act_p^T . dh,
-//       dx_p = dh . W_p^T, pool routing + ReLU mask + conv filter-gradient partial for pixel p.
-//       CTA 0 also produces the head / bias gradients and the loss / accuracy scalars.
-//   T   ticket: the last CTA to arrive reduces the 169 conv partials and applies the optimizer to the small
-//       tensors (conv kernel+bias, dense bias, head kernel+bias), writes the metrics tail, advances the
-//       step counter and releases the next step.
+//   P3  every CTA: dW_p = act_p^T . dh (+ optimizer / reduce-scatter push), dx_p = dh . W_p^T, pool routing + ReLU
+//       mask + conv filter-gradient partial for pixel p. CTAs 0..15 also produce the head-kernel gradient rows,
+//       CTA 0 the bias gradients and the loss / accuracy scalars.
+//   T   two-level ticket (13 groups of 13 CTAs): the last CTA of a group reduces its group's conv partials, the
+//       last group winner reduces the 13 group partials, applies the optimizer to the small tensors (conv
+//       kernel+bias, dense bias, head kernel+bias), writes the metrics tail, advances the step counter and
+//       releases the next step.
 //
 // Multi-GPU (MirroredStrategy / MultiWorkerMirroredStrategy, G12): the gradient all-reduce is part of the SAME
 // kernel, slice by slice, over peer memory (NVLink 5 / NVSwitch) -- GEMM -> reduce-scatter -> all-gather with
 // no NCCL call and no separate launch:
 //   * slice p is owned by rank p % W. Right after computing dW_p a non-owner stores it into the owner's
-//     receive buffer and raises a per-(rank, slice) flag (st.release.sys); it then carries on with dx / the
-//     conv backward while the bytes fly.
-//   * the owner sums the W contributions in rank order (bit-identical replicas), stores the reduced slice
-//     into every peer's `gsum` buffer and raises the per-slice "reduced" flag; every rank applies the
-//     optimizer to its own copy of slice p (optimizer state stays replicated: checkpoints need no gather).
+//     receive buffer; it then carries on with dx / the conv backward while the bytes fly.
+//   * after its ticket the owner sums the W contributions in rank order (bit-identical replicas) and stores the
+//     reduced slice into every peer's `gsum` buffer; every rank applies the optimizer to its own copy of slice p
+//     (optimizer state stays replicated: checkpoints need no gather). A non-owner picks the reduced slice up
+//     lazily, under the NEXT step's convolution, right before its GEMM needs the new weights.
 //   * the small tensors + the 4 metric scalars (G14) are exchanged one-shot by the ticket winner
 //     (double-buffered by step parity).
+//   * transport is flag-in-data: every 8 bytes on the wire carry 4 bytes of payload and the step's epoch, so there
+//     is no separate flag, no st.release.sys fence (an NVLink round trip) -- one-way latency only.
 // All waits are bounded (status word + abort), flags carry a monotonically increasing epoch kept in device
 // memory, so the kernel can be replayed from a CUDA graph.
 //
@@ -129,7 +132,7 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 
 // Bounded spin until *flag >= target (wrap-safe). SYS: the flag is written by a peer GPU. Returns false on
 // timeout or when another CTA already recorded a failure (the whole grid then drains quickly).
-#define FS_STAMP(i) do { if (p.prof && threadIdx.x == 0 && s == p.nsteps - 1) \
+#define FS_STAMP(i) do { if (p.prof && threadIdx.x == 0 && s == (p.nsteps > 1 ? p.nsteps - 2 : 0)) \
     p.prof[(long)blockIdx.x * FS_PROF_STAMPS + (i)] = globaltimer_ns(); } while (0)
 
 template <bool SYS>
@@ -158,6 +161,39 @@ __device__ __forceinline__ void grid_barrier(const FsParams& p, uint32_t target,
     wait_flag<false>(p, p.state + ST_BAR, target, 10, (int)blockIdx.x, where);
   }
   __syncthreads();
+}
+
+// ---- flag-in-data ("LL") transport over peer memory ------------------------------------------------------------
+// A float4 travels as two 16-byte stores {d0, e, d1, e} {d2, e, d3, e}: every 8-byte half carries the epoch it belongs
+// to, so the receiver needs no separate flag and the sender no fence (a st.release.sys costs an NVLink round trip
+// before the flag even leaves) -- one-way latency only, at twice the bytes, the right trade for 8 KB slices.
+// `slot` is the LL image of a float array: float4 index i lives at uint4 index 2i.
+__device__ __forceinline__ void ll_store4(float* slot, long i4, const float4 v, uint32_t e) {
+  uint4* dst = reinterpret_cast<uint4*>(slot) + 2 * i4;
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "r"(__float_as_uint(v.x)), "r"(e),
+               "r"(__float_as_uint(v.y)), "r"(e) : "memory");
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dst + 1), "r"(__float_as_uint(v.z)), "r"(e),
+               "r"(__float_as_uint(v.w)), "r"(e) : "memory");
+}
+__device__ __forceinline__ float4 ll_load4(const FsParams& p, const float* slot, long i4, uint32_t e, int code, int who,
+                                           int where) {
+  const uint4* src = reinterpret_cast<const uint4*>(slot) + 2 * i4;
+  uint4 a, b;
+  const unsigned long long t0 = globaltimer_ns();
+  unsigned spins = 0;
+  for (;;) {
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w) : "l"(src) : "memory");
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "l"(src + 1) : "memory");
+    if (a.y == e && a.w == e && b.y == e && b.w == e) break;
+    if ((++spins & 0xff) == 0) {
+      if (*reinterpret_cast<volatile int*>(p.status) != 0) break;
+      if (globaltimer_ns() - t0 > p.timeout_ns) {
+        if (atomicCAS(p.status, 0, code) == 0) { p.status[1] = (int)e; p.status[2] = who; p.status[3] = where; }
+        break;
+      }
+    }
+  }
+  return make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
 }
 
 __device__ __forceinline__ float update_one(int opt, float w, float g, float* s1, float* s2, long i, const Hyper& h) {
@@ -197,6 +233,56 @@ __device__ __forceinline__ long small_to_arena(const FsParams& p, int i) {
   return p.n + (i - p.ncls);
 }
 
+// Completes the cross-replica reduction of this CTA's dense-kernel slice for epoch `e` and applies the optimizer:
+// the owner sums the W contributions in rank order and stores the reduced slice into every peer's `gsum`; a
+// non-owner picks the reduced slice up from its own `gsum`. Every rank then updates its copy (global memory and the
+// shared-memory copy `ws` that the next step's GEMMs read).
+__device__ __forceinline__ void finish_slice(const FsParams& p, uint32_t e, int pix, int owner, const float (&gacc)[2][4],
+                                             float* ws, float* gslice, float* wslice, long aslice, const Hyper& h) {
+  const int t = threadIdx.x, tc = t >> 4, tn = t & 15;
+  const int W = p.world, R = p.rank;
+  float4 sum[2];
+  if (owner == R) {
+    const float* base = p.rs[R] + (long)pix * (2 * FS_SLICE);
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int i4 = (tc * 2 + i) * (FS_U / 4) + tn;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int r0 = 0; r0 < W; r0 += 4) {          // rank order, four peers' loads in flight at a time
+        float4 v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int r = r0 + j;
+          if (r < W)
+            v[j] = (r == R) ? make_float4(gacc[i][0], gacc[i][1], gacc[i][2], gacc[i][3])
+                            : ll_load4(p, base + (long)r * (2 * FS_ND), i4, e, 22, r, pix);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (r0 + j < W) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
+      }
+      sum[i] = a;
+      for (int k = 1; k < W; ++k) {
+        const int peer = (R + k) % W;
+        ll_store4(p.gsum[peer] + (long)pix * (2 * FS_SLICE), i4, a, e);
+      }
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+      sum[i] = ll_load4(p, p.gsum[R] + (long)pix * (2 * FS_SLICE), (tc * 2 + i) * (FS_U / 4) + tn, e, 23, owner, pix);
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int c = tc * 2 + i, off = c * FS_U + tn * 4;
+    float4* wsm = reinterpret_cast<float4*>(ws + c * WS_LD + tn * 4);
+    const float4 nw = update_four(p.opt, *wsm, sum[i], p.s1, p.s2, aslice + off, h);
+    *wsm = nw;
+    *reinterpret_cast<float4*>(gslice + off) = sum[i];
+    *reinterpret_cast<float4*>(wslice + off) = nw;
+  }
+}
+
 __global__ void __launch_bounds__(FS_THREADS, 2)
 fused_step_kernel(const FsParams p) {
   extern __shared__ __align__(16) float sm[];
@@ -229,6 +315,10 @@ fused_step_kernel(const FsParams p) {
   const bool row_cta = pix < FS_B;          // reduces row `pix` of h and runs the classifier head for it
   const bool hg_cta = pix < 16;             // computes 4 rows of the head kernel gradient
   const int grp = pix / FS_GROUPS;          // two-level ticket group
+  __shared__ Hyper s_hprev;                 // hyper-parameters of the step whose slice exchange is still pending
+  bool pending = false;                     // W > 1: the previous step's slice is reduced/updated lazily, right
+  float gacc[2][4];                         //        before this step's GEMM needs it (off the critical path)
+  const int tc = t >> 4, tn = t & 15;
 
   for (int s = 0; s < p.nsteps; ++s) {
     const uint32_t e = epoch0 + (uint32_t)s + 1u;
@@ -247,9 +337,12 @@ fused_step_kernel(const FsParams p) {
     int ylab = -1;
     {
       // dense kernel slice (8 KB) -> registers now, shared memory after the conv weights are staged
+      // (first step of a launch only: afterwards the shared-memory copy is kept current by this CTA's own updates)
       float4 wreg[2];
+      if (s == 0) {
 #pragma unroll
-      for (int i = 0; i < 2; ++i) wreg[i] = __ldcg(reinterpret_cast<const float4*>(wslice) + t + i * FS_THREADS);
+        for (int i = 0; i < 2; ++i) wreg[i] = __ldcg(reinterpret_cast<const float4*>(wslice) + t + i * FS_THREADS);
+      }
       for (int i = t; i < 320; i += FS_THREADS)
         cw[i] = __ldcg(i < 288 ? p.w + p.off_ck + i : p.w + p.off_cb + (i - 288));
       if (row_cta) {
@@ -278,10 +371,12 @@ fused_step_kernel(const FsParams p) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) patch[b * PATCH_LD + row * 4 + j] = v[j];
       }
+      if (s == 0) {
 #pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        const int idx4 = t + i * FS_THREADS, c = idx4 >> 4, n4 = idx4 & 15;
-        *reinterpret_cast<float4*>(ws + c * WS_LD + n4 * 4) = wreg[i];
+        for (int i = 0; i < 2; ++i) {
+          const int idx4 = t + i * FS_THREADS, c = idx4 >> 4, n4 = idx4 & 15;
+          *reinterpret_cast<float4*>(ws + c * WS_LD + n4 * 4) = wreg[i];
+        }
       }
     }
     __syncthreads();
@@ -316,6 +411,12 @@ fused_step_kernel(const FsParams p) {
         bits |= (uint32_t)besti << (2 * cc);
       }
       argw[b * 4 + cg] = bits;
+    }
+    if (pending) {
+      // the previous step's slice: its reduce-scatter contributions / reduced values arrived while the tail and this
+      // step's convolution ran
+      finish_slice(p, e - 1u, pix, owner, gacc, ws, gslice, wslice, aslice, s_hprev);
+      pending = false;
     }
     __syncthreads();
     {
@@ -483,8 +584,6 @@ fused_step_kernel(const FsParams p) {
     FS_STAMP(6);
     // dW_p[c, n] = sum_b act[b, c] * dh[b, n] ; thread tile 2 channels x 4 units (kept in registers until the
     // optimizer / the reduction consumes it)
-    float gacc[2][4];
-    const int tc = t >> 4, tn = t & 15;
     {
 #pragma unroll
       for (int i = 0; i < 2; ++i)
@@ -505,25 +604,12 @@ fused_step_kernel(const FsParams p) {
         }
       }
     }
-    if (W == 1) {
-      // single replica: the optimizer is the epilogue of the filter-gradient tile
-#pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        const int c = tc * 2 + i, off = c * FS_U + tn * 4;
-        const float4 gv = make_float4(gacc[i][0], gacc[i][1], gacc[i][2], gacc[i][3]);
-        const float4 wv = *reinterpret_cast<const float4*>(ws + c * WS_LD + tn * 4);
-        *reinterpret_cast<float4*>(gslice + off) = gv;
-        *reinterpret_cast<float4*>(wslice + off) = update_four(p.opt, wv, gv, p.s1, p.s2, aslice + off, h);
-      }
-    } else if (owner != R) {
-      // GEMM -> reduce-scatter: the tile goes straight into the owner's receive buffer over NVLink
-      float* dst = p.rs[owner] + (long)R * FS_ND + (long)pix * FS_SLICE;
+    if (W > 1 && owner != R) {
+      // GEMM -> reduce-scatter: the tile goes straight into the owner's receive buffer over NVLink (flag-in-data)
+      float* dst = p.rs[owner] + (long)R * (2 * FS_ND) + (long)pix * (2 * FS_SLICE);
 #pragma unroll
       for (int i = 0; i < 2; ++i)
-        __stcg(reinterpret_cast<float4*>(dst + (tc * 2 + i) * FS_U + tn * 4),
-               make_float4(gacc[i][0], gacc[i][1], gacc[i][2], gacc[i][3]));
-      __syncthreads();
-      if (t == 0) st_release_sys(p.flags[owner] + R * FS_FLAG_STRIDE + pix, e);
+        ll_store4(dst, (tc * 2 + i) * (FS_U / 4) + tn, make_float4(gacc[i][0], gacc[i][1], gacc[i][2], gacc[i][3]), e);
     }
     {
       // dx_p[b, c] = sum_n dh[b, n] * W_p[c, n], masked by ReLU; thread tile 4 rows x 2 channels
@@ -555,6 +641,19 @@ fused_step_kernel(const FsParams p) {
       }
     }
     __syncthreads();
+    if (W == 1) {
+      // single replica: the optimizer is the epilogue of the filter-gradient tile (dx above consumed the old weights)
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int c = tc * 2 + i, off = c * FS_U + tn * 4;
+        const float4 gv = make_float4(gacc[i][0], gacc[i][1], gacc[i][2], gacc[i][3]);
+        float4* wsm = reinterpret_cast<float4*>(ws + c * WS_LD + tn * 4);
+        const float4 nw = update_four(p.opt, *wsm, gv, p.s1, p.s2, aslice + off, h);
+        *wsm = nw;
+        *reinterpret_cast<float4*>(gslice + off) = gv;
+        *reinterpret_cast<float4*>(wslice + off) = nw;
+      }
+    }
     {
       // conv filter/bias gradient partial of this pixel: lane = channel, warp strides over the rows
       float acc[10];
@@ -626,27 +725,23 @@ fused_step_kernel(const FsParams p) {
       if (W == 1) {
         for (int i = t; i < nsmall; i += FS_THREADS) stage[i] = __ldcg(sp + i);
       } else {
+        // one-shot exchange of the packed small block (flag-in-data, double-buffered by step parity)
         const int parity = (int)(e & 1u);
-        for (int i = t; i < nsmall; i += FS_THREADS) {
-          const float v = __ldcg(sp + i);
-          stage[i] = v;
+        const int n4 = (nsmall + 3) >> 2;
+        for (int i = t; i < n4; i += FS_THREADS) {
+          float4 v;
+          v.x = __ldcg(sp + 4 * i); v.y = 4 * i + 1 < nsmall ? __ldcg(sp + 4 * i + 1) : 0.f;
+          v.z = 4 * i + 2 < nsmall ? __ldcg(sp + 4 * i + 2) : 0.f; v.w = 4 * i + 3 < nsmall ? __ldcg(sp + 4 * i + 3) : 0.f;
           for (int k = 1; k < W; ++k) {
             const int peer = (R + k) % W;
-            __stcg(p.srecv[peer] + ((long)parity * W + R) * FS_SMALL_MAX + i, v);
+            ll_store4(p.srecv[peer] + ((long)parity * W + R) * (2 * FS_SMALL_MAX), i, v, e);
           }
-        }
-        __syncthreads();
-        if (t < W && t != R) {
-          st_release_sys(p.flags[t] + (W + 1) * FS_FLAG_STRIDE + R, e);
-          wait_flag<true>(p, p.flags[R] + (W + 1) * FS_FLAG_STRIDE + t, e, 21, t, pix);
-        }
-        __syncthreads();
-        const float* base = p.srecv[R] + (long)parity * W * FS_SMALL_MAX;
-        for (int i = t; i < nsmall; i += FS_THREADS) {
-          const float own = stage[i];
-          float a = 0.f;
-          for (int r = 0; r < W; ++r) a += (r == R) ? own : __ldcg(base + (long)r * FS_SMALL_MAX + i);
-          stage[i] = a;
+          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int r = 0; r < W; ++r) {
+            const float4 u = (r == R) ? v : ll_load4(p, p.srecv[R] + ((long)parity * W + r) * (2 * FS_SMALL_MAX), i, e, 21, r, pix);
+            a.x += u.x; a.y += u.y; a.z += u.z; a.w += u.w;
+          }
+          stage[4 * i] = a.x; stage[4 * i + 1] = a.y; stage[4 * i + 2] = a.z; stage[4 * i + 3] = a.w;
         }
       }
       __syncthreads();
@@ -691,41 +786,13 @@ fused_step_kernel(const FsParams p) {
     FS_STAMP(9);
     // ================================ dense-kernel slice: reduce across replicas, update ================
     if (W > 1) {
-      float4 sum[2];
-      if (owner == R) {
-        if (t < W && t != R) wait_flag<true>(p, p.flags[R] + t * FS_FLAG_STRIDE + pix, e, 22, t, pix);
-        __syncthreads();
-        const float* base = p.rs[R] + (long)pix * FS_SLICE;
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          const int off = (tc * 2 + i) * FS_U + tn * 4;
-          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-          for (int r = 0; r < W; ++r) {
-            const float4 v = (r == R) ? make_float4(gacc[i][0], gacc[i][1], gacc[i][2], gacc[i][3])
-                                      : __ldcg(reinterpret_cast<const float4*>(base + (long)r * FS_ND + off));
-            a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
-          }
-          sum[i] = a;
-          for (int k = 1; k < W; ++k) {
-            const int peer = (R + k) % W;
-            __stcg(reinterpret_cast<float4*>(p.gsum[peer] + (long)pix * FS_SLICE + off), a);
-          }
-        }
-        __syncthreads();
-        if (t < W && t != R) st_release_sys(p.flags[t] + W * FS_FLAG_STRIDE + pix, e);
+      if (owner == R || s + 1 == p.nsteps) {
+        // owner: its peers sent their contributions in the middle of P3, they are here by now -> reduce, publish the
+        // reduced slice, update. (Everyone on the last step of a launch: drain.)
+        finish_slice(p, e, pix, owner, gacc, ws, gslice, wslice, aslice, h);
       } else {
-        if (t == 0) wait_flag<true>(p, p.flags[R] + W * FS_FLAG_STRIDE + pix, e, 23, owner, pix);
-        __syncthreads();
-#pragma unroll
-        for (int i = 0; i < 2; ++i)
-          sum[i] = __ldcg(reinterpret_cast<const float4*>(p.gsum[R] + (long)pix * FS_SLICE + (tc * 2 + i) * FS_U + tn * 4));
-      }
-#pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        const int c = tc * 2 + i, off = c * FS_U + tn * 4;
-        const float4 wv = *reinterpret_cast<const float4*>(ws + c * WS_LD + tn * 4);
-        *reinterpret_cast<float4*>(gslice + off) = sum[i];
-        *reinterpret_cast<float4*>(wslice + off) = update_four(p.opt, wv, sum[i], p.s1, p.s2, aslice + off, h);
+        pending = true;                       // non-owner: picks the reduced slice up under the next step's convolution
+        if (t == 0) s_hprev = h;
       }
     }
     // ================================ wait for the step to be complete ==================================
@@ -768,9 +835,9 @@ TFDE_API size_t tfde_fused_step_hbuf_floats() { return (size_t)FS_HBUF_FLOATS; }
 TFDE_API size_t tfde_fused_step_cpart_floats() { return (size_t)FS_CPART_FLOATS; }
 TFDE_API size_t tfde_fused_step_small_floats() { return (size_t)FS_SMALL_MAX; }
 TFDE_API size_t tfde_fused_step_state_words() { return (size_t)FS_STATE_WORDS; }
-TFDE_API size_t tfde_fused_step_rs_floats(int world) { return (size_t)world * FS_ND; }
-TFDE_API size_t tfde_fused_step_gsum_floats() { return (size_t)FS_ND; }
-TFDE_API size_t tfde_fused_step_srecv_floats(int world) { return (size_t)2 * world * FS_SMALL_MAX; }
+TFDE_API size_t tfde_fused_step_rs_floats(int world) { return (size_t)world * 2 * FS_ND; }       // LL image: 2x
+TFDE_API size_t tfde_fused_step_gsum_floats() { return (size_t)2 * FS_ND; }
+TFDE_API size_t tfde_fused_step_srecv_floats(int world) { return (size_t)2 * world * 2 * FS_SMALL_MAX; }
 TFDE_API size_t tfde_fused_step_flag_words(int world) { return (size_t)(world + 1) * FS_FLAG_STRIDE + 16; }
 TFDE_API int tfde_fused_step_blocks() { return FS_PIX; }
 TFDE_API int tfde_fused_step_prof_stamps() { return FS_PROF_STAMPS; }

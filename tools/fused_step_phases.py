@@ -16,7 +16,10 @@ def main():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--batch", type=int, default=64)
     a = ap.parse_args()
-    m = tf.models.build_and_compile_cnn_model(learning_rate=0.001, seed=1)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    strategy = tf.distribute.MirroredStrategy() if world > 1 else tf.distribute.get_strategy()
+    with strategy.scope():
+        m = tf.models.build_and_compile_cnn_model(learning_rate=0.001, seed=1)
     B, K = a.batch, a.steps
     g = torch.Generator().manual_seed(0)
     x = torch.randint(0, 256, (K * B, 28, 28, 1), generator=g, dtype=torch.uint8).cuda()
@@ -25,10 +28,16 @@ def main():
     m.sync()
     plan = m.fused_plan()
     for trial in range(3):
-        res = plan.profile(x, y, B, K, B)
-    print(f"whole-step kernel, batch {B}, last step of a {K}-step launch (us: mean over CTAs / max over CTAs)")
-    for k, v in res.items():
-        print(f"  {k:<40s} {v[0]:8.2f} {v[1]:8.2f}")
+        res = plan.profile(x, y, B, K, B * world)
+    if strategy.rank == 0:
+        print(f"whole-step kernel, {world} GPU(s), batch {B}/GPU, step {max(K - 2, 0)} of a {K}-step launch "
+              f"(us: mean over CTAs / max over CTAs, rank 0)")
+        for k, v in res.items():
+            print(f"  {k:<44s} {v[0]:8.2f} {v[1]:8.2f}")
+    if world > 1:
+        import torch.distributed as dist
+        strategy.shutdown()
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
