@@ -196,27 +196,26 @@ __device__ __forceinline__ float4 ll_load4(const FsParams& p, const float* slot,
   return make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
 }
 
+// Optimizer arithmetic with every rounding spelled out (no FMA-contraction freedom): the same update is inlined at
+// several call sites (owner / non-owner, immediate / deferred) and replicas must stay bit-identical, so the compiler
+// must not be free to fuse `a*b + c*d` one way here and the other way there.
 __device__ __forceinline__ float update_one(int opt, float w, float g, float* s1, float* s2, long i, const Hyper& h) {
-  g *= h.gs;
-  if (opt == 0) return w - h.lr * g;
+  g = __fmul_rn(g, h.gs);
+  if (opt == 0) return __fmaf_rn(-h.lr, g, w);
   if (opt == 1 || opt == 2) {
-    const float v = h.mu * s1[i] - h.lr * g;
+    const float lg = __fmul_rn(h.lr, g);
+    const float v = __fmaf_rn(h.mu, s1[i], -lg);
     s1[i] = v;
-    return w + (opt == 2 ? (h.mu * v - h.lr * g) : v);
+    return __fadd_rn(w, opt == 2 ? __fmaf_rn(h.mu, v, -lg) : v);
   }
-  const float m = h.b1 * s1[i] + (1.f - h.b1) * g;
-  const float v = h.b2 * s2[i] + (1.f - h.b2) * g * g;
+  const float m = __fmaf_rn(h.b1, s1[i], __fmul_rn(1.f - h.b1, g));
+  const float v = __fmaf_rn(h.b2, s2[i], __fmul_rn(__fmul_rn(1.f - h.b2, g), g));
   s1[i] = m; s2[i] = v;
-  return w - h.lr_t * m / (sqrtf(v) + h.eps);
+  return __fsub_rn(w, __fdiv_rn(__fmul_rn(h.lr_t, m), __fadd_rn(__fsqrt_rn(v), h.eps)));
 }
 
 __device__ __forceinline__ float4 update_four(int opt, float4 w, float4 g, float* s1, float* s2, long i, const Hyper& h) {
   float4 o;
-  if (opt == 0) {
-    o.x = w.x - h.lr * (g.x * h.gs); o.y = w.y - h.lr * (g.y * h.gs);
-    o.z = w.z - h.lr * (g.z * h.gs); o.w = w.w - h.lr * (g.w * h.gs);
-    return o;
-  }
   o.x = update_one(opt, w.x, g.x, s1, s2, i, h);     o.y = update_one(opt, w.y, g.y, s1, s2, i + 1, h);
   o.z = update_one(opt, w.z, g.z, s1, s2, i + 2, h); o.w = update_one(opt, w.w, g.w, s1, s2, i + 3, h);
   return o;

@@ -52,7 +52,16 @@ def test_whole_step_matches_cpu_reference(kind):
     mg, lg = _train("cuda", kind, 8, x, y, 64)
     assert mg._fused is not None, "the whole-step kernel must be the path that ran"
     np.testing.assert_allclose(lg, lc, rtol=2e-4, atol=2e-5)
-    _close(mg.get_weights(), mc.get_weights(), 5e-2 if kind == "adam" else 2e-3)
+    if kind == "adam":
+        # Adam turns the first noise-level gradient of a so-far-dead unit into a full learning-rate step, so a ReLU
+        # decision that flips under a different summation order moves a handful of weights by ~lr: bound the size of
+        # any deviation by one such step and the number of deviating weights
+        for a, b in zip(mg.get_weights(), mc.get_weights()):
+            d = np.abs(a - b)
+            assert d.max() < 1.5 * 0.002, d.max()
+            assert np.median(d) < 1e-5 and (d > 2e-4).mean() < 1e-2, (np.median(d), (d > 2e-4).mean())
+    else:
+        _close(mg.get_weights(), mc.get_weights())
 
 
 @pytest.mark.parametrize("bs", [1, 7, 37, 64])
