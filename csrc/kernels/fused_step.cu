@@ -85,6 +85,8 @@ constexpr int SM_WH = SM_RED + 8 * 10 * FS_C;           // whs  [64][17] + bh [1
 constexpr int SM_ROW = SM_WH + FS_U * WH_LD + FS_NC;    // hrow [64]
 constexpr int SM_HG = SM_ROW + FS_U;                    // hcol [64][4] + dzs [64][17]  (head-gradient CTAs only)
 constexpr int SM_TOTAL = SM_HG + FS_B * 4 + FS_B * DZ_LD;
+constexpr int FS_SMALL_F4 = (288 + 32 + 64 + 64 * FS_NC + FS_NC + 4 + 3) / 4;    // float4 groups of the largest small block
+static_assert(SM_DH + FS_MAX_RANKS * FS_SMALL_F4 * 4 <= SM_TOTAL, "tail exchange staging must fit in dh..end");
 static_assert(SM_ACT % 4 == 0 && SM_WS % 4 == 0 && SM_DH % 4 == 0 && SM_RED % 4 == 0 && SM_HG % 4 == 0, "align");
 
 struct Hyper { float lr, mu, b1, b2, eps, gs, lr_t; };
@@ -724,23 +726,58 @@ fused_step_kernel(const FsParams p) {
       if (W == 1) {
         for (int i = t; i < nsmall; i += FS_THREADS) stage[i] = __ldcg(sp + i);
       } else {
-        // one-shot exchange of the packed small block (flag-in-data, double-buffered by step parity)
+        // one-shot exchange of the packed small block (flag-in-data, double-buffered by step parity): push the own
+        // block to every peer, gather the peers' blocks into shared memory with all loads in flight at once (not one
+        // spin per peer), then sum in rank order
         const int parity = (int)(e & 1u);
         const int n4 = (nsmall + 3) >> 2;
+        float4* stage4 = reinterpret_cast<float4*>(stage);
+        float4* rbuf4 = stage4 + FS_SMALL_F4;                // [(W-1)][n4], spans dh .. end of shared memory (all dead here)
         for (int i = t; i < n4; i += FS_THREADS) {
           float4 v;
           v.x = __ldcg(sp + 4 * i); v.y = 4 * i + 1 < nsmall ? __ldcg(sp + 4 * i + 1) : 0.f;
           v.z = 4 * i + 2 < nsmall ? __ldcg(sp + 4 * i + 2) : 0.f; v.w = 4 * i + 3 < nsmall ? __ldcg(sp + 4 * i + 3) : 0.f;
+          stage4[i] = v;
           for (int k = 1; k < W; ++k) {
             const int peer = (R + k) % W;
             ll_store4(p.srecv[peer] + ((long)parity * W + R) * (2 * FS_SMALL_MAX), i, v, e);
           }
+        }
+        const int tot = (W - 1) * n4;
+        const float* rbase = p.srecv[R] + (long)parity * W * (2 * FS_SMALL_MAX);
+        for (int base = t; base < tot; base += 4 * FS_THREADS) {
+          uint4 ra[4], rb[4];
+          const uint4* src[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int idx = base + j * FS_THREADS;
+            const int k1 = idx < tot ? idx / n4 : 0, i4 = idx < tot ? idx - k1 * n4 : 0;
+            const int peer = (R + k1 + 1) % W;
+            src[j] = reinterpret_cast<const uint4*>(rbase + (long)peer * (2 * FS_SMALL_MAX)) + 2 * i4;
+            asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(ra[j].x), "=r"(ra[j].y), "=r"(ra[j].z), "=r"(ra[j].w) : "l"(src[j]) : "memory");
+            asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(rb[j].x), "=r"(rb[j].y), "=r"(rb[j].z), "=r"(rb[j].w) : "l"(src[j] + 1) : "memory");
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int idx = base + j * FS_THREADS;
+            if (idx < tot) {
+              float4 v = make_float4(__uint_as_float(ra[j].x), __uint_as_float(ra[j].z), __uint_as_float(rb[j].x), __uint_as_float(rb[j].z));
+              if (!(ra[j].y == e && ra[j].w == e && rb[j].y == e && rb[j].w == e)) {
+                const int k1 = idx / n4, i4 = idx - k1 * n4, peer = (R + k1 + 1) % W;
+                v = ll_load4(p, rbase + (long)peer * (2 * FS_SMALL_MAX), i4, e, 21, peer, pix);     // not there yet: spin
+              }
+              rbuf4[idx] = v;
+            }
+          }
+        }
+        __syncthreads();
+        for (int i = t; i < n4; i += FS_THREADS) {
           float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
           for (int r = 0; r < W; ++r) {
-            const float4 u = (r == R) ? v : ll_load4(p, p.srecv[R] + ((long)parity * W + r) * (2 * FS_SMALL_MAX), i, e, 21, r, pix);
+            const float4 u = (r == R) ? stage4[i] : rbuf4[((r - R - 1 + W) % W) * n4 + i];
             a.x += u.x; a.y += u.y; a.z += u.z; a.w += u.w;
           }
-          stage[4 * i] = a.x; stage[4 * i + 1] = a.y; stage[4 * i + 2] = a.z; stage[4 * i + 3] = a.w;
+          stage4[i] = a;
         }
       }
       __syncthreads();
