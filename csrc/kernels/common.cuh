@@ -49,6 +49,25 @@ static inline cudaError_t tfde_launch(void (*kernel)(KArgs...), dim3 grid, dim3 
   return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) applies to the CURRENT device only, so the "already raised" note a
+// launcher keeps must be per device (a process may drive several GPUs, e.g. mirrored evaluation). `done` is the
+// launcher's own static array of TFDE_MAX_DEVICES entries.
+constexpr int TFDE_MAX_DEVICES = 64;
+template <typename K>
+static inline cudaError_t tfde_ensure_dyn_smem(K kernel, size_t smem, size_t (&done)[TFDE_MAX_DEVICES]) {
+  if (smem <= 48 * 1024) return cudaSuccess;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  size_t& d = done[dev & (TFDE_MAX_DEVICES - 1)];
+  if (smem > d) {
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    d = smem;
+  }
+  return cudaSuccess;
+}
+
 static __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -369,12 +369,8 @@ template <int BN, int MT>
 int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcEpilogue& ep, int M, int N, int K, cudaStream_t stream) {
   constexpr int STAGES = (MT == 2) ? 3 : TC_STAGES;
   constexpr size_t smem = (size_t)STAGES * (MT * TC_BM * TC_BK * 2 + BN * TC_BK * 2) + 1024;
-  static bool configured = false;
-  if (!configured) {
-    const cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    configured = true;
-  }
+  static size_t configured[TFDE_MAX_DEVICES] = {};
+  { const cudaError_t e = tfde_ensure_dyn_smem(gemm_bf16_tcgen05_kernel<BN, MT>, smem, configured); if (e != cudaSuccess) return (int)e; }
   dim3 grid((N + BN - 1) / BN, (M + TC_BM * MT - 1) / (TC_BM * MT));
   gemm_bf16_tcgen05_kernel<BN, MT><<<grid, TC_THREADS, smem, stream>>>(ta, tb, ep, K);
   TFDE_RETURN_LAUNCH_STATUS();

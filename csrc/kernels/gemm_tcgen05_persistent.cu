@@ -509,12 +509,8 @@ int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, 
              size_t ws_bytes, cudaStream_t stream) {
   constexpr int STAGES = (BN == 256) ? 4 : 6;
   constexpr size_t smem = (size_t)STAGES * (P_BM * P_BK * 2 + BN * P_BK * 2) + 4 * 32 * P_STG_PITCH + 1024;
-  static bool configured = false;
-  if (!configured) {
-    const cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    configured = true;
-  }
+  static size_t configured[TFDE_MAX_DEVICES] = {};
+  { const cudaError_t e = tfde_ensure_dyn_smem(gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ>, smem, configured); if (e != cudaSuccess) return (int)e; }
   const int tiles_m = (M + P_BM - 1) / P_BM, tiles_n = (N + BN - 1) / BN;
   const int tiles = tiles_m * tiles_n;
   const int num_k = (K + P_BK - 1) / P_BK;

@@ -29,6 +29,13 @@ xent_kernel(const float* __restrict__ in, const void* __restrict__ labels, int l
     const float* r = in + (long)row * C;
     const int y = label_is_i64 ? (int)reinterpret_cast<const long long*>(labels)[row]
                                : reinterpret_cast<const int*>(labels)[row];
+    if ((unsigned)y >= (unsigned)C) {
+      // label outside [0, C): TensorFlow raises on the CPU and returns NaN on the GPU for it. Here the row poisons
+      // the loss with NaN and contributes no gradient (and no out-of-bounds read).
+      for (int c = lane; c < C; c += 32) dgrad[(long)row * C + c] = 0.f;
+      if (lane == 0) loss += __int_as_float(0x7fc00000);
+      continue;
+    }
     // arg-max (first maximum) and max value
     float mx = -INFINITY; int am = 0x7fffffff;
     for (int c = lane; c < C; c += 32) {

@@ -215,8 +215,11 @@ head_fwd_bwd_kernel(const HeadParams p) {
   // softmax / loss / accuracy / dz: one warp per row, lane = class (N <= 32)
   float loss = 0.f, correct = 0.f;
   for (int r = warp; r < rows; r += HD_THREADS / 32) {
-    const int y = p.label_is_i64 ? (int)reinterpret_cast<const long long*>(p.labels)[r0 + r]
-                                 : reinterpret_cast<const int*>(p.labels)[r0 + r];
+    const int yraw = p.label_is_i64 ? (int)reinterpret_cast<const long long*>(p.labels)[r0 + r]
+                                    : reinterpret_cast<const int*>(p.labels)[r0 + r];
+    // a label outside [0, N) poisons the loss with NaN (TensorFlow's GPU kernel does the same) and gets no gradient
+    const bool yok = (unsigned)yraw < (unsigned)N;
+    const int y = yok ? yraw : 0;
     const float z = lane < N ? zs[r * N + lane] : -INFINITY;
     float mx = z; int am = lane < N ? lane : 0x7fffffff;
 #pragma unroll
@@ -240,7 +243,8 @@ head_fwd_bwd_kernel(const HeadParams p) {
       dz = inside ? (prob - (lane == y ? 1.f : 0.f)) * (p.scale * py / cl) : 0.f;
       if (lane == 0) loss += -logf(cl);
     }
-    if (lane == 0 && am == y) correct += 1.f;
+    if (!yok) { dz = 0.f; if (lane == 0) loss = __int_as_float(0x7fc00000); }
+    if (lane == 0 && yok && am == y) correct += 1.f;
     if (lane < N) {
       if (p.out) p.out[(size_t)(r0 + r) * N + lane] = p.from_probs ? prob : z;
       zs[r * N + lane] = dz;
@@ -543,12 +547,8 @@ TFDE_API int tfde_head_fwd_bwd(const float* h, const float* w, const float* bias
   if (!tfde_head_supported(K, N) || M <= 0) return TFDE_ERR_INVALID;
   const int rpb = head_rows_per_block(M);
   const size_t smem = head_smem_bytes(K, N, rpb);
-  static size_t configured = 48 * 1024;
-  if (smem > configured) {
-    const cudaError_t e = cudaFuncSetAttribute(head_fwd_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    configured = smem;
-  }
+  static size_t configured[TFDE_MAX_DEVICES] = {};
+  { const cudaError_t e = tfde_ensure_dyn_smem(head_fwd_bwd_kernel, smem, configured); if (e != cudaSuccess) return (int)e; }
   HeadParams p{h, w, bias, labels, label_is_i64, out, dh, dw, db, out4, M, K, N, relu_mask, from_probs, rpb, scale,
                partials, counter};
   tfde_launch(head_fwd_bwd_kernel, dim3((M + rpb - 1) / rpb), dim3(HD_THREADS), smem, stream, p);

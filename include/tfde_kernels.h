@@ -205,6 +205,15 @@ int tfde_transpose_bf16(const void* x, void* y, long R, int C, long ldx, long ld
  * tf2_mnist_distributed.py:189 (gRPC RecvTensor in TF). */
 int tfde_ps_push(float* w_owner, const float* g, long n, float lr, tfde_stream_t stream);
 int tfde_ps_pull(float* w_local, const float* w_owner, long n, tfde_stream_t stream);
+/* Whole-model forms used by ParameterServerStrategy when ps and worker tasks share an NVLink domain: `table` is a
+ * device array of {owner ptr, local ptr, n, kind} segments (kind 0: trainable -- push adds -lr * local gradient into
+ * the owner with reduction atomics, kind 1: non-trainable state -- push stores the local value). push also bumps the
+ * owner-side global_step counter (device memory on ps 0) and writes the new value to *step_out.
+ * ref: mnist_keras_distributed.py:241-242 (the worker<->ps variable traffic of ParameterServerStrategy). */
+size_t tfde_ps_seg_bytes(void);
+int tfde_ps_pull_multi(const void* table, int nseg, long max_n, tfde_stream_t stream);
+int tfde_ps_push_multi(const void* table, int nseg, long max_n, float lr, unsigned* step_owner, unsigned* step_out,
+                       tfde_stream_t stream);
 /* tfde_dense_wgrad whose epilogue also stores the tiles into the peers' all-reduce receive slots
  * (`push` is a TfdePush, gemm_fp32.cu): GEMM -> reduce-scatter in one kernel. */
 int tfde_dense_wgrad_push(const float* x, const float* dy, const float* ymask, float* dw, float* db, int M,

@@ -770,29 +770,76 @@ class Sequential:
         cbs.on_train_end()
         return history
 
+    def _eval_replicas(self):
+        """[self] + one replica of this model per additional local device of a LOCAL MirroredStrategy (in-process
+        mirrored evaluation, mnist_keras_distributed.py:243). Replicas are built once and refreshed from this
+        model's weights at every evaluate()."""
+        devs = getattr(self.strategy, "local_devices", None)
+        if not devs or len(devs) < 2 or self.device.type != "cuda" or os.environ.get("TFDE_MIRRORED_EVAL", "1") != "1":
+            return [self]
+        reps = getattr(self, "_replicas", None)
+        if reps is None or [r.device for r in reps] != list(devs[1:]):
+            from ..parallel.strategy import Strategy
+            reps = []
+            cur = torch.cuda.current_device()
+            try:
+                for d in devs[1:]:
+                    with Strategy(device=str(d)).scope():
+                        layers = [L.layer_from_config(type(l).__name__, l.get_config()) for l in self.layers]
+                        rep = Sequential(layers, name=f"{self.name}_replica_{d.index}", seed=self.seed)
+                    rep.build(self.input_shape)
+                    rep.loss, rep.metrics_names, rep.compiled = self.loss, self.metrics_names, False
+                    reps.append(rep)
+            finally:
+                torch.cuda.set_device(cur)
+            self._replicas = reps
+        self.sync()
+        for rep in reps:
+            rep.arena.w.copy_(self.arena.w)
+            rep.state.copy_(self.state)
+        torch.cuda.synchronize(self.device)
+        return [self] + reps
+
     def evaluate(self, x=None, y=None, batch_size=None, steps=None, verbose=0, return_dict=False):
         """Distributed evaluation (the MirroredStrategy eval of mnist_keras_distributed.py:243): each
-        replica scores its slice of every batch; (loss_sum, correct, count) are SUM-reduced (G14)."""
+        replica scores its slice of every batch; (loss_sum, correct, count) are SUM-reduced (G14). Replicas are
+        the processes of the strategy's group and/or -- local MirroredStrategy -- the GPUs of this process."""
         from ..data.dataset import Dataset, DistributedDataset, as_distributed
         if not isinstance(x, (Dataset, DistributedDataset)):
             ds = Dataset.from_tensor_slices((np.asarray(x), np.asarray(y))).batch(batch_size or 32)
             x = ds
         dist_ds = as_distributed(x, self.strategy, for_eval=True)
-        tot = torch.zeros(4, dtype=torch.float64)
+        self.sync()
+        replicas = None
+        acc = None
         n_steps = 0
         for xb, yb, gb in dist_ds:
             if steps is not None and n_steps >= steps:
                 break
-            if xb.shape[0] > 0:
-                xd = self._to_device(xb)
-                yd = self._to_device(yb).reshape(-1).long()
+            n = int(xb.shape[0])
+            if n > 0:
                 if not self.built:
-                    self.build(tuple(xd.shape[1:]))
-                out = self._forward(xd, False)
-                o4, _ = ops.xent(out, yd, 1.0, self.loss.from_probs if self.loss else False,
-                                 out_grad=self._in_buf("dloss_eval", out.shape))
-                tot += o4.detach().to("cpu", torch.float64)
+                    self.build(tuple(xb.shape[1:]))
+                if replicas is None:
+                    replicas = self._eval_replicas()
+                    acc = [torch.zeros(4, dtype=torch.float32, device=r.device) for r in replicas]
+                R = len(replicas)
+                for i, rep in enumerate(replicas):
+                    lo, hi = n * i // R, n * (i + 1) // R
+                    if hi <= lo:
+                        continue
+                    ctx = torch.cuda.device(rep.device) if rep.device.type == "cuda" else contextlib.nullcontext()
+                    with ctx:
+                        xd = rep._to_device(xb[lo:hi])
+                        yd = rep._to_device(yb[lo:hi]).reshape(-1).long()
+                        out = rep._forward(xd, False)
+                        o4, _ = ops.xent(out, yd, 1.0, self.loss.from_probs if self.loss else False,
+                                         out_grad=rep._in_buf("dloss_eval", out.shape))
+                        acc[i] += o4.detach()          # stays on the device: no host sync per batch
             n_steps += 1
+        tot = torch.zeros(4, dtype=torch.float64)
+        for a in acc or []:
+            tot += a.to("cpu", torch.float64)
         red = tot.to(torch.float32).to(self.device)
         self.strategy.all_reduce_sum_(red)
         r = red.cpu().tolist()

@@ -333,6 +333,15 @@ def xent_logits(logits, labels, scale: float):
     ``scale`` = 1/global_batch (tf2_mnist_distributed.py:81-83). Returns
     (loss_sum*scale, correct_count, dlogits) with dlogits = (softmax - onehot) * scale."""
     labels = labels.reshape(-1).long()
+    bad = (labels < 0) | (labels >= logits.shape[-1])
+    if bad.any():
+        # a label outside [0, C) poisons the loss with NaN (what TensorFlow's GPU kernel returns) and contributes
+        # neither gradient nor accuracy; the CUDA kernels do the same
+        safe = labels.masked_fill(bad, 0)
+        loss, correct, dlogits = xent_logits(logits[~bad], safe[~bad], scale)
+        full = torch.zeros_like(logits)
+        full[~bad] = dlogits
+        return loss * float("nan"), correct, full
     lse = torch.logsumexp(logits, dim=-1)
     picked = logits.gather(1, labels[:, None]).squeeze(1)
     loss = (lse - picked).sum() * scale
@@ -346,6 +355,13 @@ def xent_probs(probs, labels, scale: float):
     """'sparse_categorical_crossentropy' on probabilities (mnist_keras_distributed.py:108,114):
     -log(clip(p[y], 1e-7, 1-1e-7)). Returns (loss_sum*scale, correct_count, dprobs)."""
     labels = labels.reshape(-1).long()
+    bad = (labels < 0) | (labels >= probs.shape[-1])
+    if bad.any():
+        safe = labels.masked_fill(bad, 0)
+        loss, correct, dp = xent_probs(probs[~bad], safe[~bad], scale)
+        full = torch.zeros_like(probs)
+        full[~bad] = dp
+        return loss * float("nan"), correct, full
     py = probs.gather(1, labels[:, None]).squeeze(1)
     clipped = py.clamp(EPS_PROB, 1.0 - EPS_PROB)
     loss = (-torch.log(clipped)).sum() * scale

@@ -211,18 +211,50 @@ class MultiWorkerMirroredStrategy(Strategy):
 
 
 class MirroredStrategy(MultiWorkerMirroredStrategy):
-    """Synchronous data parallel across the GPUs of one host.
+    """Synchronous data parallel across the GPUs of one host (mnist_keras_distributed.py:243 uses it as
+    ``eval_distribute``).
 
-    TF drives all local GPUs from one process; here each GPU has its own process (start them with
-    ``python -m tfde_b200.launch --nproc N script.py`` or torchrun). Inside such a process group this
-    class behaves exactly like :class:`MultiWorkerMirroredStrategy`; started stand-alone it is a single
-    replica on ``cuda:0`` (or the CPU).
-    """
+    TF drives all local GPUs from one process; here TRAINING runs one process per GPU: start them with
+    ``python -m tfde_b200.launch --nproc N script.py`` or torchrun, and inside such a group this class behaves
+    exactly like :class:`MultiWorkerMirroredStrategy`. Everywhere else -- started stand-alone, or constructed inside
+    a task of a parameter-server / Estimator cluster (``TF_CONFIG`` with ``ps`` or ``evaluator`` jobs, which is
+    where the reference builds it) -- it is LOCAL: it never joins or waits for the cluster's rendezvous, trains as a
+    single replica, and EVALUATES across the local GPUs from this one process (``local_devices``; per-device model
+    replicas, each batch split between them, (loss_sum, correct, count) summed -- ``Sequential.evaluate``).
+
+    ``devices``: e.g. ``["/gpu:0", "/gpu:1"]`` / ``["cuda:0", "cuda:1"]``; default: every visible GPU
+    (``TFDE_MIRRORED_DEVICES=0,1`` overrides)."""
 
     def __init__(self, devices=None, device: Optional[str] = None):
-        text = os.environ.get("TF_CONFIG") or tfc.tf_config_from_torchrun_env()
+        text = tfc.tf_config_from_torchrun_env()
+        if text is None:
+            env = os.environ.get("TF_CONFIG")
+            if env:
+                r = tfc.parse_tf_config(env)
+                sync_group = (r.distributed and r.rank >= 0 and not r.cluster.num_tasks("ps")
+                              and not r.cluster.num_tasks("evaluator"))
+                if sync_group:
+                    text = env            # the launcher's synthesized cluster of local training tasks
         super().__init__(tfc.parse_tf_config(text), device=device)
         self.devices = devices
+
+    @property
+    def local_devices(self):
+        """Devices one process evaluates on. A member of a multi-process group owns exactly its own GPU."""
+        if self.world_size > 1 or self.device.type != "cuda":
+            return [self.device]
+        spec = self.devices
+        if spec is None and os.environ.get("TFDE_MIRRORED_DEVICES"):
+            spec = [f"cuda:{int(i)}" for i in os.environ["TFDE_MIRRORED_DEVICES"].split(",") if i.strip() != ""]
+        if spec is None:
+            n = torch.cuda.device_count()
+            rest = [torch.device("cuda", i) for i in range(n) if i != self.device.index]
+            return [self.device] + rest
+        out = []
+        for d in spec:
+            name = str(d).lower().replace("/device:", "").replace("/", "").replace("gpu", "cuda")
+            out.append(torch.device(name))
+        return out or [self.device]
 
 
 class OneDeviceStrategy(Strategy):

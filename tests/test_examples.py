@@ -38,3 +38,27 @@ def test_tf2_mnist_distributed_example_both_models(tmp_path):
     _run(["examples/tf2_mnist_distributed.py", "--model-fn"],
          {"TFDE_MODEL_DIR": str(tmp_path / "a"), "TFDE_MAX_STEPS": "6"})
     assert os.path.exists(tmp_path / "a" / "checkpoint")
+
+
+@pytest.mark.timeout(420)
+def test_mnist_keras_distributed_example_ps_cluster(tmp_path):
+    """The reference's own deployment shape (mnist_keras_distributed.py:221-243): CLUSTER_SPEC / JOB_NAME /
+    TASK_INDEX with ps, master and worker tasks, ParameterServerStrategy for training and MirroredStrategy() as
+    eval_distribute constructed in EVERY task. The ps task must serve (not die in MirroredStrategy), the training
+    tasks must not wait in a synchronous rendezvous."""
+    sys.path.insert(0, ROOT)
+    from tfde_b200 import launch
+    wd = str(tmp_path / "wd")
+    env = {"TFDE_DEVICE": "cpu", "OMP_NUM_THREADS": "2", "TFDE_NO_TENSORBOARD": "1", "TFDE_RENDEZVOUS_TIMEOUT": "60"}
+    old_tf = os.environ.pop("TF_CONFIG", None)
+    try:
+        res = launch.launch([os.path.join(ROOT, "examples", "mnist_keras_distributed.py"), "--working-dir", wd,
+                             "--batch-size", "64", "--max-steps", "16"], nproc=2, n_ps=1, chief=False,
+                            env_style="cluster_spec", extra_env=env, timeout=360, capture=True)
+    finally:
+        if old_tf is not None:
+            os.environ["TF_CONFIG"] = old_tf
+    for task, rc, out in res:
+        assert rc == 0, f"{task}: rc={rc}\n{(out or '')[-3000:]}"
+    assert any("Distribution enabled" in (out or "") for _, _, out in res)
+    assert os.path.exists(os.path.join(wd, "checkpoint"))

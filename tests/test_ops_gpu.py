@@ -211,6 +211,23 @@ def test_xent(rows, C, probs, lshape):
     assert torch.allclose(o4b.cpu(), o4)
 
 
+@pytest.mark.parametrize("probs", [False, True])
+def test_xent_out_of_range_label_is_nan_loss_zero_gradient(probs):
+    """No out-of-bounds read for a label outside [0, C): NaN loss, zero gradient for that row, other rows intact."""
+    rows, C = 37, 10
+    z = _rand(rows, C, seed=3) * 2
+    lab = torch.randint(0, C, (rows,), generator=torch.Generator().manual_seed(4))
+    lab[5], lab[20] = C + 2, -1
+    inp = torch.softmax(z, -1) if probs else z
+    fn = ref.xent_probs if probs else ref.xent_logits
+    l_ref, c_ref, d_ref = fn(inp.double(), lab, 0.5)
+    o4, d = ops.xent(inp.to(DEV), lab.to(DEV), 0.5, probs)
+    assert torch.isnan(o4[0].cpu()) and torch.isnan(l_ref)
+    assert o4[1].item() == c_ref.item()
+    assert float(d[5].abs().max()) == 0.0 and float(d[20].abs().max()) == 0.0
+    _close(d, d_ref, what="dloss")
+
+
 @pytest.mark.parametrize("opt", ["sgd", "momentum", "nesterov", "adam"])
 def test_optimizer_apply(opt):
     from tfde_b200.parallel.comm import Arena
