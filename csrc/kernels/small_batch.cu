@@ -337,23 +337,10 @@ int head_rows_per_block(int M) {
 // 64-byte global segments. Deterministic (no split, fixed order).
 constexpr int SB_T = 64;
 
-// Same layout as TfdePush of gemm_fp32.cu (the contract of allreduce_p2p.cu's receive slots): with PUSH the dW
-// tile is also stored into the peers' slots (GEMM -> reduce-scatter in one kernel). EXPERIMENTAL: compiled and
-// wired behind TFDE_SKINNY_BWD_PUSH=1, not yet validated on >= 2 GPUs (ROADMAP.md item 2); off by default.
-struct SbPush {
-  int enabled, world, rank, mode;
-  long slot_floats, arena_off;
-  float* recv[8];
-  const uint32_t* epoch;
-  uint32_t* done_flag;
-};
-static_assert(sizeof(SbPush) == 112, "SbPush must mirror TfdePush");
-
-template <bool PUSH>
 __global__ void __launch_bounds__(256)
 dense_bwd_skinny_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ dy,
                         const float* __restrict__ ymask, float* __restrict__ dx, float* __restrict__ dw,
-                        float* __restrict__ db, int M, int K, const SbPush push) {
+                        float* __restrict__ db, int M, int K) {
   TFDE_PDL_PROLOGUE();
   __shared__ float gs[SB_T][SB_T + 1];      // g[m][n]
   __shared__ float ts[SB_T][SB_T + 1];      // W tile [k][n], then x tile [m][k]
@@ -430,43 +417,6 @@ dense_bwd_skinny_kernel(const float* __restrict__ x, const float* __restrict__ w
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-  if (PUSH) {
-    // contiguous columns n = 4 tx + j per thread: each finished row piece is one 16-byte store, locally and
-    // into the peers' receive slots
-#pragma unroll 8
-    for (int m = 0; m < SB_T; ++m) {
-      float a[4], b[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) a[i] = ts[m][ty + 16 * i];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) b[j] = gs[m][4 * tx + j];
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
-    }
-    const uint32_t e = __ldg(push.epoch) + 1u;
-    const int parity = (int)(e & 1u);
-    if (t == 0 && blockIdx.x == 0) *push.done_flag = e;
-    const size_t slot_base = ((size_t)parity * push.world + push.rank) * push.slot_floats;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int k = k0 + ty + 16 * i;
-      if (k >= K) continue;
-      const float4 v4 = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
-      *reinterpret_cast<float4*>(dw + (size_t)k * SB_T + 4 * tx) = v4;
-      const long gi = push.arena_off + (long)k * SB_T + 4 * tx;       // 16-byte aligned: arena_off % 4 == 0
-      if (push.mode == 0) {
-        for (int r = 0; r < push.world; ++r)
-          if (r != push.rank) __stcg(reinterpret_cast<float4*>(push.recv[r] + slot_base + gi), v4);
-      } else {
-        const int owner = (int)(gi / push.slot_floats);                // a 4-group never straddles two owners
-        if (owner != push.rank)
-          __stcg(reinterpret_cast<float4*>(push.recv[owner] + slot_base + (gi - (long)owner * push.slot_floats)), v4);
-      }
-    }
-    return;
-  }
 #pragma unroll 8
   for (int m = 0; m < SB_T; ++m) {
     float a[4], b[4];
@@ -566,21 +516,8 @@ TFDE_API int tfde_dense_bwd_skinny_supported(int M, int K, int N) {
 TFDE_API int tfde_dense_bwd_skinny(const float* x, const float* w, const float* dy, const float* ymask, float* dx,
                                    float* dw, float* db, int M, int K, int N, cudaStream_t stream) {
   if (!tfde_dense_bwd_skinny_supported(M, K, N) || !x || !w || !dy || !dw) return TFDE_ERR_INVALID;
-  tfde_launch(dense_bwd_skinny_kernel<false>, dim3((K + SB_T - 1) / SB_T), dim3(256), 0, stream, x, w, dy, ymask, dx,
-              dw, db, M, K, SbPush{});
+  tfde_launch(dense_bwd_skinny_kernel, dim3((K + SB_T - 1) / SB_T), dim3(256), 0, stream, x, w, dy, ymask, dx,
+              dw, db, M, K);
   TFDE_RETURN_LAUNCH_STATUS();
 }
 
-// EXPERIMENTAL (TFDE_SKINNY_BWD_PUSH=1): the same kernel whose dW tile is also pushed into the peers' all-reduce
-// receive slots (`push` is a TfdePush). Not yet validated on >= 2 GPUs; the default path at 2-3 GPUs remains
-// tfde_dense_wgrad_push + tfde_dense_dgrad.
-TFDE_API int tfde_dense_bwd_skinny_push(const float* x, const float* w, const float* dy, const float* ymask, float* dx,
-                                        float* dw, float* db, int M, int K, int N, const void* push,
-                                        cudaStream_t stream) {
-  if (!tfde_dense_bwd_skinny_supported(M, K, N) || !x || !w || !dy || !dw || !push) return TFDE_ERR_INVALID;
-  SbPush p = *reinterpret_cast<const SbPush*>(push);
-  if (!p.enabled || p.world < 2 || p.world > 8 || (p.arena_off & 3) || (p.slot_floats & 3)) return TFDE_ERR_INVALID;
-  tfde_launch(dense_bwd_skinny_kernel<true>, dim3((K + SB_T - 1) / SB_T), dim3(256), 0, stream, x, w, dy, ymask, dx, dw,
-              db, M, K, p);
-  TFDE_RETURN_LAUNCH_STATUS();
-}

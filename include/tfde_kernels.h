@@ -161,10 +161,6 @@ int tfde_head_fwd_bwd(const float* h, const float* w, const float* bias, const v
 int tfde_dense_bwd_skinny_supported(int M, int K, int N);
 int tfde_dense_bwd_skinny(const float* x, const float* w, const float* dy, const float* ymask, float* dx, float* dw,
                           float* db, int M, int K, int N, tfde_stream_t stream);
-/* EXPERIMENTAL (TFDE_SKINNY_BWD_PUSH=1, not yet validated on >= 2 GPUs): same kernel, dW tile also pushed into the
- * peers' all-reduce receive slots (`push` is a TfdePush). */
-int tfde_dense_bwd_skinny_push(const float* x, const float* w, const float* dy, const float* ymask, float* dx,
-                               float* dw, float* db, int M, int K, int N, const void* push, tfde_stream_t stream);
 
 /* ---- bf16 tensor-core GEMMs: tcgen05.mma + TMEM + TMA (gemm_tcgen05.cu, gemm_tcgen05_persistent.cu) -- */
 /* C[M,N] = act(A[M,K] . B[N,K]^T + bias); A, B bf16 with K contiguous (K % 8 == 0, 16-byte aligned);

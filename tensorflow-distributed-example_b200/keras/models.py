@@ -118,6 +118,7 @@ class Sequential:
         self.steps_per_execution = 1
         self._fused = None           # ops.fused_step.FusedStepPlan once the whole-step kernel is in use
         self._fused_checked = False
+        self._tracer = None          # obs.profiler.StepTracer while a ProfilerHook samples this step
         for l in layers or []:
             self.add(l)
 
@@ -311,18 +312,33 @@ class Sequential:
             self._graphs[key] = b
         return b
 
+    def _span(self, name: str):
+        return self._tracer.span(name) if self._tracer is not None else contextlib.nullcontext()
+
+    def start_trace(self):
+        """The next training step runs span by span (eagerly, layer kernels bracketed by CUDA events): used by
+        ``ProfilerHook`` on its sampled steps. Returns the tracer; ``stop_trace()`` ends the mode."""
+        from ..obs.profiler import StepTracer
+        self._tracer = StepTracer(self.device)
+        return self._tracer
+
+    def stop_trace(self):
+        self._tracer = None
+
     def _forward(self, x, training: bool):
         self._refresh_w16()
         x = self._prep_input(x)
         for node in self.exec_plan:
-            x = node.run(x, training)
+            with self._span(f"{type(node).__name__}/{node.name}/forward"):
+                x = node.run(x, training)
         return x
 
     def _backward(self, dy):
         for node in reversed(self.exec_plan):
             if dy is None:
                 break
-            dy = node.run_back(dy)
+            with self._span(f"{type(node).__name__}/{node.name}/backward"):
+                dy = node.run_back(dy)
 
     def __call__(self, x, training=False):
         from ..estimator.symbolic import SymbolicOutput, SymbolicTensor
@@ -351,12 +367,18 @@ class Sequential:
         plan = self.fused_plan(x)
         if plan is not None:
             # the whole step -- forward, loss, backward, cross-replica reduction, optimizer -- is ONE kernel
-            plan.launch(x, y, int(x.shape[0]), 1, global_batch)
+            if self._tracer is not None:
+                with self._span("whole step (one cooperative kernel)"):
+                    phases = plan.launch_traced(x, y, int(x.shape[0]), global_batch)
+                self._tracer.add_kernel_phases("tfde_fused_step", phases)
+            else:
+                plan.launch(x, y, int(x.shape[0]), 1, global_batch)
             self.optimizer.iterations += 1
             return
         asynchronous = not st.synchronous
         if asynchronous:
-            st.pull(self)              # parameter-server mode: fetch the current weights (N4)
+            with self._span("parameter-server pull"):
+                st.pull(self)              # parameter-server mode: fetch the current weights (N4)
         a = self.arena
         head = self._fusable_head(x)
         if head is not None:
@@ -364,33 +386,40 @@ class Sequential:
             self._refresh_w16()
             h = self._prep_input(x)
             for node in self.exec_plan[:-1]:
-                h = node.run(h, True)
+                with self._span(f"{type(node).__name__}/{node.name}/forward"):
+                    h = node.run(h, True)
             dh = head.buf("dx", h.shape) if head.need_dx else None
-            ops.head_fwd_bwd(h, head.kernel.value, head.bias.value if head.bias else None, y,
-                             1.0 / float(global_batch), self.loss.from_probs, False, head.need_dx,
-                             out_dh=dh, out_dw=head.kernel.grad, out_db=head.bias.grad if head.bias else None,
-                             out4=a.grad_tail)
+            with self._span(f"Dense/{head.name}/forward+loss+backward (fused head)"):
+                ops.head_fwd_bwd(h, head.kernel.value, head.bias.value if head.bias else None, y,
+                                 1.0 / float(global_batch), self.loss.from_probs, False, head.need_dx,
+                                 out_dh=dh, out_dw=head.kernel.grad, out_db=head.bias.grad if head.bias else None,
+                                 out4=a.grad_tail)
             dy = dh
             for node in reversed(self.exec_plan[:-1]):
                 if dy is None:
                     break
-                dy = node.run_back(dy)
+                with self._span(f"{type(node).__name__}/{node.name}/backward"):
+                    dy = node.run_back(dy)
         else:
             out = self._forward(x, True)
             dgrad = self._in_buf("dloss", out.shape)
-            ops.xent(out, y, 1.0 / float(global_batch), self.loss.from_probs, out_grad=dgrad, out4=a.grad_tail)
+            with self._span("loss/softmax cross-entropy + gradient"):
+                ops.xent(out, y, 1.0 / float(global_batch), self.loss.from_probs, out_grad=dgrad, out4=a.grad_tail)
             self._backward(dgrad)
         self.join_forks()              # filter-gradient GEMMs forked onto the side stream are done
         if asynchronous:
-            st.push(self)              # the owner applies w -= lr*g without waiting for other workers
+            with self._span("parameter-server push"):
+                st.push(self)          # the owner applies w -= lr*g without waiting for other workers
             a.w[a.n:] = a.g[a.n:]
             a.metrics += a.g[a.n:]
             self.optimizer.iterations += 1
         elif self.strategy.num_replicas_in_sync > 1:
-            self.strategy.comm().reduce_and_apply(a, self.optimizer)
+            with self._span("gradient all-reduce + optimizer (fused, peer memory)"):
+                self.strategy.comm().reduce_and_apply(a, self.optimizer)
             self.optimizer.iterations += 1
         else:
-            self.optimizer.apply_local(a)
+            with self._span("optimizer"):
+                self.optimizer.apply_local(a)
 
     def fused_plan(self, x=None):
         """The whole-step kernel's plan when this model/strategy/policy is covered by it (Model A topology, fp32,
@@ -518,7 +547,7 @@ class Sequential:
         if isinstance(y, np.ndarray):
             y = torch.from_numpy(y)
         plan = self.fused_plan(x)
-        if plan is not None and os.environ.get("TFDE_FUSED_DIRECT", "1") == "1":
+        if plan is not None and os.environ.get("TFDE_FUSED_DIRECT", "1") == "1" and self._tracer is None:
             # one kernel per step: no CUDA graph needed. Host batches go through the staging ring (H2D on the copy
             # stream, loss written into mapped pinned memory); device batches are consumed in place.
             yy = y.reshape(-1)
@@ -550,7 +579,8 @@ class Sequential:
         yy = y.reshape(-1)
         with torch.cuda.stream(self._stream):
             ops.native.Workspace.current(self.device)
-            graph_mode = self.use_cuda_graph and st.eager_steps >= self.graph_warmup_steps
+            graph_mode = (self.use_cuda_graph and st.eager_steps >= self.graph_warmup_steps
+                          and self._tracer is None)
             if graph_mode and not x.is_cuda:
                 # Steady state, host inputs: ONE launch per step. The captured graph starts with the H2D
                 # copies out of a pinned staging slot and ends with a D2H copy of the 4-float metrics tail

@@ -264,6 +264,26 @@ class FusedStepPlan:
         out["P1..P3 critical path (max end - min start)"] = (float((t[:, 7].max() - t[:, 0].min()) / 1e3),) * 2
         return out
 
+    def launch_traced(self, x, y, B, global_batch):
+        """One step with the in-kernel phase stamps on: returns [(phase, start_us, dur_us)] for CTA-averaged phases
+        relative to the kernel's first stamp (ProfilerHook timelines)."""
+        L = native.load()
+        prof = torch.zeros((L.tfde_fused_step_blocks(), L.tfde_fused_step_prof_stamps()), dtype=torch.int64,
+                           device=self.device)
+        self.desc.prof = prof.data_ptr()
+        try:
+            self.launch(x, y, B, 1, global_batch)
+            torch.cuda.current_stream(self.device).synchronize()
+        finally:
+            self.desc.prof = None
+        t = prof.cpu().double()
+        t0 = float(t[:, 0].min())
+        out = []
+        for i, name in enumerate(self.PHASES):
+            start = float(t[:, i].mean() - t0) / 1e3
+            out.append((name, start, max(float((t[:, i + 1] - t[:, i]).mean()) / 1e3, 0.0)))
+        return out
+
     def check(self):
         st = self.status.cpu().tolist()
         if st[0] != 0:

@@ -126,6 +126,15 @@ def register_optional(name, args, res=c_i):
 
 
 _launches = 0
+_trace_sink = None
+
+
+def set_trace_sink(sink):
+    """While set, every native entry point that launches records its name into ``sink`` (obs.profiler.StepTracer).
+    Returns the previous sink."""
+    global _trace_sink
+    prev, _trace_sink = _trace_sink, sink
+    return prev
 
 
 def check(code: int, what: str, kernels: int = 1):
@@ -134,6 +143,8 @@ def check(code: int, what: str, kernels: int = 1):
     if code != 0:
         raise RuntimeError(f"{what} failed with CUDA error {code}")
     _launches += kernels
+    if _trace_sink is not None and kernels:
+        _trace_sink.append("tfde_" + what)
 
 
 def launch_count() -> int:
@@ -257,8 +268,6 @@ def dense_fwd(x, w, bias=None, act="none", out=None):
 
 
 _SKINNY_BWD = os.environ.get("TFDE_SKINNY_BWD", "1") == "1"
-_SKINNY_BWD_PUSH = os.environ.get("TFDE_SKINNY_BWD_PUSH", "0") == "1"     # experimental, see ROADMAP.md item 2
-register_optional("tfde_dense_bwd_skinny_push", [c_p] * 7 + [c_i] * 3 + [c_p, c_p])
 register_optional("tfde_dense_bwd_skinny_supported", [c_i, c_i, c_i])
 register_optional("tfde_dense_bwd_skinny", [c_p] * 7 + [c_i] * 3 + [c_p])
 
@@ -295,15 +304,6 @@ def dense_bwd(x, w, y, dy, act="none", need_dx=True, has_bias=True, out_dx=None,
         dx = (out_dx if out_dx is not None else torch.empty((M, K), dtype=torch.float32, device=dev)) if need_dx else None
         check(L.tfde_dense_bwd_skinny(x.data_ptr(), w.data_ptr(), dy.data_ptr(), ptr(mask), ptr(dx), dw.data_ptr(),
                                       ptr(db), M, K, N, stream_ptr()), "dense_bwd_skinny")
-        return dx, dw, db
-
-    if (pd is not None and _SKINNY_BWD_PUSH and hasattr(L, "tfde_dense_bwd_skinny_push")
-            and L.tfde_dense_bwd_skinny_supported(M, K, N)):
-        # EXPERIMENTAL (off by default, not yet validated on >= 2 GPUs): one-launch backward that also pushes dW
-        dx = (out_dx if out_dx is not None else torch.empty((M, K), dtype=torch.float32, device=dev)) if need_dx else None
-        check(L.tfde_dense_bwd_skinny_push(x.data_ptr(), w.data_ptr(), dy.data_ptr(), ptr(mask), ptr(dx), dw.data_ptr(),
-                                           ptr(db), M, K, N, ctypes.byref(pd), stream_ptr()), "dense_bwd_skinny_push")
-        _push.stats["pushed_launches"] += 1
         return dx, dw, db
 
     def launch_wgrad(ws_):

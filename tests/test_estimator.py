@@ -124,6 +124,18 @@ def test_profiler_hook_writes_chrome_trace(tmp_path):
     assert names == ["timeline-0.json", "timeline-2.json", "timeline-4.json"]
     trace = json.load(open(tmp_path / "prof" / names[0]))
     assert trace["traceEvents"][0]["ph"] == "X"
+    # per-layer timeline (Model B): at least one span per executed layer in each direction, plus loss and optimizer
+    spans = [e["name"] for e in trace["traceEvents"] if e["ph"] == "X"]
+    model = est._models[next(iter(est._models))]
+    for node in model.exec_plan:
+        if getattr(node, "fused_away", False):
+            continue
+        assert any(f"/{node.name}/forward" in s for s in spans), (node.name, spans)
+    for kind in ("Conv2D", "BatchNormalization", "Dense"):
+        assert any(s.startswith("host: " + kind) and "/backward" in s for s in spans), kind
+    assert any("cross-entropy" in s or "fused head" in s for s in spans) and any("optimizer" in s for s in spans)
+    # the step after a sampled one is back on the normal path
+    assert model._tracer is None
 
 
 def test_custom_model_fn_with_manual_global_batch_scaling(tmp_path):

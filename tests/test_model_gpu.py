@@ -108,3 +108,37 @@ def test_tiny_resnet_matches_cpu_reference():
     mc, lc = _train(builder, "cpu", 4, x, y, 16)
     mg, lg = _train(builder, "cuda", 4, x, y, 16)
     np.testing.assert_allclose(lg, lc, rtol=1e-2, atol=1e-3)
+
+
+def test_profiler_hook_per_kernel_timeline_on_gpu(tmp_path):
+    """ProfilerHook (mnist_keras_distributed.py:235-237): the sampled step's Chrome trace has a device span per
+    layer and direction that names the native entry points it launched; the whole-step kernel of Model A is
+    resolved into its in-kernel phases."""
+    import json
+    from tfde_b200 import estimator as E
+    x, y = _data(128, flat=True)
+    hook = E.ProfilerHook(save_steps=3, output_dir=str(tmp_path / "b"))
+    mb = tf.models.build_and_compile_model_b(learning_rate=0.05, seed=1)
+    hook.begin()
+    for step in range(4):
+        hook.before_run(step, mb)
+        mb.train_on_batch(x, y.reshape(-1, 1))
+        hook.after_run(step, mb)
+    ev = json.load(open(tmp_path / "b" / "timeline-3.json"))["traceEvents"]
+    dev = [e for e in ev if e.get("pid") == 1 and e["ph"] == "X" and e.get("tid") == 0]
+    names = [e["name"] for e in dev]
+    assert sum("/forward" in n for n in names) >= 8 and sum("/backward" in n for n in names) >= 8, names
+    kernels = {k for e in dev for k in e.get("args", {}).get("kernels", [])}
+    assert any(k.startswith("tfde_conv2d") for k in kernels) and any(k.startswith("tfde_bn") for k in kernels), kernels
+    assert all(e["dur"] >= 0 for e in dev)
+    # Model A: one kernel per step, its phases come from the in-kernel stamps
+    hook = E.ProfilerHook(save_steps=2, output_dir=str(tmp_path / "a"))
+    ma = tf.models.build_and_compile_cnn_model(learning_rate=0.05, seed=1)
+    xa, ya = _data(64)
+    for step in range(3):
+        hook.before_run(step, ma)
+        ma.train_on_batch(xa, ya)
+        hook.after_run(step, ma)
+    ev = json.load(open(tmp_path / "a" / "timeline-2.json"))["traceEvents"]
+    phases = [e["name"] for e in ev if e.get("tid") == 1]
+    assert any("P1 conv" in n for n in phases) and any("two-level ticket" in n for n in phases), phases
