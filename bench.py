@@ -81,7 +81,7 @@ class ClockSampler:
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
                0x4: "sw_power_cap", 0x80: "hw_power_brake_slowdown"}
 
-    def __init__(self, gpu_index=0, period_s=0.004):
+    def __init__(self, gpu_index=0, period_s=0.0005):
         self.gpu_index, self.period_s = gpu_index, period_s
         self.proc = None
         self.lines = []

@@ -467,9 +467,18 @@ class Sequential:
         gb = global_batch if global_batch is not None else B * self.strategy.num_replicas_in_sync
         plan = self.fused_plan() if self.device.type == "cuda" else None
         if plan is None or not plan.supports(x, B):
+            # not covered by the whole-step kernel: the steps run one after the other (each its own launch sequence /
+            # graph replay); every step's loss is collected one step late so the reads overlap the next step
+            losses = []
             for k in range(K):
                 self.train_on_batch(x[k * B:(k + 1) * B], yy[k * B:(k + 1) * B], global_batch=gb)
+                if k > 0:
+                    losses.append(self.last_step_loss(lag=1))
+            losses.append(self.last_step_loss())
+            self._exec_losses_prev, self._exec_losses = getattr(self, "_exec_losses", None), losses
+            self._host_tail_mode = "steps"
             return
+        self._host_tail_mode = "fused"
         if self._stream is None:
             self._stream = torch.cuda.Stream(device=self.device)
         if x.is_cuda:
@@ -486,6 +495,8 @@ class Sequential:
         """Per-step losses (global mean) of the most recent ``train_on_batches`` / ``train_on_batch`` execution from
         host batches (``lag=1``: of the one before it, so a loop can read every loss while the next execution is
         already running). Waits for that execution only."""
+        if getattr(self, "_host_tail_mode", None) == "steps":
+            return list((self._exec_losses if lag == 0 else self._exec_losses_prev) or [])
         plan = self._fused
         if plan is not None and getattr(self, "_host_tail", None) == "fused":
             slot = plan.last_slot if lag == 0 else plan.prev_slot

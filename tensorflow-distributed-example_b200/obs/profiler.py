@@ -127,6 +127,7 @@ class ProfilerHook:
                 events.append({"name": "memory", "ph": "C", "pid": 1, "ts": 0,
                                "args": {"allocated_MiB": torch.cuda.memory_allocated() / 2 ** 20,
                                         "reserved_MiB": torch.cuda.memory_reserved() / 2 ** 20}})
+        os.makedirs(self.output_dir, exist_ok=True)
         path = os.path.join(self.output_dir, f"timeline-{step}.json")
         with open(path, "w") as f:
             json.dump({"traceEvents": events, "displayTimeUnit": "ms"}, f)

@@ -135,6 +135,7 @@ def test_profiler_hook_per_kernel_timeline_on_gpu(tmp_path):
     hook = E.ProfilerHook(save_steps=2, output_dir=str(tmp_path / "a"))
     ma = tf.models.build_and_compile_cnn_model(learning_rate=0.05, seed=1)
     xa, ya = _data(64)
+    hook.begin()
     for step in range(3):
         hook.before_run(step, ma)
         ma.train_on_batch(xa, ya)

@@ -10,10 +10,10 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "tensorflow-distributed-example_b200", "_lib", "libtfde_kernels.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-KEEP = ("gemm_bf16_tcgen05_kernel", "allreduce_fused_kernel", "dense_skinny_fwd_kernel", "head_fwd_bwd_kernel",
+KEEP = ("fused_step_kernel", "dense_bwd_skinny_kernel", "ps_push_multi_kernel", "gemm_bf16_tcgen05_kernel", "allreduce_fused_kernel", "dense_skinny_fwd_kernel", "head_fwd_bwd_kernel",
         "conv3x3c1_relu_pool", "allreduce_nvls_kernel", "gemm_bf16_tcgen05_persistent_kernel", "colstats_bf16_kernel",
         "bn_bwd_apply_bf16_kernel", "gemm_fp32_kernel")
-N_LISTED = 9     # kernels of KEEP[:N_LISTED] get a full listing; the rest only a row in the summary
+N_LISTED = 12     # kernels of KEEP[:N_LISTED] get a full listing; the rest only a row in the summary
 MNEMONICS = ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMAPF", "SYNCS", "LDGSTS", "UCGABAR", "LDGMC", "HMMA", "FFMA", "LDG",
              "STG", "STS", "LDS", "ATOMG", "REDG", "MEMBAR", "CCTL")
 
