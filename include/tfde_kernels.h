@@ -44,6 +44,18 @@ int tfde_conv2d_dgrad(const float* dy, const float* ymask, const float* w, float
                       int C, int KH, int KW, int Ho, int Wo, int sh, int sw, int pt, int pl, int Cout,
                       float* ws, size_t ws_bytes, unsigned* counters, tfde_stream_t stream);
 int tfde_gemm_max_counters(void);
+/* Direct convolution for small channel counts (Cin, Cout <= 32, image + filter fit in shared memory): one CTA per
+ * image, no GEMM tiles wasted on padding, stride-2 data gradient visits only the taps of its stride phase.
+ * ref: the Conv2D(6,3) / Conv2D(12,6,s2) / Conv2D(24,6,s2) layers of mnist_keras_distributed.py:83-98. */
+int tfde_smallconv_supported(int B, int H, int W, int Cin, int KH, int KW, int Ho, int Wo, int sh, int sw, int pt,
+                             int pl, int Cout, int bwd, int need_dx);
+size_t tfde_smallconv_bwd_ws_floats(int B, int Cin, int KH, int KW, int Cout);
+int tfde_smallconv_fwd(const float* x, const float* w, const float* bias, float* y, int B, int H, int W, int Cin,
+                       int KH, int KW, int Ho, int Wo, int sh, int sw, int pt, int pl, int Cout, int relu,
+                       tfde_stream_t stream);
+int tfde_smallconv_bwd(const float* x, const float* dy, const float* w, float* dx, float* dw, float* ws, int B, int H,
+                       int W, int Cin, int KH, int KW, int Ho, int Wo, int sh, int sw, int pt, int pl, int Cout,
+                       tfde_stream_t stream);
 /* tfde_dense_fwd for callers that cannot allocate device memory (a plug-in inside a process whose GPU
  * memory pool belongs to another framework, or a loop where cudaMalloc is forbidden): the split-K scratch
  * is a static __device__ array inside the library (about 2 MiB, held by every GPU that loads the library

@@ -347,12 +347,25 @@ def _conv_out(x_shape, w_shape, stride, pads):
     return ho, wo
 
 
+register_optional("tfde_smallconv_supported", [c_i] * 15)
+register_optional("tfde_smallconv_bwd_ws_floats", [c_i] * 5, c_z)
+register_optional("tfde_smallconv_fwd", [c_p, c_p, c_p, c_p] + [c_i] * 14 + [c_p])
+register_optional("tfde_smallconv_bwd", [c_p] * 6 + [c_i] * 13 + [c_p])
+_SMALLCONV = os.environ.get("TFDE_SMALLCONV", "1") == "1"
+
+
 def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), relu=False, out=None):
     L = load()
     _f32c(x, "x"); _f32c(w, "w")
     ho, wo = _conv_out(x.shape, w.shape, stride, pads)
     y = out if out is not None else torch.empty((x.shape[0], ho, wo, w.shape[3]), dtype=torch.float32,
                                                 device=x.device)
+    g = _geom(x.shape, w.shape, stride, pads, ho, wo)
+    if _SMALLCONV and L.tfde_smallconv_supported(*g, 0, 0):
+        # small channel counts (Model B's 6/12/24-channel layers): direct convolution, one CTA per image
+        check(L.tfde_smallconv_fwd(x.data_ptr(), w.data_ptr(), ptr(bias), y.data_ptr(), *g, 1 if relu else 0,
+                                   stream_ptr()), "smallconv_fwd")
+        return y
     wsp = Workspace.current(x.device)
     check(L.tfde_conv2d_fwd(x.data_ptr(), w.data_ptr(), ptr(bias), y.data_ptr(),
                             *_geom(x.shape, w.shape, stride, pads, ho, wo), 1 if relu else 0,
@@ -370,6 +383,14 @@ def conv2d_bwd(x, w, y, dy, stride=(1, 1), pads=(0, 0, 0, 0), relu=False, need_d
     wsp = Workspace.current(dev)
     mask = y if relu else None
     dw = out_dw if out_dw is not None else torch.empty(tuple(w.shape), dtype=torch.float32, device=dev)
+    if (_SMALLCONV and not relu and not has_bias and L.tfde_smallconv_supported(*g, 1, 1 if need_dx else 0)
+            and L.tfde_smallconv_bwd_ws_floats(g[0], g[3], g[4], g[5], g[12]) * 4 <= wsp.ws_bytes):
+        dx = None
+        if need_dx:
+            dx = out_dx if out_dx is not None else torch.empty(tuple(x.shape), dtype=torch.float32, device=dev)
+        check(L.tfde_smallconv_bwd(x.data_ptr(), dy.data_ptr(), w.data_ptr(), ptr(dx), dw.data_ptr(), wsp.ws.data_ptr(),
+                                   *g, stream_ptr()), "smallconv_bwd", kernels=3 if need_dx else 2)
+        return dx, dw, None
     db = None
     if has_bias:
         db = out_db if out_db is not None else torch.empty((w.shape[3],), dtype=torch.float32, device=dev)

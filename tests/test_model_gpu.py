@@ -129,7 +129,7 @@ def test_profiler_hook_per_kernel_timeline_on_gpu(tmp_path):
     names = [e["name"] for e in dev]
     assert sum("/forward" in n for n in names) >= 8 and sum("/backward" in n for n in names) >= 8, names
     kernels = {k for e in dev for k in e.get("args", {}).get("kernels", [])}
-    assert any(k.startswith("tfde_conv2d") for k in kernels) and any(k.startswith("tfde_bn") for k in kernels), kernels
+    assert any(k.startswith(("tfde_conv2d", "tfde_smallconv")) for k in kernels) and any(k.startswith("tfde_bn") for k in kernels), kernels
     assert all(e["dur"] >= 0 for e in dev)
     # Model A: one kernel per step, its phases come from the in-kernel stamps
     hook = E.ProfilerHook(save_steps=2, output_dir=str(tmp_path / "a"))

@@ -85,6 +85,42 @@ def test_conv2d_fwd_bwd(B, H, W, C, k, s, pad, Co, bias, relu):
         _close(db, db_ref, what="conv db", rtol=5e-4)
 
 
+SMALLCONVS = [  # B,H,W,C, k, stride, padding, Cout, need_dx   (no bias, no activation: Model B's convolutions)
+    (128, 28, 28, 1, 3, 1, "same", 6, False),
+    (128, 28, 28, 6, 6, 2, "same", 12, True),
+    (128, 14, 14, 12, 6, 2, "same", 24, True),
+    (2, 11, 9, 4, 5, 2, "same", 8, True),
+    (3, 13, 13, 2, 3, 1, "valid", 4, True),
+    (1, 10, 12, 6, 4, 3, "same", 10, True),
+    (5, 7, 7, 8, 3, 1, "same", 2, True),
+]
+
+
+@pytest.mark.parametrize("B,H,W,C,k,s,pad,Co,need_dx", SMALLCONVS)
+def test_small_channel_direct_conv(B, H, W, C, k, s, pad, Co, need_dx):
+    """csrc/kernels/small_conv.cu against the fp64 PyTorch restatement, and proof that it is the path that ran."""
+    from tfde_b200.ops import native
+    x, w = _rand(B, H, W, C, seed=11), _rand(k, k, C, Co, seed=12) * 0.2
+    ho, wo, pads = ops.conv_geometry(H, W, k, k, (s, s), pad)
+    dy = _rand(B, ho, wo, Co, seed=13)
+    y_ref = ref.conv2d_fwd(x.double(), w.double(), None, (s, s), pads, False)
+    dx_ref, dw_ref, _ = ref.conv2d_bwd(x.double(), w.double(), y_ref, dy.double(), (s, s), pads, False, need_dx, False)
+    sink = []
+    prev = native.set_trace_sink(sink)
+    try:
+        y = ops.conv2d_fwd(x.to(DEV), w.to(DEV), None, (s, s), pads, False)
+        dx, dw, _ = ops.conv2d_bwd(x.to(DEV), w.to(DEV), y, dy.to(DEV), (s, s), pads, False, need_dx, False)
+    finally:
+        native.set_trace_sink(prev)
+    assert sink == ["tfde_smallconv_fwd", "tfde_smallconv_bwd"], sink
+    _close(y, y_ref, what="conv fwd")
+    _close(dw, dw_ref, what="conv dw", rtol=5e-4)
+    if need_dx:
+        _close(dx, dx_ref, what="conv dx", rtol=5e-4)
+    else:
+        assert dx is None
+
+
 @pytest.mark.parametrize("B,u8", [(64, False), (3, False), (1, True), (65, True)])
 def test_fused_conv_relu_pool(B, u8):
     g = torch.Generator().manual_seed(5)
