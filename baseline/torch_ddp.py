@@ -26,6 +26,23 @@ def build_model_a(torch):
                          nn.Linear(5408, 64), nn.ReLU(), nn.Linear(64, 10))
 
 
+def build_model_b(torch):
+    """Model B of mnist_keras_distributed.py:79-109 in torch (NCHW, cuDNN): 3 x (Conv-BN-ReLU), Dense200-BN-ReLU,
+    Dropout, Dense10. BatchNorm without scale (affine weight frozen at 1), eps 1e-3, momentum 0.01 (= Keras 0.99)."""
+    nn = torch.nn
+
+    def bn(c, two_d=True):
+        m = (nn.BatchNorm2d if two_d else nn.BatchNorm1d)(c, eps=1e-3, momentum=0.01)
+        m.weight.requires_grad_(False)
+        return m
+    return nn.Sequential(nn.Unflatten(1, (1, 28, 28)),
+                         nn.Conv2d(1, 6, 3, padding=1, bias=False), bn(6), nn.ReLU(),
+                         nn.Conv2d(6, 12, 6, stride=2, padding=2, bias=False), bn(12), nn.ReLU(),
+                         nn.Conv2d(12, 24, 6, stride=2, padding=2, bias=False), bn(24), nn.ReLU(),
+                         nn.Flatten(), nn.Linear(1176, 200, bias=False), bn(200, False), nn.ReLU(), nn.Dropout(0.5),
+                         nn.Linear(200, 10))
+
+
 def run(args, METRIC, ClockSampler, max_over_ranks, barrier, dist_env, make_batches):
     import torch
     import torch.distributed as dist
@@ -144,10 +161,12 @@ def run_graphed(args, METRIC, ClockSampler, max_over_ranks, barrier, dist_env, m
         dist.init_process_group("cpu:gloo,cuda:nccl", device_id=dev)
     torch.backends.cudnn.benchmark = True
     torch.manual_seed(1234)
-    model = build_model_a(torch).to(dev).to(memory_format=torch.channels_last)
-    params = [p for p in model.parameters()]
+    is_b = getattr(args, "model", "a") == "b"
+    model = (build_model_b(torch) if is_b else build_model_a(torch)).to(dev).to(memory_format=torch.channels_last)
+    model.train()
+    params = [p for p in model.parameters() if p.requires_grad]
     if world > 1:
-        for p in params:
+        for p in model.parameters():
             dist.broadcast(p.data, src=0)
     # one flat gradient bucket: a single NCCL all-reduce per step, gradients are views into it
     flat = torch.zeros(sum(p.numel() for p in params), device=dev)
@@ -161,14 +180,18 @@ def run_graphed(args, METRIC, ClockSampler, max_over_ranks, barrier, dist_env, m
     gb = B * world
     K, W = args.steps, max(args.warmup, 3)
     xs, ys = make_batches(8, B, seed=100 + rank)
-    xs = [x.permute(0, 3, 1, 2).contiguous().pin_memory() for x in xs]
-    in_x = torch.empty((B, 1, 28, 28), dtype=torch.uint8, device=dev)
+    if is_b:       # the reference feeds Model B float rows of 784 (mnist_keras_distributed.py:211)
+        xs = [x.reshape(B, 784).float().div_(255.0).pin_memory() for x in xs]
+        in_x = torch.empty((B, 784), dtype=torch.float32, device=dev)
+    else:
+        xs = [x.permute(0, 3, 1, 2).contiguous().pin_memory() for x in xs]
+        in_x = torch.empty((B, 1, 28, 28), dtype=torch.uint8, device=dev)
     in_y = torch.empty((B,), dtype=torch.int64, device=dev)
     loss_dev = torch.zeros((), device=dev)
     loss_host = [torch.zeros(()).pin_memory() for _ in range(2)]
 
     def step():
-        x = in_x.float().div_(255.0).contiguous(memory_format=torch.channels_last)
+        x = in_x if is_b else in_x.float().div_(255.0).contiguous(memory_format=torch.channels_last)
         flat.zero_()
         loss = lossf(model(x), in_y) / gb          # SUM over ranks of per-rank sums / global batch
         loss.backward()
@@ -201,10 +224,13 @@ def run_graphed(args, METRIC, ClockSampler, max_over_ranks, barrier, dist_env, m
     sampler.start()
     time.sleep(0.05)
     REPS = 5
-    per = in_x.numel() + in_y.numel() * 8
+    per = in_x.numel() * in_x.element_size() + in_y.numel() * 8
     P = max(K * REPS, -(-(136 << 20) // per))
     gen = torch.Generator(device=dev).manual_seed(4321 + rank)
-    pool_x = torch.randint(0, 256, (P,) + tuple(in_x.shape), generator=gen, dtype=torch.uint8, device=dev)
+    if is_b:
+        pool_x = torch.rand((P,) + tuple(in_x.shape), generator=gen, dtype=torch.float32, device=dev)
+    else:
+        pool_x = torch.randint(0, 256, (P,) + tuple(in_x.shape), generator=gen, dtype=torch.uint8, device=dev)
     pool_y = torch.randint(0, 10, (P,) + tuple(in_y.shape), generator=gen, dtype=torch.int64, device=dev)
     torch.empty(256 << 20, dtype=torch.uint8, device=dev).fill_(1)
     dev_ms = []
@@ -244,7 +270,8 @@ def run_graphed(args, METRIC, ClockSampler, max_over_ranks, barrier, dist_env, m
     out = {"metric": METRIC, "value": gb * K / (dev_med / 1e3), "unit": "images/sec", "n_gpus": world, "steps": K,
            "warmup": W, "ms_per_step": dev_med / K, "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": "torch_cudagraph_nccl_standin",
-           "config": {"model": "keras_mnist_cnn_conv32_pool_dense64_dense10", "global_batch": gb,
+           "config": {"model": "model_b_bn_cnn" if is_b else "keras_mnist_cnn_conv32_pool_dense64_dense10",
+                      "global_batch": gb,
                       "per_gpu_batch": B, "parallelism": f"dp{world}", "optimizer": "sgd", "cuda_graph": True,
                       "l2": "inputs larger than L2 (distinct device-resident batch per step)",
                       "allreduce": "one NCCL all-reduce of a flat gradient bucket inside the graph" if world > 1 else "n/a",

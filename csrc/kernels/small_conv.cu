@@ -207,22 +207,35 @@ smallconv_wgrad_kernel(const SCParams p, int pch) {
   }
 }
 
+// dw[i] = sum_b part[b][i] in a fixed order: block = 32 elements x 8 batch groups (each thread adds B/8 partials with
+// 8 loads in flight), the groups are then combined in order through shared memory.
 __global__ void __launch_bounds__(256)
 smallconv_wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ dw, int nW, int B) {
   TFDE_PDL_PROLOGUE();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nW) return;
+  __shared__ float s_p[8][32];
+  const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
+  const int i = blockIdx.x * 32 + lane;
   float a = 0.f;
-  int b = 0;
-  for (; b + 8 <= B; b += 8) {
-    float v[8];
+  if (i < nW) {
+    const int per = (B + 7) / 8, b0 = grp * per, b1 = min(B, b0 + per);
+    int b = b0;
+    for (; b + 8 <= b1; b += 8) {
+      float v[8];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) v[u] = __ldcg(part + (size_t)(b + u) * nW + i);
+      for (int u = 0; u < 8; ++u) v[u] = __ldcg(part + (size_t)(b + u) * nW + i);
 #pragma unroll
-    for (int u = 0; u < 8; ++u) a += v[u];
+      for (int u = 0; u < 8; ++u) a += v[u];
+    }
+    for (; b < b1; ++b) a += __ldcg(part + (size_t)b * nW + i);
   }
-  for (; b < B; ++b) a += __ldcg(part + (size_t)b * nW + i);
-  dw[i] = a;
+  s_p[grp][lane] = a;
+  __syncthreads();
+  if (grp == 0 && i < nW) {
+    float t = 0.f;
+#pragma unroll
+    for (int g8 = 0; g8 < 8; ++g8) t += s_p[g8][lane];
+    dw[i] = t;
+  }
 }
 
 }  // namespace
@@ -337,7 +350,7 @@ TFDE_API int tfde_smallconv_bwd(const float* x, const float* dy, const float* w,
       default: e = tfde_ensure_dyn_smem(smallconv_wgrad_kernel<2>, smem, d2); if (!e) tfde_launch(smallconv_wgrad_kernel<2>, dim3(B), dim3(SC_THREADS), smem, stream, p, pch); break;
     }
     if (e != cudaSuccess) return (int)e;
-    tfde_launch(smallconv_wgrad_reduce_kernel, dim3((nW + 255) / 256), dim3(256), 0, stream, (const float*)ws, dw, nW, B);
+    tfde_launch(smallconv_wgrad_reduce_kernel, dim3((nW + 31) / 32), dim3(256), 0, stream, (const float*)ws, dw, nW, B);
   }
   if (dx != nullptr) {
     const size_t smem = sc_smem_dgrad(p);

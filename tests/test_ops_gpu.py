@@ -162,7 +162,9 @@ def test_maxpool(B, H, W, C, pool, stride, pad):
 
 @pytest.mark.parametrize("shape,gamma,relu", [((128, 28, 28, 6), False, True), ((16, 7, 7, 24), False, True),
                                               ((128, 200), False, True), ((33, 5, 5, 70), True, False),
-                                              ((2, 3), True, False)])
+                                              ((2, 3), True, False), ((128, 14, 14, 12), False, True),
+                                              ((37, 9, 11, 7), True, True), ((64, 13, 13, 32), True, False),
+                                              ((128, 7, 7, 24), False, True)])
 def test_batchnorm(shape, gamma, relu):
     c = shape[-1]
     x = _rand(*shape, seed=1) * 2.0 + 0.5
