@@ -42,6 +42,9 @@
 //
 // Numerics: exact fp32 FFMA everywhere (the reference trains in fp32), fixed summation orders.
 #include "common.cuh"
+#include "umma_tf32.cuh"
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 namespace {
@@ -87,9 +90,56 @@ constexpr int SM_HG = SM_ROW + FS_U;                    // hcol [64][4] + dzs [6
 constexpr int SM_TOTAL = SM_HG + FS_B * 4 + FS_B * DZ_LD;
 constexpr int FS_SMALL_F4 = (288 + 32 + 64 + 64 * FS_NC + FS_NC + 4 + 3) / 4;    // float4 groups of the largest small block
 static_assert(SM_DH + FS_MAX_RANKS * FS_SMALL_F4 * 4 <= SM_TOTAL, "tail exchange staging must fit in dh..end");
+constexpr int FS_STAGE_FLOATS = FS_MAX_RANKS * FS_SMALL_F4 * 4;
 static_assert(SM_ACT % 4 == 0 && SM_WS % 4 == 0 && SM_DH % 4 == 0 && SM_RED % 4 == 0 && SM_HG % 4 == 0, "align");
 
+// Shared memory layout of the TENSOR-CORE variant (TC): the three per-CTA GEMMs run as kind::tf32 tcgen05.mma with the
+// accumulators in TMEM. Operands are the no-swizzle K-major core-block tiles of umma_tf32.cuh; a tile that is needed in
+// both orientations is written twice (activations, weight slice, gradient tile). The M = 128 instruction shape reads
+// 64 rows past each A tile: the tiles are ordered so that those reads stay inside the allocation.
+constexpr int T_PATCH = 0;
+constexpr int T_ACTK = T_PATCH + FS_B * PATCH_LD;        // act  [b 64][c 32]  RB 256   A of the forward GEMM
+constexpr int T_WTK = T_ACTK + 2048;                     // W^T  [n 64][c 32]  RB 256   B of the forward GEMM
+constexpr int T_ACTB = T_WTK + 2048;                     // act^T[c 32][b 64]  RB 512   B of the filter gradient
+constexpr int T_WSB = T_ACTB + 2048;                     // W    [c 32][n 64]  RB 512   B of the data gradient
+constexpr int T_DHB = T_WSB + 2048;                      // dh   [b 64][n 64]  RB 512   A of the data gradient
+constexpr int T_DHT = T_DHB + 4096;                      // dh^T [n 64][b 64]  RB 512   A of the filter gradient
+constexpr int T_ARG = T_DHT + 4096;
+constexpr int T_DX = T_ARG + FS_B * 4;
+constexpr int T_CW = T_DX + FS_B * DX_LD;
+constexpr int T_RED = T_CW + 10 * FS_C;
+constexpr int T_WH = T_RED + 8 * 10 * FS_C;
+constexpr int T_ROW = T_WH + FS_U * WH_LD + FS_NC;
+constexpr int T_HG = T_ROW + FS_U;
+constexpr int T_GB = T_RED;                              // dW staging [32][68] (TMEM rows are units, threads want 2x4 tiles); aliases `red`
+constexpr int T_TOTAL = T_HG + FS_B * 4 + FS_B * DZ_LD;
+static_assert(FS_C * 68 <= 8 * 10 * FS_C, "dW staging must fit in red");
+static_assert(T_ACTK % 4 == 0 && T_DHB % 4 == 0 && T_RED % 4 == 0 && T_HG % 4 == 0 && T_GB % 4 == 0, "align");
+static_assert(T_DHT + 2 * 4096 <= T_TOTAL, "M=128 over-read of the dh^T tile must stay inside the allocation");
+static_assert(T_DHB + 8 * ((288 + 32 + 64 + 64 * FS_NC + FS_NC + 4 + 3) / 4) * 4 <= T_TOTAL, "tail exchange staging (TC)");
+constexpr int FS_TMEM_COLS = 128;                        // D1 [0,64) | dW^T [64,96) | dx [96,128)
+
 struct Hyper { float lr, mu, b1, b2, eps, gs, lr_t; };
+
+// The CTA's copy of its dense-kernel slice in shared memory: plain [c][68] (FFMA variant) or the two blocked tiles.
+template <bool TC>
+struct WTile {
+  float* base;      // FFMA: ws ; TC: sm (tile offsets are added here)
+  __device__ __forceinline__ float4 load(int c, int n) const {
+    if (TC) return *reinterpret_cast<const float4*>(base + T_WSB + umma::blk(c, n, 512));
+    return *reinterpret_cast<const float4*>(base + c * WS_LD + n);
+  }
+  __device__ __forceinline__ void store(int c, int n, const float4 v) const {
+    if (TC) {
+      *reinterpret_cast<float4*>(base + T_WSB + umma::blk(c, n, 512)) = v;
+      float* wt = base + T_WTK;
+      wt[umma::blk(n, c, 256)] = v.x; wt[umma::blk(n + 1, c, 256)] = v.y;
+      wt[umma::blk(n + 2, c, 256)] = v.z; wt[umma::blk(n + 3, c, 256)] = v.w;
+    } else {
+      *reinterpret_cast<float4*>(base + c * WS_LD + n) = v;
+    }
+  }
+};
 
 struct FsParams {
   const void* x; const long long* y;
@@ -238,8 +288,9 @@ __device__ __forceinline__ long small_to_arena(const FsParams& p, int i) {
 // the owner sums the W contributions in rank order and stores the reduced slice into every peer's `gsum`; a
 // non-owner picks the reduced slice up from its own `gsum`. Every rank then updates its copy (global memory and the
 // shared-memory copy `ws` that the next step's GEMMs read).
+template <bool TC>
 __device__ __forceinline__ void finish_slice(const FsParams& p, uint32_t e, int pix, int owner, const float (&gacc)[2][4],
-                                             float* ws, float* gslice, float* wslice, long aslice, const Hyper& h) {
+                                             const WTile<TC> ws, float* gslice, float* wslice, long aslice, const Hyper& h) {
   const int t = threadIdx.x, tc = t >> 4, tn = t & 15;
   const int W = p.world, R = p.rank;
   float4 sum[2];
@@ -276,31 +327,42 @@ __device__ __forceinline__ void finish_slice(const FsParams& p, uint32_t e, int 
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     const int c = tc * 2 + i, off = c * FS_U + tn * 4;
-    float4* wsm = reinterpret_cast<float4*>(ws + c * WS_LD + tn * 4);
-    const float4 nw = update_four(p.opt, *wsm, sum[i], p.s1, p.s2, aslice + off, h);
-    *wsm = nw;
+    const float4 nw = update_four(p.opt, ws.load(c, tn * 4), sum[i], p.s1, p.s2, aslice + off, h);
+    ws.store(c, tn * 4, nw);
     *reinterpret_cast<float4*>(gslice + off) = sum[i];
     *reinterpret_cast<float4*>(wslice + off) = nw;
   }
 }
 
+template <bool TC>
 __global__ void __launch_bounds__(FS_THREADS, 2)
 fused_step_kernel(const FsParams p) {
-  extern __shared__ __align__(16) float sm[];
-  float* patch = sm + SM_PATCH;
-  float* actT = sm + SM_ACT;
-  uint32_t* argw = reinterpret_cast<uint32_t*>(sm + SM_ARG);
-  float* ws = sm + SM_WS;
-  float* dh = sm + SM_DH;
-  float* dxs = sm + SM_DX;
-  float* cw = sm + SM_CW;
-  float* red = sm + SM_RED;
-  float* whs = sm + SM_WH;
+  extern __shared__ __align__(128) float sm[];
+  float* patch = sm + (TC ? T_PATCH : SM_PATCH);
+  float* actT = sm + (TC ? T_ACTB : SM_ACT);             // FFMA: [c][68] ; TC: blocked [c][b] tile
+  uint32_t* argw = reinterpret_cast<uint32_t*>(sm + (TC ? T_ARG : SM_ARG));
+  float* dh = sm + (TC ? T_DHB : SM_DH);                 // FFMA: [b][68] ; TC: blocked [b][n] tile (tail: staging)
+  float* dxs = sm + (TC ? T_DX : SM_DX);
+  float* cw = sm + (TC ? T_CW : SM_CW);
+  float* red = sm + (TC ? T_RED : SM_RED);
+  float* whs = sm + (TC ? T_WH : SM_WH);
   float* bh = whs + FS_U * WH_LD;
-  float* hrow = sm + SM_ROW;
-  float* hcol = sm + SM_HG;
+  float* hrow = sm + (TC ? T_ROW : SM_ROW);
+  float* hcol = sm + (TC ? T_HG : SM_HG);
   float* dzs = hcol + FS_B * 4;
+  const WTile<TC> ws{TC ? sm : sm + SM_WS};
   __shared__ int s_last;
+  __shared__ uint64_t s_mbar;                            // TC: completion of the committed tcgen05.mma batch
+  __shared__ uint32_t s_tmem;
+  uint32_t mma_parity = 0;
+  if (TC) {
+    if (threadIdx.x < 32) umma::tmem_alloc(&s_tmem, FS_TMEM_COLS);
+    if (threadIdx.x == 0) umma::mbar_init(&s_mbar, 1);
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+  }
+  const uint32_t tmem = TC ? s_tmem : 0u;
 
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int pix = blockIdx.x, py = pix / FS_PW, px = pix - py * FS_PW;
@@ -376,7 +438,7 @@ fused_step_kernel(const FsParams p) {
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
           const int idx4 = t + i * FS_THREADS, c = idx4 >> 4, n4 = idx4 & 15;
-          *reinterpret_cast<float4*>(ws + c * WS_LD + n4 * 4) = wreg[i];
+          ws.store(c, n4 * 4, wreg[i]);
         }
       }
     }
@@ -408,7 +470,12 @@ fused_step_kernel(const FsParams p) {
             o = fmaxf(o, 0.f);
             if (o > best) { best = o; besti = dy * 2 + dx; }
           }
-        actT[c * ACT_LD + b] = best;
+        if (TC) {
+          actT[umma::blk(c, b, 512)] = best;
+          sm[T_ACTK + umma::blk(b, c, 256)] = best;
+        } else {
+          actT[c * ACT_LD + b] = best;
+        }
         bits |= (uint32_t)besti << (2 * cc);
       }
       argw[b * 4 + cg] = bits;
@@ -416,9 +483,36 @@ fused_step_kernel(const FsParams p) {
     if (pending) {
       // the previous step's slice: its reduce-scatter contributions / reduced values arrived while the tail and this
       // step's convolution ran
-      finish_slice(p, e - 1u, pix, owner, gacc, ws, gslice, wslice, aslice, s_hprev);
+      finish_slice<TC>(p, e - 1u, pix, owner, gacc, ws, gslice, wslice, aslice, s_hprev);
       pending = false;
     }
+    if (TC) {
+      // split-K partial on the tensor core: D1[b, n] = sum_c act[b, c] * W_p[c, n]  (4 x UMMA 128x64x8, TF32)
+      umma::fence_operands();
+      __syncthreads();
+      if (t == 0) {
+        umma::fence_after_sync();
+        const uint32_t a0 = umma::smem_u32(sm + T_ACTK), b0 = umma::smem_u32(sm + T_WTK);
+        const uint32_t id = umma::idesc_tf32(128, 64, 0, 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma::mma_tf32(tmem, umma::desc(a0 + 2 * k * 128, 128, 1024), umma::desc(b0 + 2 * k * 128, 128, 1024), id, k > 0);
+        umma::commit(&s_mbar);
+      }
+      if ((warp & 3) < 2) {
+        // warps 0,1 read columns [0,32) of rows 0..63, warps 4,5 columns [32,64): one accumulator row per thread
+        umma::mbar_wait(&s_mbar, mma_parity);
+        umma::fence_after_sync();
+        const int b = (warp & 3) * 32 + lane, col0 = (warp >> 2) * 32;
+        float r[32];
+        umma::tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + col0, r);
+        float4* dst = reinterpret_cast<float4*>(p.part + (long)pix * (FS_B * FS_U) + b * FS_U + col0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) __stcg(dst + j, make_float4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]));
+        umma::fence_before_sync();
+      }
+      mma_parity ^= 1u;
+    } else {
     __syncthreads();
     {
       // split-K partial: h_p[b, n] = sum_c act[b, c] * W_p[c, n]; thread tile 4 rows x 4 units
@@ -431,7 +525,7 @@ fused_step_kernel(const FsParams p) {
 #pragma unroll 8
       for (int c = 0; c < FS_C; ++c) {
         const float4 a = *reinterpret_cast<const float4*>(actT + c * ACT_LD + tb * 4);
-        const float4 wv = *reinterpret_cast<const float4*>(ws + c * WS_LD + tn * 4);
+        const float4 wv = ws.load(c, tn * 4);
         const float av[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -444,6 +538,7 @@ fused_step_kernel(const FsParams p) {
       for (int i = 0; i < 4; ++i)
         __stcg(dst + (tb * 4 + i) * (FS_U / 4) + tn, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
     }
+    }   // !TC
     FS_STAMP(1);
     grid_barrier(p, bar_base + (uint32_t)grid, 1);
     FS_STAMP(2);
@@ -534,7 +629,15 @@ fused_step_kernel(const FsParams p) {
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int f4 = t + i * FS_THREADS, b = f4 >> 4, k4 = f4 & 15;
-        *reinterpret_cast<float4*>(dh + b * DH_LD + k4 * 4) = __ldcg(reinterpret_cast<const float4*>(p.hbuf + HB_DH) + f4);
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(p.hbuf + HB_DH) + f4);
+        if (TC) {
+          *reinterpret_cast<float4*>(dh + umma::blk(b, k4 * 4, 512)) = v;
+          float* dt = sm + T_DHT;
+          dt[umma::blk(k4 * 4, b, 512)] = v.x; dt[umma::blk(k4 * 4 + 1, b, 512)] = v.y;
+          dt[umma::blk(k4 * 4 + 2, b, 512)] = v.z; dt[umma::blk(k4 * 4 + 3, b, 512)] = v.w;
+        } else {
+          *reinterpret_cast<float4*>(dh + b * DH_LD + k4 * 4) = v;
+        }
       }
       if (hg_cta) {
         if (t < FS_B) *reinterpret_cast<float4*>(hcol + t * 4) = __ldcg(reinterpret_cast<const float4*>(p.hbuf + HB_H) + t * 16 + pix);
@@ -543,8 +646,24 @@ fused_step_kernel(const FsParams p) {
         d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
       }
     }
+    if (TC) umma::fence_operands();
     __syncthreads();
     FS_STAMP(5);
+    if (TC && t == 0) {
+      // filter gradient dW_p^T[n, c] = sum_b dh[b, n] * act[b, c] and data gradient dx_p[b, c] = sum_n dh[b, n] * W_p[c, n]
+      // on the tensor core (2 x 8 UMMA 128x32x8, TF32); they run while CTAs 0..15 do the head gradients below
+      umma::fence_after_sync();
+      const uint32_t id = umma::idesc_tf32(128, 32, 0, 0);
+      const uint32_t aT = umma::smem_u32(sm + T_DHT), bA = umma::smem_u32(sm + T_ACTB);
+      const uint32_t aD = umma::smem_u32(sm + T_DHB), bW = umma::smem_u32(sm + T_WSB);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        umma::mma_tf32(tmem + 64, umma::desc(aT + 2 * k * 128, 128, 2048), umma::desc(bA + 2 * k * 128, 128, 2048), id, k > 0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        umma::mma_tf32(tmem + 96, umma::desc(aD + 2 * k * 128, 128, 2048), umma::desc(bW + 2 * k * 128, 128, 2048), id, k > 0);
+      umma::commit(&s_mbar);
+    }
     if (hg_cta) {
       // head kernel gradient rows [4*pix, 4*pix+4): dWh[k, c] = sum_b h[b, k] * dz[b, c]   -> packed small block
       float* sp = p.small;
@@ -561,7 +680,7 @@ fused_step_kernel(const FsParams p) {
           const int n = t - 64;
           float a = 0.f;
 #pragma unroll 8
-          for (int b = 0; b < FS_B; ++b) a += dh[b * DH_LD + n];
+          for (int b = 0; b < FS_B; ++b) a += TC ? dh[umma::blk(b, n, 512)] : dh[b * DH_LD + n];
           __stcg(sp + 320 + n, a);
         } else if (t < 128 + FS_NC) {                          // head bias: dbh[c] = sum_b dz[b, c]
           const int c = t - 128;
@@ -585,6 +704,34 @@ fused_step_kernel(const FsParams p) {
     FS_STAMP(6);
     // dW_p[c, n] = sum_b act[b, c] * dh[b, n] ; thread tile 2 channels x 4 units (kept in registers until the
     // optimizer / the reduction consumes it)
+    if (TC) {
+      // accumulators come back one row per thread: dW^T rows (n) go through a small staging tile so that every thread
+      // ends up with the same 2 x 4 tile of dW_p as in the FFMA variant; dx rows get the ReLU mask on the way out
+      float* gb = sm + T_GB;
+      if ((warp & 3) < 2) {
+        umma::mbar_wait(&s_mbar, mma_parity);
+        umma::fence_after_sync();
+        const int row = (warp & 3) * 32 + lane;
+        float r[32];
+        if (warp < 4) {
+          umma::tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + 64, r);       // row = unit n, columns = channel c
+#pragma unroll
+          for (int c = 0; c < 32; ++c) gb[c * 68 + row] = r[c];
+        } else {
+          umma::tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + 96, r);       // row = batch row b, columns = c
+#pragma unroll
+          for (int c = 0; c < 32; ++c) dxs[row * DX_LD + c] = actT[umma::blk(c, row, 512)] > 0.f ? r[c] : 0.f;
+        }
+        umma::fence_before_sync();
+      }
+      mma_parity ^= 1u;
+      __syncthreads();
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const float4 v = *reinterpret_cast<const float4*>(gb + (tc * 2 + i) * 68 + tn * 4);
+        gacc[i][0] = v.x; gacc[i][1] = v.y; gacc[i][2] = v.z; gacc[i][3] = v.w;
+      }
+    } else
     {
 #pragma unroll
       for (int i = 0; i < 2; ++i)
@@ -612,7 +759,7 @@ fused_step_kernel(const FsParams p) {
       for (int i = 0; i < 2; ++i)
         ll_store4(dst, (tc * 2 + i) * (FS_U / 4) + tn, make_float4(gacc[i][0], gacc[i][1], gacc[i][2], gacc[i][3]), e);
     }
-    {
+    if (!TC) {
       // dx_p[b, c] = sum_n dh[b, n] * W_p[c, n], masked by ReLU; thread tile 4 rows x 2 channels
       const int tb = t >> 4, tq = t & 15;
       float acc[4][2];
@@ -620,8 +767,8 @@ fused_step_kernel(const FsParams p) {
       for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = 0.f;
 #pragma unroll 4
       for (int n4 = 0; n4 < FS_U / 4; ++n4) {
-        const float4 w0 = *reinterpret_cast<const float4*>(ws + (tq * 2) * WS_LD + n4 * 4);
-        const float4 w1 = *reinterpret_cast<const float4*>(ws + (tq * 2 + 1) * WS_LD + n4 * 4);
+        const float4 w0 = ws.load(tq * 2, n4 * 4);
+        const float4 w1 = ws.load(tq * 2 + 1, n4 * 4);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const float4 d = *reinterpret_cast<const float4*>(dh + (tb * 4 + i) * DH_LD + n4 * 4);
@@ -648,9 +795,8 @@ fused_step_kernel(const FsParams p) {
       for (int i = 0; i < 2; ++i) {
         const int c = tc * 2 + i, off = c * FS_U + tn * 4;
         const float4 gv = make_float4(gacc[i][0], gacc[i][1], gacc[i][2], gacc[i][3]);
-        float4* wsm = reinterpret_cast<float4*>(ws + c * WS_LD + tn * 4);
-        const float4 nw = update_four(p.opt, *wsm, gv, p.s1, p.s2, aslice + off, h);
-        *wsm = nw;
+        const float4 nw = update_four(p.opt, ws.load(c, tn * 4), gv, p.s1, p.s2, aslice + off, h);
+        ws.store(c, tn * 4, nw);
         *reinterpret_cast<float4*>(gslice + off) = gv;
         *reinterpret_cast<float4*>(wslice + off) = nw;
       }
@@ -825,7 +971,7 @@ fused_step_kernel(const FsParams p) {
       if (owner == R || s + 1 == p.nsteps) {
         // owner: its peers sent their contributions in the middle of P3, they are here by now -> reduce, publish the
         // reduced slice, update. (Everyone on the last step of a launch: drain.)
-        finish_slice(p, e, pix, owner, gacc, ws, gslice, wslice, aslice, h);
+        finish_slice<TC>(p, e, pix, owner, gacc, ws, gslice, wslice, aslice, h);
       } else {
         pending = true;                       // non-owner: picks the reduced slice up under the next step's convolution
         if (t == 0) s_hprev = h;
@@ -840,10 +986,15 @@ fused_step_kernel(const FsParams p) {
     FS_STAMP(11);
     if (*reinterpret_cast<volatile int*>(p.status) != 0) break;    // a wait timed out somewhere: drain
   }
+  if (TC) {
+    umma::fence_before_sync();
+    __syncthreads();
+    if (threadIdx.x < 32) { umma::fence_after_sync(); umma::tmem_dealloc(tmem, FS_TMEM_COLS); }
+  }
 }
 
 struct DeviceInit { bool done = false; int max_blocks = 0; };
-DeviceInit g_init[64];
+DeviceInit g_init[2][64];      // [variant: 0 exact-fp32 FFMA, 1 TF32 tensor core][device]
 std::mutex g_init_mu;
 
 }  // namespace
@@ -855,7 +1006,7 @@ struct TfdeFusedStepDesc {
   int B, nsteps, ncls, opt;
   float* w; float* g; float* s1; float* s2;
   long off_ck, off_cb, off_dk, off_db, off_hk, off_hb, n;
-  float loss_scale; int rank; int world; int reserved;
+  float loss_scale; int rank; int world; int use_tc;     // use_tc: 1 = TF32 tcgen05 GEMMs, 0 = exact fp32 FFMA
   void* hp; float* metrics; float* tails;
   float* part; float* hbuf; float* cpart; float* small_block;
   void* state; void* status;
@@ -888,22 +1039,40 @@ TFDE_API int tfde_fused_step(const TfdeFusedStepDesc* d, cudaStream_t stream) {
   int dev = 0;
   cudaError_t err = cudaGetDevice(&dev);
   if (err != cudaSuccess) return (int)err;
-  const size_t smem = (size_t)SM_TOTAL * sizeof(float);
+  const int tcv = d->use_tc ? 1 : 0;
+  const size_t smem = (size_t)(tcv ? T_TOTAL : SM_TOTAL) * sizeof(float);
   {
     std::lock_guard<std::mutex> lk(g_init_mu);
-    DeviceInit& di = g_init[dev & 63];
+    DeviceInit& di = g_init[tcv][dev & 63];
     if (!di.done) {
-      err = cudaFuncSetAttribute(fused_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      const void* fn = tcv ? (const void*)fused_step_kernel<true> : (const void*)fused_step_kernel<false>;
+      err = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (err != cudaSuccess) return (int)err;
+      // two CTAs per SM need the large shared-memory carve-out (the default is sized for ONE block of this kernel)
+      err = cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
       if (err != cudaSuccess) return (int)err;
       int per_sm = 0, sms = 0;
-      err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_step_kernel, FS_THREADS, smem);
+      err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, FS_THREADS, smem);
       if (err != cudaSuccess) return (int)err;
       err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
       if (err != cudaSuccess) return (int)err;
       di.max_blocks = per_sm * sms;
       di.done = true;
     }
-    if (di.max_blocks < FS_PIX) return TFDE_ERR_INVALID;     // the grid could not be co-resident on this GPU
+    if (di.max_blocks < FS_PIX && !(tcv && getenv("TFDE_FUSED_TC_FORCE"))) {   // the grid could not be co-resident on this GPU
+      cudaFuncAttributes fa{};
+      const void* fn2 = tcv ? (const void*)fused_step_kernel<true> : (const void*)fused_step_kernel<false>;
+      cudaFuncGetAttributes(&fa, fn2);
+      size_t avail2 = 0;
+      cudaOccupancyAvailableDynamicSMemPerBlock(&avail2, fn2, 2, FS_THREADS);
+      int smem_sm = 0;
+      cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+      fprintf(stderr, "tfde_fused_step: only %d CTAs of %zu bytes shared memory can be co-resident (need %d); regs %d, "
+              "static smem %zu, max dyn %d, carveout %d, dyn smem available at 2 CTAs/SM %zu, smem per SM %d\n",
+              di.max_blocks, smem, FS_PIX, fa.numRegs, fa.sharedSizeBytes, fa.maxDynamicSharedSizeBytes,
+              fa.preferredShmemCarveout, avail2, smem_sm);
+      return TFDE_ERR_INVALID;
+    }
   }
   FsParams p{};
   p.x = d->x; p.y = (const long long*)d->y; p.x_is_u8 = d->x_is_u8; p.in_scale = d->in_scale;
@@ -930,7 +1099,13 @@ TFDE_API int tfde_fused_step(const TfdeFusedStepDesc* d, cudaStream_t stream) {
   attr[0].id = cudaLaunchAttributeCooperative;
   attr[0].val.cooperative = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  err = cudaLaunchKernelEx(&cfg, fused_step_kernel, p);
+  if (tcv && g_init[1][dev & 63].max_blocks < FS_PIX) {
+    // TFDE_FUSED_TC_FORCE (bring-up experiment): the runtime's occupancy calculator grants kernels that allocate tensor
+    // memory ONE CTA per SM, so a cooperative launch of 169 CTAs is refused; launch plainly and rely on the bounded
+    // waits to report (status word) rather than hang if the CTAs turn out not to be co-resident
+    cfg.numAttrs = 0;
+  }
+  err = tcv ? cudaLaunchKernelEx(&cfg, fused_step_kernel<true>, p) : cudaLaunchKernelEx(&cfg, fused_step_kernel<false>, p);
   if (err != cudaSuccess) return (int)err;
   TFDE_RETURN_LAUNCH_STATUS();
 }
@@ -972,4 +1147,14 @@ TFDE_API int tfde_fused_exec(const TfdeFusedStepDesc* d, const void* host_x, con
   int rc = tfde_fused_step(d, stream);
   if (rc != 0) return rc;
   return (int)cudaEventRecord((cudaEvent_t)ev_done, stream);
+}
+
+// Diagnostics: resident CTAs per SM the runtime grants either variant at `dyn_smem` bytes of dynamic shared memory.
+TFDE_API int tfde_fused_step_occupancy(int use_tc, size_t dyn_smem) {
+  const void* fn = use_tc ? (const void*)fused_step_kernel<true> : (const void*)fused_step_kernel<false>;
+  cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(dyn_smem > 49152 ? dyn_smem : 49152));
+  cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+  int per_sm = -1;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, FS_THREADS, dyn_smem);
+  return per_sm;
 }
