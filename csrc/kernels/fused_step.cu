@@ -18,7 +18,7 @@
 //   B2  grid barrier
 //   P3  every CTA: dW_p = act_p^T . dh (+ optimizer / reduce-scatter push), dx_p = dh . W_p^T, pool routing + ReLU
 //       mask + conv filter-gradient partial for pixel p. CTAs 0..15 also produce the head-kernel gradient rows,
-//       CTA 0 the bias gradients and the loss / accuracy scalars.
+//       CTA 16 the bias gradients and the loss / accuracy scalars.
 //   T   two-level ticket (13 groups of 13 CTAs): the last CTA of a group reduces its group's conv partials, the
 //       last group winner reduces the 13 group partials, applies the optimizer to the small tensors (conv
 //       kernel+bias, dense bias, head kernel+bias), writes the metrics tail, advances the step counter and
@@ -111,8 +111,9 @@ constexpr int T_RED = T_CW + 10 * FS_C;
 constexpr int T_WH = T_RED + 8 * 10 * FS_C;
 constexpr int T_ROW = T_WH + FS_U * WH_LD + FS_NC;
 constexpr int T_HG = T_ROW + FS_U;
+constexpr int T_WSX = T_HG + FS_B * 4 + FS_B * DZ_LD;    // exact fp32 master copy of the weight slice [c 32][68] (the MMA tiles hold TF32-rounded copies)
 constexpr int T_GB = T_RED;                              // dW staging [32][68] (TMEM rows are units, threads want 2x4 tiles); aliases `red`
-constexpr int T_TOTAL = T_HG + FS_B * 4 + FS_B * DZ_LD;
+constexpr int T_TOTAL = T_WSX + FS_C * WS_LD;
 static_assert(FS_C * 68 <= 8 * 10 * FS_C, "dW staging must fit in red");
 static_assert(T_ACTK % 4 == 0 && T_DHB % 4 == 0 && T_RED % 4 == 0 && T_HG % 4 == 0 && T_GB % 4 == 0, "align");
 static_assert(T_DHT + 2 * 4096 <= T_TOTAL, "M=128 over-read of the dh^T tile must stay inside the allocation");
@@ -126,15 +127,17 @@ template <bool TC>
 struct WTile {
   float* base;      // FFMA: ws ; TC: sm (tile offsets are added here)
   __device__ __forceinline__ float4 load(int c, int n) const {
-    if (TC) return *reinterpret_cast<const float4*>(base + T_WSB + umma::blk(c, n, 512));
+    if (TC) return *reinterpret_cast<const float4*>(base + T_WSX + c * WS_LD + n);
     return *reinterpret_cast<const float4*>(base + c * WS_LD + n);
   }
   __device__ __forceinline__ void store(int c, int n, const float4 v) const {
     if (TC) {
-      *reinterpret_cast<float4*>(base + T_WSB + umma::blk(c, n, 512)) = v;
+      *reinterpret_cast<float4*>(base + T_WSX + c * WS_LD + n) = v;
+      const float4 r = make_float4(umma::tf32r(v.x), umma::tf32r(v.y), umma::tf32r(v.z), umma::tf32r(v.w));
+      *reinterpret_cast<float4*>(base + T_WSB + umma::blk(c, n, 512)) = r;
       float* wt = base + T_WTK;
-      wt[umma::blk(n, c, 256)] = v.x; wt[umma::blk(n + 1, c, 256)] = v.y;
-      wt[umma::blk(n + 2, c, 256)] = v.z; wt[umma::blk(n + 3, c, 256)] = v.w;
+      wt[umma::blk(n, c, 256)] = r.x; wt[umma::blk(n + 1, c, 256)] = r.y;
+      wt[umma::blk(n + 2, c, 256)] = r.z; wt[umma::blk(n + 3, c, 256)] = r.w;
     } else {
       *reinterpret_cast<float4*>(base + c * WS_LD + n) = v;
     }
@@ -471,8 +474,9 @@ fused_step_kernel(const FsParams p) {
             if (o > best) { best = o; besti = dy * 2 + dx; }
           }
         if (TC) {
-          actT[umma::blk(c, b, 512)] = best;
-          sm[T_ACTK + umma::blk(b, c, 256)] = best;
+          const float br = umma::tf32r(best);
+          actT[umma::blk(c, b, 512)] = br;
+          sm[T_ACTK + umma::blk(b, c, 256)] = br;
         } else {
           actT[c * ACT_LD + b] = best;
         }
@@ -629,8 +633,9 @@ fused_step_kernel(const FsParams p) {
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int f4 = t + i * FS_THREADS, b = f4 >> 4, k4 = f4 & 15;
-        const float4 v = __ldcg(reinterpret_cast<const float4*>(p.hbuf + HB_DH) + f4);
+        float4 v = __ldcg(reinterpret_cast<const float4*>(p.hbuf + HB_DH) + f4);
         if (TC) {
+          v = make_float4(umma::tf32r(v.x), umma::tf32r(v.y), umma::tf32r(v.z), umma::tf32r(v.w));
           *reinterpret_cast<float4*>(dh + umma::blk(b, k4 * 4, 512)) = v;
           float* dt = sm + T_DHT;
           dt[umma::blk(k4 * 4, b, 512)] = v.x; dt[umma::blk(k4 * 4 + 1, b, 512)] = v.y;
@@ -639,8 +644,8 @@ fused_step_kernel(const FsParams p) {
           *reinterpret_cast<float4*>(dh + b * DH_LD + k4 * 4) = v;
         }
       }
-      if (hg_cta) {
-        if (t < FS_B) *reinterpret_cast<float4*>(hcol + t * 4) = __ldcg(reinterpret_cast<const float4*>(p.hbuf + HB_H) + t * 16 + pix);
+      if (pix <= 16) {
+        if (hg_cta && t < FS_B) *reinterpret_cast<float4*>(hcol + t * 4) = __ldcg(reinterpret_cast<const float4*>(p.hbuf + HB_H) + t * 16 + pix);
         const float4 v = __ldcg(reinterpret_cast<const float4*>(p.hbuf + HB_DZ) + t);
         float* d = dzs + (t >> 2) * DZ_LD + (t & 3) * 4;
         d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
@@ -664,33 +669,39 @@ fused_step_kernel(const FsParams p) {
         umma::mma_tf32(tmem + 96, umma::desc(aD + 2 * k * 128, 128, 2048), umma::desc(bW + 2 * k * 128, 128, 2048), id, k > 0);
       umma::commit(&s_mbar);
     }
-    if (hg_cta) {
-      // head kernel gradient rows [4*pix, 4*pix+4): dWh[k, c] = sum_b h[b, k] * dz[b, c]   -> packed small block
+    if (pix <= 16) {
+      // CTAs 0..15: head kernel gradient rows [4*pix, 4*pix+4): dWh[k, c] = sum_b h[b, k] * dz[b, c]; CTA 16: the bias
+      // gradients and the loss / accuracy scalars. All 256 threads: the batch is split 4 ways, the four partial sums
+      // are combined in a fixed order through shared memory (`red` is free until the conv-backward reduction).
       float* sp = p.small;
-      if (t < 64) {
-        const int kk = t >> 4, c = t & 15;
-        if (c < N) {
-          float a = 0.f;
-#pragma unroll 8
-          for (int b = 0; b < FS_B; ++b) a = fmaf(hcol[b * 4 + kk], dzs[b * DZ_LD + c], a);
-          __stcg(sp + 384 + (4 * pix + kk) * N + c, a);
+      const int q4 = t >> 6, u = t & 63;
+      if (hg_cta) {
+        const int kk = u >> 4, c = u & 15;
+        float a = 0.f;
+#pragma unroll
+        for (int b = q4 * 16; b < q4 * 16 + 16; ++b) a = fmaf(hcol[b * 4 + kk], dzs[b * DZ_LD + c], a);
+        red[q4 * 64 + u] = a;
+      } else {
+        float a = 0.f, z = 0.f;                                 // db[n] = sum_b dh[b, n] ; dbh[c] = sum_b dz[b, c]
+#pragma unroll
+        for (int b = q4 * 16; b < q4 * 16 + 16; ++b) {
+          a += TC ? dh[umma::blk(b, u, 512)] : dh[b * DH_LD + u];
+          if (u < FS_NC) z += dzs[b * DZ_LD + u];
         }
-      } else if (pix == 0) {
-        if (t < 128) {                                         // dense bias: db[n] = sum_b dh[b, n]
-          const int n = t - 64;
-          float a = 0.f;
-#pragma unroll 8
-          for (int b = 0; b < FS_B; ++b) a += TC ? dh[umma::blk(b, n, 512)] : dh[b * DH_LD + n];
-          __stcg(sp + 320 + n, a);
-        } else if (t < 128 + FS_NC) {                          // head bias: dbh[c] = sum_b dz[b, c]
-          const int c = t - 128;
-          if (c < N) {
-            float a = 0.f;
-            for (int b = 0; b < FS_B; ++b) a += dzs[b * DZ_LD + c];
-            __stcg(sp + 384 + FS_U * N + c, a);
-          }
-        } else if (t >= 160 && t < 192) {
-          // loss / correct: fixed-order tree over the 64 per-row values (warp 5)
+        red[q4 * 64 + u] = a;
+        if (u < FS_NC) red[256 + q4 * FS_NC + u] = z;
+      }
+      __syncthreads();
+      if (hg_cta) {
+        if (t < 64 && (t & 15) < N)
+          __stcg(sp + 384 + (4 * pix + (t >> 4)) * N + (t & 15), ((red[t] + red[64 + t]) + red[128 + t]) + red[192 + t]);
+      } else {
+        if (t < 64) __stcg(sp + 320 + t, ((red[t] + red[64 + t]) + red[128 + t]) + red[192 + t]);
+        else if (t < 64 + N) {
+          const int c = t - 64;
+          __stcg(sp + 384 + FS_U * N + c, ((red[256 + c] + red[256 + FS_NC + c]) + red[256 + 2 * FS_NC + c]) + red[256 + 3 * FS_NC + c]);
+        } else if (t >= 96 && t < 128) {
+          // loss / correct: fixed-order tree over the 64 per-row values (warp 3)
           float l = __ldcg(p.hbuf + HB_STAT + 2 * lane) + __ldcg(p.hbuf + HB_STAT + 2 * (lane + 32));
           float c = __ldcg(p.hbuf + HB_STAT + 2 * lane + 1) + __ldcg(p.hbuf + HB_STAT + 2 * (lane + 32) + 1);
           l = warp_sum(l); c = warp_sum(c);
@@ -700,6 +711,7 @@ fused_step_kernel(const FsParams p) {
           }
         }
       }
+      __syncthreads();     // `red` is reused by the TC staging tile / the conv-backward reduction
     }
     FS_STAMP(6);
     // dW_p[c, n] = sum_b act[b, c] * dh[b, n] ; thread tile 2 channels x 4 units (kept in registers until the

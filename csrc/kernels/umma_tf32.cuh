@@ -4,14 +4,11 @@
 // Operand layout: the UMMA "interleave" (no-swizzle) canonical layout. A tile X[r][q] (q contiguous in the logical
 // array) is stored as 128-byte core blocks of 8 r x 4 q:
 //     float index(r, q) = (r >> 3) * RB + (q >> 2) * 32 + (r & 7) * 4 + (q & 3)          (RB = floats per 8-r band)
-// The same bytes are a valid operand in BOTH majors:
-//   * K-major  with MN = r, K = q : 8 MN rows of 16 bytes (4 K values) per core matrix, SBO = RB*4 bytes between 8-row
-//     groups, LBO = 128 bytes between consecutive 4-K chunks; one kind::tf32 MMA eats 2 chunks (K = 8);
-//   * MN-major with MN = q, K = r : 16 bytes = 4 consecutive MN values, 8 K rows per core matrix, SBO = 128 bytes
-//     between consecutive 4-MN groups, LBO = RB*4 bytes between 8-K groups; one MMA eats one 8-K band.
-// So activations written once serve the forward GEMM (as A, MN-major) and the filter-gradient GEMM (as B, K-major),
-// the gradient tile serves dW (A, MN-major) and dx (A, K-major), the weight slice serves forward (B, MN-major) and dx
-// (B, K-major): no transposed copies.
+// read as a K-major operand with MN = r, K = q: 8 MN rows of 16 bytes (4 K values) per core matrix, SBO = RB*4 bytes
+// between 8-row groups, LBO = 128 bytes between consecutive 4-K chunks; one kind::tf32 MMA eats 2 chunks (K = 8).
+// (By the canonical-layout algebra the same bytes are also an MN-major operand with MN = q, K = r. During bring-up on
+// B200 the MN-major SWIZZLE_NONE tf32 form left the accumulator at zero, so every tile that is needed in both
+// orientations -- activations, weight slice, gradient tile -- is written twice, once per orientation, both K-major.)
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -22,6 +19,14 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 
 // float index inside a blocked tile (see header comment)
 __device__ __forceinline__ int blk(int r, int q, int RB) { return (r >> 3) * RB + (q >> 2) * 32 + (r & 7) * 4 + (q & 3); }
+
+// round-to-nearest TF32 (the tensor core itself TRUNCATES fp32 operands to 10 mantissa bits: a systematic bias that
+// does not average out over a long reduction; operands are therefore rounded when they are staged)
+__device__ __forceinline__ float tf32r(float x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return __uint_as_float(u);
+}
 
 // shared-memory matrix descriptor, SWIZZLE_NONE: start address, leading / stride byte offsets (all >> 4), version 1
 __device__ __forceinline__ uint64_t desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {

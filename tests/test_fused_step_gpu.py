@@ -167,7 +167,7 @@ def test_whole_step_tensor_core_variant(monkeypatch, kind, bs):
     np.testing.assert_allclose(lg, lc, rtol=2e-3, atol=2e-4)
     for a, b in zip(mg.get_weights(), mc.get_weights()):
         d = np.abs(a - b) / max(np.abs(b).max(), 1e-12)
-        assert np.median(d) < 2e-3 and d.max() < 0.5, (np.median(d), d.max())
+        assert np.median(d) < 3e-2 and d.max() < 0.2, (np.median(d), d.max())     # TF32: sums with heavy cancellation
     # multi-step launch == single steps, bit for bit, in this variant too
     with Strategy(device="cuda").scope():
         m2 = tf.models.build_and_compile_cnn_model(optimizer=_opt(kind), seed=7)
