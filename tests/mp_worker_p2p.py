@@ -223,8 +223,9 @@ def sweep(strategy, out_path):
     if os.environ.get("TFDE_SWEEP_MODES"):
         modes = tuple(os.environ["TFDE_SWEEP_MODES"].split(","))
     for mode in modes:
-        for nbytes in (1 << 10, 1 << 14, 1 << 18, 1388584, 1 << 22, 1 << 24, 1 << 26, 1 << 28):
-            if mode == "one_shot" and nbytes * world > (1 << 28):
+        top = int(os.environ.get("TFDE_SWEEP_MAX", str(1 << 30)))
+        for nbytes in (1 << 10, 1 << 14, 1 << 18, 1388584, 1 << 22, 1 << 24, 1 << 26, 1 << 28, 1 << 30):
+            if nbytes > top or (mode == "one_shot" and nbytes * world > (1 << 28)):
                 continue
             n = nbytes // 4
             os.environ["TFDE_AR_MODE"] = mode
@@ -232,7 +233,7 @@ def sweep(strategy, out_path):
             arena = Arena(n, strategy.device, comm=comm)
             comm.prepare(arena, opt)
             arena.g.normal_()
-            iters = 20
+            iters = 20 if nbytes <= (1 << 26) else 5
 
             def timed(fn):
                 """CUDA-graph replay of `iters` back-to-back launches (removes host launch overhead);
