@@ -292,7 +292,11 @@ def run_ours(args):
     K = args.steps
     W = max(args.warmup, 3)
     R = max(1, args.repeats)
+    # steps_per_execution (Keras): the device-timed region feeds device-resident batches, where one launch can take all
+    # K steps; the end-to-end region wants >= 4 executions in flight so that the H2D copies of one execution overlap the
+    # kernel of the previous one
     spe = args.steps_per_execution if args.steps_per_execution > 0 else max(1, min(16, K // 4))
+    spe_dev = args.steps_per_execution if args.steps_per_execution > 0 else max(1, min(64, K))
     if args.dtype == "bf16":
         tf.keras.mixed_precision.set_global_policy("mixed_bfloat16")
     check = correctness_check(tf, strategy, args, rank, world) if not args.no_check else None
@@ -348,6 +352,7 @@ def run_ours(args):
         pool_x = torch.rand((P * B, 784), generator=gen, dtype=torch.float32, device=dev)
     pool_y = torch.randint(0, 10, (P * B,), generator=gen, dtype=torch.int64, device=dev)
     chunks = [(i, min(spe, K - i)) for i in range(0, K, spe)]
+    chunks_dev = [(i, min(spe_dev, K - i)) for i in range(0, K, spe_dev)]
 
     def timed_device(rep):
         torch.empty(256 << 20, dtype=torch.uint8, device=dev).fill_(rep + 1)      # evict L2
@@ -358,7 +363,7 @@ def run_ours(args):
         c0 = native.launch_count()
         sampler.begin()
         model.record_event(e0)            # both events sit on the stream the model launches its steps on
-        for i, n in chunks:
+        for i, n in chunks_dev:
             lo = (base + i) * B
             model.train_on_batches(pool_x[lo:lo + n * B], pool_y[lo:lo + n * B], steps=n, global_batch=gb)
         model.record_event(e1)
@@ -367,6 +372,7 @@ def run_ours(args):
         barrier(world)
         return max_over_ranks(e0.elapsed_time(e1), world), native.launch_count() - c0
 
+    timed_device(R)                    # untimed pass: first launch of the device-resident execution shape
     dev_ms, launches = [], 0
     for rep in range(R):
         ms, launches = timed_device(rep)
@@ -421,6 +427,7 @@ def run_ours(args):
                    "global_batch": gb, "per_gpu_batch": B, "seq_len": None, "input": list(in_shape),
                    "parallelism": f"dp{world}", "optimizer": args.optimizer,
                    "whole_step_kernel": fused, "steps_per_execution": spe,
+                   "steps_per_execution_device_timed": spe_dev,
                    "l2": (f"inputs larger than L2: each timed step reads a distinct device-resident batch from a "
                           f"{(P * per) >> 20} MiB pool (L2 evicted by a 256 MiB write before each repeat); K steps "
                           f"back to back, one event pair; weights stay resident as in training"),
