@@ -868,6 +868,28 @@ fused_step_kernel(const FsParams p) {
     if (s_last) {
       __threadfence();
       float* sp = p.small;
+      float* stage = dh;                                   // packed small block in shared memory (dh is dead by now)
+      float4* stage4 = reinterpret_cast<float4*>(stage);
+      const int n4 = (nsmall + 3) >> 2;
+      // everything the tail will need from L2 is requested up front, so the round trips overlap: the head / bias
+      // gradients written by CTAs 0..16, the current values of the small parameters, the metric accumulators
+      float4 early = make_float4(0.f, 0.f, 0.f, 0.f);
+      const int ie = 80 + t;
+      if (ie < n4) {
+        early.x = __ldcg(sp + 4 * ie);
+        early.y = 4 * ie + 1 < nsmall ? __ldcg(sp + 4 * ie + 1) : 0.f;
+        early.z = 4 * ie + 2 < nsmall ? __ldcg(sp + 4 * ie + 2) : 0.f;
+        early.w = 4 * ie + 3 < nsmall ? __ldcg(sp + 4 * ie + 3) : 0.f;
+      }
+      const int ntrain = nsmall - 4;
+      long ai[8]; float wv[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int i = t + j * FS_THREADS;
+        ai[j] = i < ntrain ? small_to_arena(p, i) : -1;
+        wv[j] = ai[j] >= 0 ? __ldcg(p.w + ai[j]) : 0.f;
+      }
+      const float metric_prev = (t < 4 && p.metrics) ? __ldcg(p.metrics + t) : 0.f;
       if (t < 80) {
         float4 v[FS_GROUPS];
 #pragma unroll
@@ -876,31 +898,33 @@ fused_step_kernel(const FsParams p) {
         float4 a = v[0];
 #pragma unroll
         for (int j = 1; j < FS_GROUPS; ++j) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
-        __stcg(reinterpret_cast<float4*>(sp) + t, a);
+        stage4[t] = a;
+      }
+      if (ie < n4) stage4[ie] = early;
+      if (FS_THREADS + 80 < n4 && t + FS_THREADS + 80 < n4) {     // ncls > 13: a few more groups than threads
+        const int i2 = t + FS_THREADS + 80;
+        float4 e2;
+        e2.x = __ldcg(sp + 4 * i2); e2.y = 4 * i2 + 1 < nsmall ? __ldcg(sp + 4 * i2 + 1) : 0.f;
+        e2.z = 4 * i2 + 2 < nsmall ? __ldcg(sp + 4 * i2 + 2) : 0.f; e2.w = 4 * i2 + 3 < nsmall ? __ldcg(sp + 4 * i2 + 3) : 0.f;
+        stage4[i2] = e2;
       }
       __syncthreads();
-      // `sp` now holds this replica's packed small gradients + [loss*scale, correct, rows, 0]
-      float* stage = dh;                                   // reduced block (shared memory, dead by now)
-      if (W == 1) {
-        for (int i = t; i < nsmall; i += FS_THREADS) stage[i] = __ldcg(sp + i);
-      } else {
+      FS_STAMP(12);
+      // `stage` now holds this replica's packed small gradients + [loss*scale, correct, rows, 0]
+      if (W > 1) {
         // one-shot exchange of the packed small block (flag-in-data, double-buffered by step parity): push the own
         // block to every peer, gather the peers' blocks into shared memory with all loads in flight at once (not one
         // spin per peer), then sum in rank order
         const int parity = (int)(e & 1u);
-        const int n4 = (nsmall + 3) >> 2;
-        float4* stage4 = reinterpret_cast<float4*>(stage);
         float4* rbuf4 = stage4 + FS_SMALL_F4;                // [(W-1)][n4], spans dh .. end of shared memory (all dead here)
         for (int i = t; i < n4; i += FS_THREADS) {
-          float4 v;
-          v.x = __ldcg(sp + 4 * i); v.y = 4 * i + 1 < nsmall ? __ldcg(sp + 4 * i + 1) : 0.f;
-          v.z = 4 * i + 2 < nsmall ? __ldcg(sp + 4 * i + 2) : 0.f; v.w = 4 * i + 3 < nsmall ? __ldcg(sp + 4 * i + 3) : 0.f;
-          stage4[i] = v;
+          const float4 v = stage4[i];
           for (int k = 1; k < W; ++k) {
             const int peer = (R + k) % W;
             ll_store4(p.srecv[peer] + ((long)parity * W + R) * (2 * FS_SMALL_MAX), i, v, e);
           }
         }
+        FS_STAMP(13);
         const int tot = (W - 1) * n4;
         const float* rbase = p.srecv[R] + (long)parity * W * (2 * FS_SMALL_MAX);
         for (int base = t; base < tot; base += 4 * FS_THREADS) {
@@ -929,6 +953,7 @@ fused_step_kernel(const FsParams p) {
           }
         }
         __syncthreads();
+        FS_STAMP(14);
         for (int i = t; i < n4; i += FS_THREADS) {
           float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
           for (int r = 0; r < W; ++r) {
@@ -939,30 +964,19 @@ fused_step_kernel(const FsParams p) {
         }
       }
       __syncthreads();
-      const int ntrain = nsmall - 4;
-      {
-        // up to 8 parameters per thread: all loads first, then the updates (one L2 round trip, not eight)
-        long ai[8]; float wv[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int i = t + j * FS_THREADS;
-          ai[j] = i < ntrain ? small_to_arena(p, i) : -1;
-          wv[j] = ai[j] >= 0 ? __ldcg(p.w + ai[j]) : 0.f;
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          if (ai[j] >= 0) {
-            const float gv = stage[t + j * FS_THREADS];
-            p.g[ai[j]] = gv;
-            p.w[ai[j]] = update_one(p.opt, wv[j], gv, p.s1, p.s2, ai[j], h);
-          }
+      for (int j = 0; j < 8; ++j) {
+        if (ai[j] >= 0) {
+          const float gv = stage[t + j * FS_THREADS];
+          p.g[ai[j]] = gv;
+          p.w[ai[j]] = update_one(p.opt, wv[j], gv, p.s1, p.s2, ai[j], h);
         }
       }
       if (t < 4) {
         const float v = stage[ntrain + t];
         p.g[p.n + t] = v;
         p.w[p.n + t] = v;
-        if (p.metrics) p.metrics[t] += v;
+        if (p.metrics) p.metrics[t] = metric_prev + v;
         if (p.tails) p.tails[(long)s * 4 + t] = v;
       }
       __syncthreads();
@@ -973,8 +987,7 @@ fused_step_kernel(const FsParams p) {
           p.state[ST_EPOCH0] = epoch0 + (uint32_t)p.nsteps;
           if (p.tails) __threadfence_system();
         }
-        __threadfence();
-        st_release_gpu(p.state + ST_DONE, e);
+        st_release_gpu(p.state + ST_DONE, e);     // release: cumulative over the CTA's writes ordered by the barrier above
       }
     }
     FS_STAMP(9);

@@ -267,6 +267,15 @@ class FusedStepPlan:
         for i, name in enumerate(self.PHASES):
             d = (t[:, i + 1] - t[:, i]) / 1e3
             out[name] = (float(d.mean()), float(d.max()))
+        win = int(torch.argmax(t[:, 12]))            # the ticket winner is the only CTA that stamps inside the tail
+        if t[win, 12] > 0:
+            out["tail: local reduce of conv partials"] = (float((t[win, 12] - t[win, 8]) / 1e3),) * 2
+            if t[win, 13] > 0:
+                out["tail: pack + push small block to peers"] = (float((t[win, 13] - t[win, 12]) / 1e3),) * 2
+                out["tail: gather peers' small blocks (wait)"] = (float((t[win, 14] - t[win, 13]) / 1e3),) * 2
+                out["tail: sum + optimizer + release"] = (float((t[win, 9] - t[win, 14]) / 1e3),) * 2
+            else:
+                out["tail: optimizer + release"] = (float((t[win, 9] - t[win, 12]) / 1e3),) * 2
         out["step span (first start -> last end)"] = (float((t[:, 10].max() - t[:, 0].min()) / 1e3),) * 2
         out["P1..P3 critical path (max end - min start)"] = (float((t[:, 7].max() - t[:, 0].min()) / 1e3),) * 2
         return out
