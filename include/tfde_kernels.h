@@ -222,6 +222,55 @@ size_t tfde_ps_seg_bytes(void);
 int tfde_ps_pull_multi(const void* table, int nseg, long max_n, tfde_stream_t stream);
 int tfde_ps_push_multi(const void* table, int nseg, long max_n, float lr, unsigned* step_owner, unsigned* step_out,
                        tfde_stream_t stream);
+
+/* ---- the whole training step of the reference's Keras CNN in one cooperative kernel (fused_step.cu) ---------- */
+/* Conv2D(32,3,relu) -> MaxPooling2D -> Flatten -> Dense(64,relu) -> Dense(ncls <= 16), sparse CE from logits, SGD /
+ * momentum / Adam, per-replica batch <= 64: forward, loss, backward, cross-replica gradient reduction over peer memory
+ * (world > 1) and optimizer, `nsteps` steps per launch (step s reads x + s * x_step_bytes and y + s * B).
+ * ref: distributed_with_keras.py:33-43 (model, loss, optimizer), :16,63 (the per-step all-reduce under
+ * MultiWorkerMirroredStrategy), :13 (batch 64 per worker). */
+typedef struct TfdeFusedStepDesc {
+  const void* x; const void* y;            /* uint8 or float [nsteps*B,28,28,1]; int64 labels [nsteps*B] */
+  int x_is_u8; float in_scale; long x_step_bytes;
+  int B, nsteps, ncls, opt;                /* opt: 0 SGD, 1 momentum, 2 nesterov, 3 Adam */
+  float* w; float* g; float* s1; float* s2;                      /* flat parameter / gradient / slot arenas */
+  long off_ck, off_cb, off_dk, off_db, off_hk, off_hb, n;        /* arena offsets of the 6 tensors; n = trainable floats */
+  float loss_scale; int rank; int world; int use_tc;             /* loss_scale = 1 / global batch */
+  void* hp; float* metrics; float* tails;  /* hyper-parameter block; running metric sums; per-step [loss,correct,rows,0] */
+  float* part; float* hbuf; float* cpart; float* small_block;    /* scratch, sizes from tfde_fused_step_*_floats() */
+  void* state; void* status;               /* zero-initialised words: barrier / ticket / epoch state; int[4] status */
+  unsigned long long timeout_ns;
+  void* rs[8]; void* gsum[8]; void* srecv[8]; void* flags[8];    /* world > 1: peer-mapped receive buffers */
+  void* prof;                              /* optional globaltimer stamps [169][16] */
+} TfdeFusedStepDesc;
+size_t tfde_fused_step_desc_bytes(void);
+size_t tfde_fused_step_part_floats(void);
+size_t tfde_fused_step_hbuf_floats(void);
+size_t tfde_fused_step_cpart_floats(void);
+size_t tfde_fused_step_small_floats(void);
+size_t tfde_fused_step_state_words(void);
+size_t tfde_fused_step_rs_floats(int world);
+size_t tfde_fused_step_gsum_floats(void);
+size_t tfde_fused_step_srecv_floats(int world);
+size_t tfde_fused_step_flag_words(int world);
+int tfde_fused_step_blocks(void);
+int tfde_fused_step_prof_stamps(void);
+int tfde_fused_step_occupancy(int use_tc, size_t dyn_smem);
+int tfde_fused_step(const TfdeFusedStepDesc* d, tfde_stream_t stream);
+/* End-to-end form (Keras steps_per_execution): per step one cudaMemcpyAsync of that step's pinned images and one of its
+ * labels on `copy_stream` into d->x / d->y, an event edge, one launch, `ev_done` recorded behind it.
+ * ref: the host->device feed of every batch inside Keras fit, distributed_with_keras.py:63. */
+int tfde_fused_exec(const TfdeFusedStepDesc* d, const void* host_x, const void* host_y, size_t x_bytes_per_step,
+                    size_t y_bytes_per_step, tfde_stream_t copy_stream, void* ev_copied, void* ev_done,
+                    tfde_stream_t stream);
+int tfde_event_create(void** out);
+int tfde_event_destroy(void* e);
+int tfde_event_synchronize(void* e);
+int tfde_event_query(void* e);
+/* Self-test of the TF32 tcgen05 path fed from thread-written shared memory (umma_tf32.cuh): act [64][32], W [32][64],
+ * dh [64][64] -> D1 = act.W, D2 = act^T.dh, D3 = dh.W^T. ref: the Dense(64) GEMMs of distributed_with_keras.py:37. */
+int tfde_umma_tf32_selftest(const float* act, const float* W, const float* dh, float* D1, float* D2, float* D3,
+                            int variant, tfde_stream_t stream);
 /* tfde_dense_wgrad whose epilogue also stores the tiles into the peers' all-reduce receive slots
  * (`push` is a TfdePush, gemm_fp32.cu): GEMM -> reduce-scatter in one kernel. */
 int tfde_dense_wgrad_push(const float* x, const float* dy, const float* ymask, float* dw, float* db, int M,
