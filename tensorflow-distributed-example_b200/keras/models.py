@@ -470,11 +470,13 @@ class Sequential:
             # not covered by the whole-step kernel: the steps run one after the other (each its own launch sequence /
             # graph replay); every step's loss is collected one step late so the reads overlap the next step
             losses = []
+            on_host = not x.is_cuda
             for k in range(K):
                 self.train_on_batch(x[k * B:(k + 1) * B], yy[k * B:(k + 1) * B], global_batch=gb)
-                if k > 0:
+                if k > 0 and on_host:
                     losses.append(self.last_step_loss(lag=1))
-            losses.append(self.last_step_loss())
+            if on_host:
+                losses.append(self.last_step_loss())     # device-resident inputs: nothing is read back, no sync
             self._exec_losses_prev, self._exec_losses = getattr(self, "_exec_losses", None), losses
             self._host_tail_mode = "steps"
             return
