@@ -385,6 +385,24 @@ fused_step_kernel(const FsParams p) {
   bool pending = false;                     // W > 1: the previous step's slice is reduced/updated lazily, right
   float gacc[2][4];                         //        before this step's GEMM needs it (off the critical path)
   const int tc = t >> 4, tn = t & 15;
+  float pv[4];                              // one row of this thread's 4x4 input patch (thread = (batch row, patch row))
+  auto load_patch = [&](int step, float (&v)[4]) {
+    const int b = t >> 2, row = t & 3;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = 0.f;
+    if (b < p.B) {
+      const long off = ((long)b * FS_HW + (2 * py + row)) * FS_HW + 2 * px;
+      if (p.x_is_u8) {
+        const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x) + (long)step * p.x_step_bytes + off;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = (float)__ldg(xb + j) * p.in_scale;
+      } else {
+        const float* xf = reinterpret_cast<const float*>(reinterpret_cast<const char*>(p.x) + (long)step * p.x_step_bytes) + off;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = __ldg(xf + j) * p.in_scale;
+      }
+    }
+  };
 
   for (int s = 0; s < p.nsteps; ++s) {
     const uint32_t e = epoch0 + (uint32_t)s + 1u;
@@ -420,22 +438,12 @@ fused_step_kernel(const FsParams p) {
         }
       }
       {
+        // this step's 4x4 input patches: loaded here for the first step of a launch, otherwise already in registers
+        // (requested before the wait for the previous step's completion: the HBM latency hides behind the tail)
         const int b = t >> 2, row = t & 3;
-        float v[4] = {0.f, 0.f, 0.f, 0.f};
-        if (b < p.B) {
-          const long off = ((long)b * FS_HW + (2 * py + row)) * FS_HW + 2 * px;
-          if (p.x_is_u8) {
-            const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x) + (long)s * p.x_step_bytes + off;
+        if (s == 0) load_patch(0, pv);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v[j] = (float)__ldg(xb + j) * p.in_scale;
-          } else {
-            const float* xf = reinterpret_cast<const float*>(reinterpret_cast<const char*>(p.x) + (long)s * p.x_step_bytes) + off;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) v[j] = __ldg(xf + j) * p.in_scale;
-          }
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) patch[b * PATCH_LD + row * 4 + j] = v[j];
+        for (int j = 0; j < 4; ++j) patch[b * PATCH_LD + row * 4 + j] = pv[j];
       }
       if (s == 0) {
 #pragma unroll
@@ -1005,6 +1013,7 @@ fused_step_kernel(const FsParams p) {
     // ================================ wait for the step to be complete ==================================
     FS_STAMP(10);
     if (s + 1 < p.nsteps) {
+      load_patch(s + 1, pv);               // next step's inputs: in flight while this step's tail finishes
       if (t == 0) wait_flag<false>(p, p.state + ST_DONE, e, 11, pix, 3);
       __syncthreads();
     }
