@@ -174,3 +174,41 @@ def test_whole_step_tensor_core_variant(monkeypatch, kind, bs):
     m2.train_on_batches(x[:8 * bs], y[:8 * bs], steps=8)
     for a, b in zip(mg.get_weights(), m2.get_weights()):
         assert np.array_equal(a, b)
+
+
+def test_epoch_counters_wrap_around_2_pow_32():
+    """The kernel's barrier / ticket / epoch counters only ever grow (they make the kernel replayable without host
+    resets) and are compared modulo 2^32. Start them 20 steps before the wrap and train across it: the result must be
+    bit-identical to a run that starts at zero."""
+    x, y = _data(64 * 8, seed=31)
+    ref_m, ref_l = _train("cuda", "momentum", 8, x, y, 64)          # counters start at 0
+    with Strategy(device="cuda").scope():
+        m = tf.models.build_and_compile_cnn_model(optimizer=_opt("momentum"), seed=7)
+    m.train_on_batch(x[:64], y[:64])                                 # builds the plan (epoch 1)
+    m.sync()
+    plan = m.fused_plan()
+    assert plan is not None
+    # rebuild the same model so the weights are fresh, then plant the counters: every word is a multiple of the epoch
+    with Strategy(device="cuda").scope():
+        m = tf.models.build_and_compile_cnn_model(optimizer=_opt("momentum"), seed=7)
+    m.train_on_batches(x[:64].cuda(), y[:64].cuda(), steps=1)       # epoch 1 on the new plan (its own state words)
+    m.sync()
+    plan = m.fused_plan()
+    E0 = (1 << 32) - 3                                               # 3 steps before the wrap
+    grid = 169
+    st = torch.zeros_like(plan.state, dtype=torch.int64)
+    st[0] = (E0 * 2 * grid) % (1 << 32)                              # ST_BAR
+    st[32] = (E0 * 13) % (1 << 32)                                   # ST_TICKET
+    st[64] = E0                                                      # ST_DONE
+    st[96] = E0                                                      # ST_EPOCH0
+    for g in range(13):
+        st[128 + 32 * g] = (E0 * 13) % (1 << 32)                     # ST_GROUP
+    plan.state.copy_(torch.where(st >= (1 << 31), st - (1 << 32), st).to(torch.int32))
+    m.train_on_batches(x[64:64 * 5].cuda(), y[64:64 * 5].cuda(), steps=4)   # crosses 2^32 inside one launch
+    for k in range(5, 8):
+        m.train_on_batch(x[64 * k:64 * (k + 1)], y[64 * k:64 * (k + 1)])
+    m.sync()
+    plan.check()
+    assert int(plan.state[96].item()) & 0xFFFFFFFF == (E0 + 7) % (1 << 32)
+    for a, b in zip(m.get_weights(), ref_m.get_weights()):
+        assert np.array_equal(a, b)

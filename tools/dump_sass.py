@@ -10,10 +10,10 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "tensorflow-distributed-example_b200", "_lib", "libtfde_kernels.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-KEEP = ("fused_step_kernel", "dense_bwd_skinny_kernel", "ps_push_multi_kernel", "gemm_bf16_tcgen05_kernel", "allreduce_fused_kernel", "dense_skinny_fwd_kernel", "head_fwd_bwd_kernel",
+KEEP = ("fused_step_kernel", "dense_bwd_skinny_kernel", "ps_push_multi_kernel", "smallconv_dgrad_kernelILi6", "umma_tf32_selftest", "gemm_bf16_tcgen05_kernel", "allreduce_fused_kernel", "dense_skinny_fwd_kernel", "head_fwd_bwd_kernel",
         "conv3x3c1_relu_pool", "allreduce_nvls_kernel", "gemm_bf16_tcgen05_persistent_kernel", "colstats_bf16_kernel",
-        "bn_bwd_apply_bf16_kernel", "gemm_fp32_kernel")
-N_LISTED = 12     # kernels of KEEP[:N_LISTED] get a full listing; the rest only a row in the summary
+        "bn_bwd_apply_bf16_kernel", "gemm_fp32_kernel", "smallconv", "bn_reduce_smallc")
+N_LISTED = 14     # kernels of KEEP[:N_LISTED] get a full listing; the rest only a row in the summary
 MNEMONICS = ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMAPF", "SYNCS", "LDGSTS", "UCGABAR", "LDGMC", "HMMA", "FFMA", "LDG",
              "STG", "STS", "LDS", "ATOMG", "REDG", "MEMBAR", "CCTL")
 
@@ -31,6 +31,12 @@ def main():
         clean = dem.replace("(anonymous namespace)::", "").replace("<unnamed>::", "")
         clean = re.sub(r"^void\s+", "", clean)
         short = re.sub(r"[^A-Za-z0-9_]+", "_", clean.split("(")[0]).strip("_")[:90]
+        if "fused_step_kernel" in name:      # two instantiations: exact-fp32 FFMA and TF32 tcgen05
+            short = "fused_step_kernel_tf32_tcgen05" if "Lb1" in name else "fused_step_kernel"
+        if "smallconv" in name or "bn_reduce_smallc" in name:
+            m2 = re.search(r"(smallconv_\w+?_kernel|bn_reduce_smallc_kernel)ILi?b?(\d+)", name)
+            if m2:
+                short = f"{m2.group(1)}_{m2.group(2)}"
         counts = collections.Counter()
         for line in body.splitlines():
             m = re.search(r"/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
