@@ -48,6 +48,17 @@ __device__ __forceinline__ void p_tma_load_2d(void* dst, const CUtensorMap* map,
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(p_smem_u32(dst)), "l"(map), "r"(p_smem_u32(bar)), "r"(c_inner), "r"(c_outer) : "memory");
 }
+// im2col-mode load of an NHWC activation: `pixelsPerColumn` pixels x `channelsPerPixel` channels of the tensor map,
+// starting at the base pixel (w, h, n) of the bounding box and walking W, then H, then N with the map's traversal
+// strides; (ow, oh) is the filter tap added to every pixel; out-of-image pixels are zero-filled. The box lands as
+// one 128-byte (64 bf16 channel) row per pixel, SWIZZLE_128B: the same bytes a tiled {64, rows} box would leave.
+__device__ __forceinline__ void p_tma_load_im2col(void* dst, const CUtensorMap* map, uint64_t* bar, int c, int w, int h,
+                                                  int n, int ow, int oh) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(p_smem_u32(dst)), "l"(map), "r"(p_smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)ow),
+        "h"((uint16_t)oh) : "memory");
+}
 __device__ __forceinline__ uint64_t p_smem_desc(uint32_t addr) {   // K-major, SWIZZLE_128B (see gemm_tcgen05.cu)
   return (uint64_t)((addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
@@ -91,17 +102,38 @@ struct PEpilogue {
   float* stat_sum; float* stat_sq;
 };
 
+// Convolution geometry of the implicit-GEMM modes (CONV != 0): the A operand is never materialised, the producer
+// warp fetches it from the NHWC activation with im2col-mode TMA loads.
+//   pixel grid = the positions the bounding box of the tensor map can take: [n][gh][gw], linear index = GEMM row
+//   (CONV 1, 2) or GEMM reduction index (CONV 3); base coordinate of grid position (p, q) = (p*sh - off_h, q*sw - off_w)
+struct PConv {
+  int gw, ghw;          // grid width, grid height * width
+  int sw, sh;           // traversal strides
+  int off_w, off_h;     // -lower corner (the padding seen by tap 0)
+  int kw, taps;         // filter width, KH*KW
+  int cblk;             // 64-channel blocks per tap along the reduction (CONV 1: Cin/64, CONV 2: Cout/64)
+  int cin;              // CONV 2: rows per tap of the [taps*Cin, Cout] weight matrix; CONV 3: Cin
+};
+
 // MNMAJ is a bit mask: bit 0 = A is MN-major (stored [K, M], M contiguous), bit 1 = B is MN-major (stored
 // [K, N], N contiguous); a clear bit means K-major ([M, K] / [N, K], K contiguous).
 //   0: A[M,K] B[N,K]   forward / data-gradient GEMMs with pre-transposed weights
 //   2: A[M,K] B[K,N]   forward convolution / dense with the weights exactly as Keras stores them (HWIO, (in,out))
 //   3: A[K,M] B[K,N]   filter gradient: activations [rows, Cin] and gradients [rows, Cout], reduced over rows
 // so no transposed copies of weights, activations or gradients are needed.
-template <int BN, int MNMAJ>
+// CONV selects how the A operand (and, for 2, the B operand) is addressed:
+//   0: plain GEMM, tiled tensor maps
+//   1: convolution forward, MNMAJ 2: A = im2col(x) [pixels, taps*Cin] fetched tap by tap (128 pixels x 64 channels per
+//      k-block), B = HWIO weights [taps*Cin, Cout] as stored
+//   2: data gradient of a stride-1 convolution, MNMAJ 0: A = im2col(dy) over the input grid with the mirrored padding,
+//      B = the SAME weight matrix read K-major as [taps*Cin, Cout] rows (tap mirrored: taps-1-tap), no rotated copy
+//   3: filter gradient, MNMAJ 3: A = im2col(x) MN-major (64 pixels x 64 channels per box, two boxes per 128-row
+//      tile = two (tap, channel-block) pairs), B = dy [pixels, Cout], reduced over pixels
+template <int BN, int MNMAJ, int CONV = 0>
 __global__ void __launch_bounds__(P_THREADS, 1)
 gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                                     const PEpilogue ep_in, const int K, const int tiles_m, const int tiles_n,
-                                    const int splits, float* __restrict__ ws) {
+                                    const int splits, float* __restrict__ ws, const PConv cv) {
   constexpr uint32_t A_BYTES = P_BM * P_BK * 2;
   constexpr uint32_t B_BYTES = BN * P_BK * 2;
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
@@ -153,12 +185,41 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
         const int tile = item / splits, z = item % splits;
         const int m0 = (tile / tiles_n) * P_BM, n0 = (tile % tiles_n) * BN;
         const int kb_end = min(num_k, (z + 1) * kb_per);
+        // implicit GEMM: where this tile starts on the pixel grid (CONV 1, 2) / which (tap, channel block) pairs its
+        // two 64-row halves are (CONV 3)
+        int img = 0, bw = 0, bh = 0, tap3[2] = {0, 0}, ch3[2] = {0, 0}, nbox3 = 0;
+        if (CONV == 1 || CONV == 2) {
+          img = m0 / cv.ghw;
+          const int rem = m0 - img * cv.ghw, p = rem / cv.gw;
+          bh = p * cv.sh - cv.off_h; bw = (rem - p * cv.gw) * cv.sw - cv.off_w;
+        }
+        if (CONV == 3) {
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const int mi = m0 + j * 64;
+            if (mi < ep_in.M) { tap3[j] = mi / cv.cin; ch3[j] = mi - tap3[j] * cv.cin; nbox3 = j + 1; }
+          }
+        }
         for (int kb = z * kb_per; kb < kb_end; ++kb, ++it) {
           const uint32_t s = it % STAGES, ph = (it / STAGES) & 1u;
           p_mbar_wait(&empty_bar[s], ph ^ 1u);
-          p_mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+          p_mbar_expect_tx(&full_bar[s], CONV == 3 ? (uint32_t)nbox3 * 8192u + B_BYTES : STAGE_BYTES);
           uint8_t* a_dst = smem + (size_t)s * STAGE_BYTES;
-          if (MNMAJ & 1) {
+          if (CONV == 1 || CONV == 2) {
+            const int tap = kb / cv.cblk, cb = kb - tap * cv.cblk, r = tap / cv.kw;
+            p_tma_load_im2col(a_dst, &tmA, &full_bar[s], cb * 64, bw, bh, img, tap - r * cv.kw, r);
+            if (CONV == 2) {
+              p_tma_load_2d(a_dst + A_BYTES, &tmB, &full_bar[s], cb * 64, (cv.taps - 1 - tap) * cv.cin + n0);
+              continue;
+            }
+          } else if (CONV == 3) {
+            const int pix = kb * P_BK, n3 = pix / cv.ghw, rem = pix - n3 * cv.ghw, p = rem / cv.gw;
+            const int h3 = p * cv.sh - cv.off_h, w3 = (rem - p * cv.gw) * cv.sw - cv.off_w;
+            for (int j = 0; j < nbox3; ++j) {
+              const int r = tap3[j] / cv.kw;
+              p_tma_load_im2col(a_dst + j * 8192, &tmA, &full_bar[s], ch3[j], w3, h3, n3, tap3[j] - r * cv.kw, r);
+            }
+          } else if (MNMAJ & 1) {
 #pragma unroll
             for (int j = 0; j < P_BM / 64; ++j) p_tma_load_2d(a_dst + j * 8192, &tmA, &full_bar[s], m0 + j * 64, kb * P_BK);
           } else {
@@ -504,13 +565,13 @@ int p_make_map_ld(CUtensorMap* map, const void* ptr, long rows, long cols, long 
   return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
 }
 
-template <int BN, int MNMAJ>
+template <int BN, int MNMAJ, int CONV = 0>
 int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, int M, int N, int K, float* ws,
-             size_t ws_bytes, cudaStream_t stream) {
+             size_t ws_bytes, cudaStream_t stream, const PConv& cv = PConv{}) {
   constexpr int STAGES = (BN == 256) ? 4 : 6;
   constexpr size_t smem = (size_t)STAGES * (P_BM * P_BK * 2 + BN * P_BK * 2) + 4 * 32 * P_STG_PITCH + 1024;
   static size_t configured[TFDE_MAX_DEVICES] = {};
-  { const cudaError_t e = tfde_ensure_dyn_smem(gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ>, smem, configured); if (e != cudaSuccess) return (int)e; }
+  { const cudaError_t e = tfde_ensure_dyn_smem(gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ, CONV>, smem, configured); if (e != cudaSuccess) return (int)e; }
   const int tiles_m = (M + P_BM - 1) / P_BM, tiles_n = (N + BN - 1) / BN;
   const int tiles = tiles_m * tiles_n;
   const int num_k = (K + P_BK - 1) / P_BK;
@@ -529,8 +590,8 @@ int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, 
   }
   const int items = tiles * splits;
   const int grid = items < 148 ? items : 148;
-  tfde_launch(gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ>, dim3(grid), dim3(P_THREADS), smem, stream, ta, tb, ep, K, tiles_m,
-              tiles_n, splits, ws);
+  tfde_launch(gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ, CONV>, dim3(grid), dim3(P_THREADS), smem, stream, ta, tb, ep, K,
+              tiles_m, tiles_n, splits, ws, cv);
   if (splits > 1) {
     const long total4 = (long)M * N / 4;
     const bool vec = (N & 3) == 0 && (ep.ldc & 3) == 0;
@@ -643,4 +704,139 @@ TFDE_API int tfde_gemm_bf16_nn_stats_persistent(const void* A, const void* B, vo
   if (BN == 64) return p_launch<64, 2>(ta, tb, ep, M, N, K, nullptr, 0, stream);
   if (BN == 128) return p_launch<128, 2>(ta, tb, ep, M, N, K, nullptr, 0, stream);
   return p_launch<256, 2>(ta, tb, ep, M, N, K, nullptr, 0, stream);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Implicit-GEMM convolutions (reference layers: /root/reference/mnist_keras_distributed.py:83-98 Conv2D,
+// /root/reference/distributed_with_keras.py:34): the A operand is fetched from the NHWC bf16 activation by
+// im2col-mode TMA loads (cuTensorMapEncodeIm2col), nothing is gathered into HBM first.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+
+typedef CUresult (*PEncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*,
+                                    CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                    CUtensorMapFloatOOBfill);
+PEncodeIm2colFn p_encode_im2col = nullptr;
+
+int p_resolve_encode_im2col() {
+  std::lock_guard<std::mutex> lock(p_encode_mu);
+  if (p_encode_im2col == nullptr) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    const cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &fn, cudaEnableDefault, &q);
+    if (e != cudaSuccess) return (int)e;
+    if (q != cudaDriverEntryPointSuccess || fn == nullptr) return (int)cudaErrorNotSupported;
+    p_encode_im2col = reinterpret_cast<PEncodeIm2colFn>(fn);
+  }
+  return 0;
+}
+
+// NHWC bf16 tensor [B, H, W, C] as an im2col map: boxes of `pixels` x 64 channels; the bounding box of base pixels
+// is [lo, dim + hi) per spatial dimension, walked with strides (sw, sh).
+int p_make_im2col_map(CUtensorMap* map, const void* ptr, int B, int H, int W, int C, int lo_w, int lo_h, int hi_w,
+                      int hi_h, int sw, int sh, int pixels) {
+  const int rc = p_resolve_encode_im2col();
+  if (rc != 0) return rc;
+  if (lo_w < -128 || lo_w > 127 || lo_h < -128 || lo_h > 127 || hi_w < -128 || hi_w > 127 || hi_h < -128 || hi_h > 127 ||
+      sw < 1 || sw > 8 || sh < 1 || sh > 8 || pixels < 1 || pixels > 1024)
+    return TFDE_ERR_INVALID;
+  cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+  cuuint64_t gstride[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  int lower[2] = {lo_w, lo_h}, upper[2] = {hi_w, hi_h};
+  cuuint32_t estr[4] = {1, (cuuint32_t)sw, (cuuint32_t)sh, 1};
+  const CUresult r = p_encode_im2col(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), gdim, gstride, lower,
+                                     upper, 64, (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return (int)cudaErrorInvalidValue;
+  // im2col maps of tensors smaller than 128 KB: drivers up to 13.1 set a descriptor bit that makes the load misbehave
+  // (the fix-up CUTLASS applies in cute/atom/copy_traits_sm90_im2col.hpp)
+  int drv = 0;
+  if (cudaDriverGetVersion(&drv) == cudaSuccess && drv <= 13010 && (size_t)B * H * W * C * 2 < 131072)
+    reinterpret_cast<uint64_t*>(map)[1] &= ~(1ull << 21);
+  return 0;
+}
+
+bool p_conv_ok(int B, int H, int W, int C, int KH, int KW, int Ho, int Wo, int Cout) {
+  return B > 0 && H > 0 && W > 0 && Ho > 0 && Wo > 0 && KH > 0 && KW > 0 && KH * KW > 1 && KH <= 16 && KW <= 16 && C > 0 &&
+         Cout > 0 && (C & 63) == 0 && (Cout & 63) == 0 && (long)B * Ho * Wo < (1L << 31) && (long)B * H * W < (1L << 31);
+}
+
+}  // namespace
+
+// 1 when the three implicit-GEMM entry points below take this convolution (dgrad additionally needs stride 1).
+TFDE_API int tfde_conv_igemm_supported(int B, int H, int W, int C, int KH, int KW, int Ho, int Wo, int Cout) {
+  return p_conv_ok(B, H, W, C, KH, KW, Ho, Wo, Cout) ? 1 : 0;
+}
+
+// y[B,Ho,Wo,Cout] (bf16) = conv(x[B,H,W,C] bf16, w[KH,KW,C,Cout] bf16 as stored) + bias; pads = (top, bottom, left,
+// right). stat_sum / stat_sq (optional, both or none): fused batch-norm partial statistics, [ceil(M/32)][Cout].
+TFDE_API int tfde_conv_igemm_fwd(const void* x, const void* w16, void* y, const float* bias, int B, int H, int W, int C,
+                                 int KH, int KW, int Ho, int Wo, int sh, int sw, int pt, int pb, int pl, int pr, int Cout,
+                                 float* stat_sum, float* stat_sq, float* ws, size_t ws_bytes, cudaStream_t stream) {
+  if (!x || !w16 || !y || !p_conv_ok(B, H, W, C, KH, KW, Ho, Wo, Cout) || ((stat_sum == nullptr) != (stat_sq == nullptr)))
+    return TFDE_ERR_INVALID;
+  if ((H + pt + pb - KH) / sh + 1 != Ho || (W + pl + pr - KW) / sw + 1 != Wo) return TFDE_ERR_INVALID;
+  if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(w16) & 15) || (reinterpret_cast<uintptr_t>(y) & 15))
+    return TFDE_ERR_INVALID;
+  const int M = B * Ho * Wo, N = Cout, K = KH * KW * C;
+  const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+  CUtensorMap ta, tb;
+  // base pixels [-pad, dim + pad_far - (k-1)): exactly Ho x Wo positions at the traversal strides
+  int rc = p_make_im2col_map(&ta, x, B, H, W, C, -pl, -pt, pr - (KW - 1), pb - (KH - 1), sw, sh, P_BM);
+  if (rc != 0) return rc;
+  rc = p_make_map_ld(&tb, w16, K, N, N, P_BK, 64);
+  if (rc != 0) return rc;
+  PEpilogue ep{nullptr, (__nv_bfloat16*)y, N, bias, 0, M, N, stat_sum, stat_sq};
+  const PConv cv{Wo, Ho * Wo, sw, sh, pl, pt, KW, KH * KW, C / 64, C};
+  if (stat_sum != nullptr) { ws = nullptr; ws_bytes = 0; }     // partial tiles have no statistics
+  if (BN == 64) return p_launch<64, 2, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
+  if (BN == 128) return p_launch<128, 2, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
+  return p_launch<256, 2, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
+}
+
+// dx[B,H,W,C] (bf16) of a STRIDE-1 convolution: a convolution of dy[B,Ho,Wo,Cout] with the mirrored filter and the
+// complementary padding; the weights are the forward pass's bf16 copy, addressed tap-mirrored and K-major.
+TFDE_API int tfde_conv_igemm_dgrad(const void* dy, const void* w16, void* dx, int B, int H, int W, int C, int KH, int KW,
+                                   int Ho, int Wo, int pt, int pl, int Cout, float* ws, size_t ws_bytes,
+                                   cudaStream_t stream) {
+  if (!dy || !w16 || !dx || !p_conv_ok(B, H, W, C, KH, KW, Ho, Wo, Cout)) return TFDE_ERR_INVALID;
+  if ((reinterpret_cast<uintptr_t>(dy) & 15) || (reinterpret_cast<uintptr_t>(w16) & 15) || (reinterpret_cast<uintptr_t>(dx) & 15))
+    return TFDE_ERR_INVALID;
+  const int M = B * H * W, N = C, K = KH * KW * Cout;
+  const int BN = (N % 256 == 0) ? 256 : ((N % 128 == 0) ? 128 : 64);   // a B tile stays inside one tap's Cin rows
+  const int lo_w = -(KW - 1 - pl), lo_h = -(KH - 1 - pt);
+  CUtensorMap ta, tb;
+  // W positions of the base pixel: Wo + hi - lo = W
+  int rc = p_make_im2col_map(&ta, dy, B, Ho, Wo, Cout, lo_w, lo_h, W - Wo + lo_w, H - Ho + lo_h, 1, 1, P_BM);
+  if (rc != 0) return rc;
+  rc = p_make_map(&tb, w16, (long)KH * KW * C, Cout, BN);
+  if (rc != 0) return rc;
+  PEpilogue ep{nullptr, (__nv_bfloat16*)dx, N, nullptr, 0, M, N};
+  const PConv cv{W, H * W, 1, 1, -lo_w, -lo_h, KW, KH * KW, Cout / 64, C};
+  if (BN == 64) return p_launch<64, 0, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
+  if (BN == 128) return p_launch<128, 0, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
+  return p_launch<256, 0, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
+}
+
+// dw[KH,KW,C,Cout] (fp32) = im2col(x)^T . dy, reduced over the B*Ho*Wo output pixels (split-K through ws).
+TFDE_API int tfde_conv_igemm_wgrad(const void* x, const void* dy, float* dw, int B, int H, int W, int C, int KH, int KW,
+                                   int Ho, int Wo, int sh, int sw, int pt, int pb, int pl, int pr, int Cout, float* ws,
+                                   size_t ws_bytes, cudaStream_t stream) {
+  if (!x || !dy || !dw || !p_conv_ok(B, H, W, C, KH, KW, Ho, Wo, Cout)) return TFDE_ERR_INVALID;
+  if ((H + pt + pb - KH) / sh + 1 != Ho || (W + pl + pr - KW) / sw + 1 != Wo) return TFDE_ERR_INVALID;
+  if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(dy) & 15)) return TFDE_ERR_INVALID;
+  const int M = KH * KW * C, N = Cout, K = B * Ho * Wo;
+  const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+  CUtensorMap ta, tb;
+  int rc = p_make_im2col_map(&ta, x, B, H, W, C, -pl, -pt, pr - (KW - 1), pb - (KH - 1), sw, sh, P_BK);
+  if (rc != 0) return rc;
+  rc = p_make_map_ld(&tb, dy, K, N, N, P_BK, 64);
+  if (rc != 0) return rc;
+  PEpilogue ep{dw, nullptr, N, nullptr, 0, M, N};
+  const PConv cv{Wo, Ho * Wo, sw, sh, pl, pt, KW, KH * KW, 1, C};
+  if (BN == 64) return p_launch<64, 3, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
+  if (BN == 128) return p_launch<128, 3, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
+  return p_launch<256, 3, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
 }

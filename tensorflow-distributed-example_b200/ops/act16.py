@@ -19,6 +19,7 @@ from . import native, tensorcore
 from . import reference as ref
 from .mixed import cast_bf16_masked
 from .mixed_conv import _scratch, _geom, _r8
+from . import conv_igemm
 
 c_p, c_i, c_l, c_f, c_z = native.c_p, native.c_i, native.c_l, native.c_f, native.c_z
 BF = torch.bfloat16
@@ -308,6 +309,8 @@ def a_operand_shape(x_shape, w_shape, stride, ho, wo, x_is_bf16=True):
     kh, kw = w_shape[0], w_shape[1]
     if x_is_bf16 and kh == 1 and kw == 1 and tuple(stride) == (1, 1):
         return None
+    if x_is_bf16 and conv_igemm.ENABLED and conv_igemm.supported(x_shape, w_shape, ho, wo):
+        return None                                    # implicit GEMM: the operand is fetched by im2col-mode TMA
     return (b * ho * wo, _r8(kh * kw * c))
 
 
@@ -361,8 +364,13 @@ def conv2d_fwd(x, w, bias=None, stride=(1, 1), pads=(0, 0, 0, 0), out=None, a_ca
         return y
     L = native.load()
     M, kc = b * ho * wo, kh * kw * c
-    a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "A", cache=a_cache)
     y = out if out is not None else torch.empty((b, ho, wo, cout), dtype=BF, device=x.device)
+    if conv_igemm.eligible(x, w.shape, ho, wo):
+        # implicit GEMM: A tiles come straight from the activation (im2col-mode TMA), B is the bf16 weight copy
+        wb = w16 if w16 is not None else cast_bf16_masked(w.reshape(kc, cout), None,
+                                                          out=_scratch(x.device, "B", kc * cout).view(kc, cout))
+        return conv_igemm.fwd(x, wb.reshape(kh, kw, c, cout), bias, stride, pads, y, bn_partials)
+    a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "A", cache=a_cache)
     if _FWD_NN:
         # weights exactly as Keras stores them (HWIO = [kc, cout] row-major): the GEMM reads them MN-major, the
         # only per-step weight work is a flat fp32 -> bf16 cast (padded im2col columns meet zero-filled rows)
@@ -408,9 +416,22 @@ def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bia
     M, kc, min_, kd = b * ho * wo, kh * kw * c, b * h * wd, kh * kw * cout
     dy2 = dy.reshape(M, cout)
     # filter gradient: dW[kc, cout] = A^T[kc, M] . dy^T[cout, M]^T (both K-major after a bf16 transpose)
-    a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "C", cache=a_cache, reuse=a_cache is not None)
     dw = out_dw if out_dw is not None else torch.empty(tuple(w.shape), dtype=torch.float32, device=dev)
-    if _WGRAD_NT and kc % 8 == 0:
+    igemm = conv_igemm.eligible(x, w.shape, ho, wo) and dy.dtype == BF and dy.is_contiguous()
+    if igemm:
+        # implicit GEMM: im2col(x) tiles fetched MN-major by TMA, dy as it is, reduced over the output pixels
+        if side_stream is not None and need_dx:
+            side_stream.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side_stream):
+                conv_igemm.wgrad(x, dy, w.shape, stride, pads, dw)
+        else:
+            conv_igemm.wgrad(x, dy, w.shape, stride, pads, dw)
+        a = kp = None
+    else:
+        a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "C", cache=a_cache, reuse=a_cache is not None)
+    if igemm:
+        pass
+    elif _WGRAD_NT and kc % 8 == 0:
         # operands as the forward pass left them: A[M, kc] and dy[M, cout], reduced over rows -> the tcgen05
         # GEMM reads them MN-major, no transposed copies
         a_nt = a[:, :kc] if kp != kc else a
@@ -449,6 +470,13 @@ def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bia
             tensorcore.gemm_bf16_tn(dy2, wr, None, False, BF, out=gc)
             native.check(L.tfde_strided_scatter_b2b(gc.data_ptr(), dx.data_ptr(), b, h, wd, c, ho, wo, stride[0],
                                                     stride[1], native.stream_ptr()), "strided_scatter_b2b")
+            return dx, dw, db
+        if igemm and conv_igemm.dgrad_eligible(stride):
+            # a stride-1 data gradient is a convolution of dy with the mirrored filter: same kernel, the forward
+            # pass's bf16 weights addressed tap-mirrored (no rotated copy, no gathered operand)
+            wb = w16 if w16 is not None else cast_bf16_masked(w.reshape(kc, cout), None,
+                                                              out=_scratch(dev, "B", kc * cout).view(kc, cout))
+            conv_igemm.dgrad(dy, wb.reshape(kh, kw, c, cout), pads, dx)
             return dx, dw, db
         if kh == 1 and kw == 1 and tuple(stride) == (1, 1):
             ga = dy2                                                     # Min == M: dy IS the operand
