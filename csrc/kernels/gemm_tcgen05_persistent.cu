@@ -13,6 +13,7 @@
 #include "common.cuh"
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cstdlib>
 #include <mutex>
 
 namespace {
@@ -22,6 +23,7 @@ constexpr int P_BK = 64;
 constexpr int P_THREADS = 192;
 constexpr int P_UMMA_K = 16;
 constexpr int P_STG_PITCH = 144;   // bytes per staged epilogue row: 128 of payload + 16 of padding
+constexpr int P_EPI_BYTES = 4 * 2 * 32 * 128;   // epilogue staging: 4 warps x 2 TMA-store slabs (>= 4 x 32 x P_STG_PITCH)
 
 __device__ __forceinline__ uint32_t p_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void p_mbar_init(uint64_t* bar, uint32_t count) {
@@ -58,6 +60,14 @@ __device__ __forceinline__ void p_tma_load_im2col(void* dst, const CUtensorMap* 
       "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
       ::"r"(p_smem_u32(dst)), "l"(map), "r"(p_smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)ow),
         "h"((uint16_t)oh) : "memory");
+}
+// TMA store of one staged {64 x bf16 = 128 B, 32 rows} slab (SWIZZLE_128B in shared memory) into the output tensor;
+// rows past the tensor's end are clipped by the tensor map. Bulk-group completion: wait_group.read N = the shared
+// memory of all but the N newest groups may be overwritten.
+__device__ __forceinline__ void p_tma_store_2d(const CUtensorMap* map, const void* src, int c_inner, int c_outer) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(map), "r"(p_smem_u32(src)), "r"(c_inner), "r"(c_outer) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
 __device__ __forceinline__ uint64_t p_smem_desc(uint32_t addr) {   // K-major, SWIZZLE_128B (see gemm_tcgen05.cu)
   return (uint64_t)((addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
@@ -100,6 +110,9 @@ struct PEpilogue {
   // column sums / sums of squares of the ROUNDED outputs, [ceil(M/32)][N] each -- the consumer of a
   // convolution's output is a batch-norm whose first pass would otherwise re-read the whole tensor
   float* stat_sum; float* stat_sq;
+  // bf16 output written by TMA stores (tmC describes c_bf16 as [M, N] with 128-byte x 32-row boxes): the epilogue
+  // warps only fill swizzled shared-memory slabs, the copy engine moves them out while the next slab is converted
+  int tma_store;
 };
 
 // Convolution geometry of the implicit-GEMM modes (CONV != 0): the A operand is never materialised, the producer
@@ -132,8 +145,9 @@ struct PConv {
 template <int BN, int MNMAJ, int CONV = 0>
 __global__ void __launch_bounds__(P_THREADS, 1)
 gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                                    const PEpilogue ep_in, const int K, const int tiles_m, const int tiles_n,
-                                    const int splits, float* __restrict__ ws, const PConv cv) {
+                                    const __grid_constant__ CUtensorMap tmC, const PEpilogue ep_in, const int K,
+                                    const int tiles_m, const int tiles_n, const int splits, float* __restrict__ ws,
+                                    const PConv cv) {
   constexpr uint32_t A_BYTES = P_BM * P_BK * 2;
   constexpr uint32_t B_BYTES = BN * P_BK * 2;
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
@@ -141,7 +155,9 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
   constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;      // 128 / 256 / 512: powers of two
   extern __shared__ __align__(1024) uint8_t p_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p_smem_raw) + 1023) & ~(uintptr_t)1023);
-  float* epi_tiles = reinterpret_cast<float*>(smem + (size_t)STAGES * STAGE_BYTES);   // 4 warps x 32x33 floats
+  // epilogue staging: 4 warps x 32 rows x 144 bytes (padded, coalesced-store path) or 4 warps x 2 buffers x 32 rows x
+  // 128 bytes (swizzled, TMA-store path); P_EPI_BYTES covers the larger
+  float* epi_tiles = reinterpret_cast<float*>(smem + (size_t)STAGES * STAGE_BYTES);
   __shared__ __align__(8) uint64_t full_bar[STAGES];
   __shared__ __align__(8) uint64_t empty_bar[STAGES];
   __shared__ __align__(8) uint64_t tmem_full[2];
@@ -265,7 +281,8 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
     }
   } else {
     const int q = warp & 3;
-    uint32_t tl = 0;
+    uint32_t tl = 0, slab = 0;                          // slab: TMA-store slabs issued by this warp (buffer = slab & 1)
+    const bool tma_out = ep_in.tma_store != 0 && splits == 1 && ep_in.c_bf16 != nullptr && ep_in.c_f32 == nullptr;
     for (int item = blockIdx.x; item < num_tiles; item += gridDim.x, ++tl) {
       const int tile = item / splits, z = item % splits;
       const uint32_t acc = tl & 1u, aph = (tl >> 1) & 1u;
@@ -285,12 +302,17 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
       // every store instruction covers 4 complete 128-byte lines.
       int c_done = 0;
       if (((ep.c_f32 == nullptr) != (ep.c_bf16 == nullptr)) && (ep.ldc & 7) == 0) {
-        uint8_t* stg = reinterpret_cast<uint8_t*>(epi_tiles) + q * (32 * P_STG_PITCH);
+        uint8_t* stg = reinterpret_cast<uint8_t*>(epi_tiles) + (tma_out ? q * 8192 : q * (32 * P_STG_PITCH));
         const bool out16 = ep.c_bf16 != nullptr;
         const int pass = out16 ? 64 : 32;                       // columns per 128-byte row slab
 #pragma unroll 1
         for (int c0 = 0; c0 + pass <= BN && n0 + c0 + pass <= ep.N; c0 += pass) {
           const int nbase = n0 + c0;
+          uint8_t* sb = stg + (tma_out ? (slab & 1u) * 4096u : 0u);
+          if (tma_out) {                                   // the store that last used this buffer has read it
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            __syncwarp();
+          }
 #pragma unroll 1
           for (int h = 0; h * 32 < pass; ++h) {
             uint32_t r[32];
@@ -303,7 +325,17 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
               v[j] = ep.relu ? fmaxf(x, 0.f) : x;
             }
             uint4* srow = reinterpret_cast<uint4*>(stg + lane * P_STG_PITCH);
-            if (out16) {
+            if (tma_out) {                                 // 128-byte rows, 16-byte chunk c of row r at c ^ (r & 7)
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                uint4 o;
+                __nv_bfloat162 p0 = __floats2bfloat162_rn(v[j], v[j + 1]), p1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+                __nv_bfloat162 p2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]), p3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
+                o.x = *reinterpret_cast<uint32_t*>(&p0); o.y = *reinterpret_cast<uint32_t*>(&p1);
+                o.z = *reinterpret_cast<uint32_t*>(&p2); o.w = *reinterpret_cast<uint32_t*>(&p3);
+                *reinterpret_cast<uint4*>(sb + lane * 128 + (((h * 4 + (j >> 3)) ^ (lane & 7)) << 4)) = o;
+              }
+            } else if (out16) {
 #pragma unroll
               for (int j = 0; j < 32; j += 8) {
                 uint4 o;
@@ -320,6 +352,7 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
                                           __float_as_uint(v[j + 3]));
             }
           }
+          if (tma_out) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
           __syncwarp();
           if (ep.stat_sum != nullptr && out16) {
             // fused batch-norm statistics: lane owns columns 2*lane, 2*lane+1 of the 64-column slab and walks
@@ -329,7 +362,9 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
 #pragma unroll 8
             for (int rr = 0; rr < 32; ++rr) {
               if (rr < nrows) {
-                const uint32_t pr = *reinterpret_cast<const uint32_t*>(stg + rr * P_STG_PITCH + lane * 4);
+                const uint32_t pr = tma_out
+                    ? *reinterpret_cast<const uint32_t*>(sb + rr * 128 + (((lane >> 2) ^ (rr & 7)) << 4) + (lane & 3) * 4)
+                    : *reinterpret_cast<const uint32_t*>(stg + rr * P_STG_PITCH + lane * 4);
                 const float a = __uint_as_float(pr << 16), b = __uint_as_float(pr & 0xffff0000u);
                 s0 += a; s1 += b; q0 = fmaf(a, a, q0); q1 = fmaf(b, b, q1);
               }
@@ -339,6 +374,12 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
               *reinterpret_cast<float2*>(ep.stat_sum + o) = make_float2(s0, s1);
               *reinterpret_cast<float2*>(ep.stat_sq + o) = make_float2(q0, q1);
             }
+          }
+          if (tma_out) {
+            if (lane == 0 && row0 < ep.M) p_tma_store_2d(&tmC, sb, nbase, row0);
+            if (row0 < ep.M) ++slab;
+            c_done = c0 + pass;
+            continue;
           }
           uint8_t* gbase = out16 ? reinterpret_cast<uint8_t*>(ep.c_bf16 + nbase) : reinterpret_cast<uint8_t*>(ep.c_f32 + nbase);
           const size_t gpitch = (size_t)ep.ldc * (out16 ? 2 : 4);
@@ -408,6 +449,7 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
     }
   }
 
+  if (warp >= 2 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // TMA stores have landed
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 1) {
@@ -565,11 +607,28 @@ int p_make_map_ld(CUtensorMap* map, const void* ptr, long rows, long cols, long 
   return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
 }
 
+// TMA-store epilogue (bf16-only output in whole 64-column slabs): build the output map, set ep.tma_store.
+// TFDE_TMA_STORE=0 keeps the coalesced-store epilogue.
+bool p_tma_store_wanted() {
+  static const bool on = [] { const char* e = getenv("TFDE_TMA_STORE"); return e == nullptr || e[0] != '0'; }();
+  return on;
+}
+int p_prepare_store(PEpilogue& ep, CUtensorMap* tc) {
+  ep.tma_store = 0;
+  if (!p_tma_store_wanted() || ep.c_bf16 == nullptr || ep.c_f32 != nullptr || (ep.N & 63) || (ep.ldc & 7) ||
+      (reinterpret_cast<uintptr_t>(ep.c_bf16) & 15))
+    return 0;
+  const int rc = p_make_map_ld(tc, ep.c_bf16, ep.M, ep.N, ep.ldc, 32, 64);
+  if (rc != 0) return rc;
+  ep.tma_store = 1;
+  return 0;
+}
+
 template <int BN, int MNMAJ, int CONV = 0>
 int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, int M, int N, int K, float* ws,
-             size_t ws_bytes, cudaStream_t stream, const PConv& cv = PConv{}) {
+             size_t ws_bytes, cudaStream_t stream, const PConv& cv = PConv{}, const CUtensorMap* tc = nullptr) {
   constexpr int STAGES = (BN == 256) ? 4 : 6;
-  constexpr size_t smem = (size_t)STAGES * (P_BM * P_BK * 2 + BN * P_BK * 2) + 4 * 32 * P_STG_PITCH + 1024;
+  constexpr size_t smem = (size_t)STAGES * (P_BM * P_BK * 2 + BN * P_BK * 2) + P_EPI_BYTES + 1024;
   static size_t configured[TFDE_MAX_DEVICES] = {};
   { const cudaError_t e = tfde_ensure_dyn_smem(gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ, CONV>, smem, configured); if (e != cudaSuccess) return (int)e; }
   const int tiles_m = (M + P_BM - 1) / P_BM, tiles_n = (N + BN - 1) / BN;
@@ -579,19 +638,27 @@ int p_launch(const CUtensorMap& ta, const CUtensorMap& tb, const PEpilogue& ep, 
   // gradient GEMMs of a convolution: output [KH*KW*Cin, Cout], reduction over B*Ho*Wo)
   int splits = 1;
   if (ws != nullptr && tiles < 148 && num_k >= 8) {
-    splits = (148 + tiles - 1) / tiles;
-    if (splits > num_k / 4) splits = num_k / 4;
-    if (splits > 64) splits = 64;
+    // choose the split count by a cost model in k-block units: waves of 148 CTAs x (k-blocks + epilogue) per item,
+    // plus the second kernel that adds the partials. (A plain ceil(148 / tiles) leaves 150..216 items for the
+    // filter-gradient shapes of a ResNet: a second wave for a handful of CTAs, twice the time.)
     const size_t per = (size_t)M * N * sizeof(float);
-    if (per * (size_t)splits > ws_bytes) splits = (int)(ws_bytes / per);
-    if (splits < 1) splits = 1;
-    const int kb_per = (num_k + splits - 1) / splits;
-    splits = (num_k + kb_per - 1) / kb_per;          // no empty split
+    int smax = num_k / 4;
+    if (smax > 148) smax = 148;
+    if ((size_t)smax * per > ws_bytes) smax = (int)(ws_bytes / per);
+    double best = 1e30;
+    for (int s = 1; s <= smax; ++s) {
+      const int kb_per = (num_k + s - 1) / s;
+      const int s_eff = (num_k + kb_per - 1) / kb_per;            // no empty split
+      if (s_eff != s) continue;
+      const int waves = (tiles * s + 147) / 148;
+      const double cost = (double)waves * (kb_per + BN / 32) + (s > 1 ? 4.0 + (double)s * (double)per / 2.0e6 : 0.0);
+      if (cost < best) { best = cost; splits = s; }
+    }
   }
   const int items = tiles * splits;
   const int grid = items < 148 ? items : 148;
-  tfde_launch(gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ, CONV>, dim3(grid), dim3(P_THREADS), smem, stream, ta, tb, ep, K,
-              tiles_m, tiles_n, splits, ws, cv);
+  tfde_launch(gemm_bf16_tcgen05_persistent_kernel<BN, MNMAJ, CONV>, dim3(grid), dim3(P_THREADS), smem, stream, ta, tb,
+              tc != nullptr ? *tc : ta, ep, K, tiles_m, tiles_n, splits, ws, cv);
   if (splits > 1) {
     const long total4 = (long)M * N / 4;
     const bool vec = (N & 3) == 0 && (ep.ldc & 3) == 0;
@@ -629,9 +696,13 @@ TFDE_API int tfde_gemm_bf16_tn_persistent(const void* A, const void* B, float* c
   rc = p_make_map(&tb, B, N, K, BN);
   if (rc != 0) return rc;
   PEpilogue ep{c_f32, (__nv_bfloat16*)c_bf16, ldc, bias, relu, M, N};
-  if (BN == 64) return p_launch<64, 0>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
-  if (BN == 128) return p_launch<128, 0>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
-  return p_launch<256, 0>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  CUtensorMap tc;
+  rc = p_prepare_store(ep, &tc);
+  if (rc != 0) return rc;
+  const CUtensorMap* tcp = ep.tma_store ? &tc : nullptr;
+  if (BN == 64) return p_launch<64, 0>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, PConv{}, tcp);
+  if (BN == 128) return p_launch<128, 0>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, PConv{}, tcp);
+  return p_launch<256, 0>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, PConv{}, tcp);
 }
 
 // C[M,N] = A[K,M]^T . B[K,N]: both operands "MN-major" (row-major with the REDUCED dimension as rows), which
@@ -652,9 +723,13 @@ TFDE_API int tfde_gemm_bf16_nt_persistent(const void* A, const void* B, float* c
   rc = p_make_map_ld(&tb, B, K, N, ldb, P_BK, 64);
   if (rc != 0) return rc;
   PEpilogue ep{c_f32, (__nv_bfloat16*)c_bf16, ldc, nullptr, 0, M, N};
-  if (BN == 64) return p_launch<64, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
-  if (BN == 128) return p_launch<128, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
-  return p_launch<256, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  CUtensorMap tc;
+  rc = p_prepare_store(ep, &tc);
+  if (rc != 0) return rc;
+  const CUtensorMap* tcp = ep.tma_store ? &tc : nullptr;
+  if (BN == 64) return p_launch<64, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, PConv{}, tcp);
+  if (BN == 128) return p_launch<128, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, PConv{}, tcp);
+  return p_launch<256, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, PConv{}, tcp);
 }
 
 // C[M,N] = act(A[M,K] . B[K,N] + bias): A K-major, B MN-major -- a convolution / dense forward with the weight
@@ -675,9 +750,13 @@ TFDE_API int tfde_gemm_bf16_nn_persistent(const void* A, const void* B, float* c
   rc = p_make_map_ld(&tb, B, kb, N, ldb, P_BK, 64);
   if (rc != 0) return rc;
   PEpilogue ep{c_f32, (__nv_bfloat16*)c_bf16, ldc, bias, relu, M, N};
-  if (BN == 64) return p_launch<64, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
-  if (BN == 128) return p_launch<128, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
-  return p_launch<256, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream);
+  CUtensorMap tc;
+  rc = p_prepare_store(ep, &tc);
+  if (rc != 0) return rc;
+  const CUtensorMap* tcp = ep.tma_store ? &tc : nullptr;
+  if (BN == 64) return p_launch<64, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, PConv{}, tcp);
+  if (BN == 128) return p_launch<128, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, PConv{}, tcp);
+  return p_launch<256, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, PConv{}, tcp);
 }
 
 // Same GEMM with bf16 output only, plus the batch-norm statistics of that output fused into the epilogue:
@@ -701,9 +780,13 @@ TFDE_API int tfde_gemm_bf16_nn_stats_persistent(const void* A, const void* B, vo
   rc = p_make_map_ld(&tb, B, kb, N, ldb, P_BK, 64);
   if (rc != 0) return rc;
   PEpilogue ep{nullptr, (__nv_bfloat16*)c_bf16, ldc, bias, 0, M, N, stat_sum, stat_sq};
-  if (BN == 64) return p_launch<64, 2>(ta, tb, ep, M, N, K, nullptr, 0, stream);
-  if (BN == 128) return p_launch<128, 2>(ta, tb, ep, M, N, K, nullptr, 0, stream);
-  return p_launch<256, 2>(ta, tb, ep, M, N, K, nullptr, 0, stream);
+  CUtensorMap tc;
+  rc = p_prepare_store(ep, &tc);
+  if (rc != 0) return rc;
+  const CUtensorMap* tcp = ep.tma_store ? &tc : nullptr;
+  if (BN == 64) return p_launch<64, 2>(ta, tb, ep, M, N, K, nullptr, 0, stream, PConv{}, tcp);
+  if (BN == 128) return p_launch<128, 2>(ta, tb, ep, M, N, K, nullptr, 0, stream, PConv{}, tcp);
+  return p_launch<256, 2>(ta, tb, ep, M, N, K, nullptr, 0, stream, PConv{}, tcp);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -791,9 +874,13 @@ TFDE_API int tfde_conv_igemm_fwd(const void* x, const void* w16, void* y, const 
   PEpilogue ep{nullptr, (__nv_bfloat16*)y, N, bias, 0, M, N, stat_sum, stat_sq};
   const PConv cv{Wo, Ho * Wo, sw, sh, pl, pt, KW, KH * KW, C / 64, C};
   if (stat_sum != nullptr) { ws = nullptr; ws_bytes = 0; }     // partial tiles have no statistics
-  if (BN == 64) return p_launch<64, 2, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
-  if (BN == 128) return p_launch<128, 2, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
-  return p_launch<256, 2, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
+  CUtensorMap tc;
+  rc = p_prepare_store(ep, &tc);
+  if (rc != 0) return rc;
+  const CUtensorMap* tcp = ep.tma_store ? &tc : nullptr;
+  if (BN == 64) return p_launch<64, 2, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv, tcp);
+  if (BN == 128) return p_launch<128, 2, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv, tcp);
+  return p_launch<256, 2, 1>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv, tcp);
 }
 
 // dx[B,H,W,C] (bf16) of a STRIDE-1 convolution: a convolution of dy[B,Ho,Wo,Cout] with the mirrored filter and the
@@ -815,9 +902,13 @@ TFDE_API int tfde_conv_igemm_dgrad(const void* dy, const void* w16, void* dx, in
   if (rc != 0) return rc;
   PEpilogue ep{nullptr, (__nv_bfloat16*)dx, N, nullptr, 0, M, N};
   const PConv cv{W, H * W, 1, 1, -lo_w, -lo_h, KW, KH * KW, Cout / 64, C};
-  if (BN == 64) return p_launch<64, 0, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
-  if (BN == 128) return p_launch<128, 0, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
-  return p_launch<256, 0, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
+  CUtensorMap tc;
+  rc = p_prepare_store(ep, &tc);
+  if (rc != 0) return rc;
+  const CUtensorMap* tcp = ep.tma_store ? &tc : nullptr;
+  if (BN == 64) return p_launch<64, 0, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv, tcp);
+  if (BN == 128) return p_launch<128, 0, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv, tcp);
+  return p_launch<256, 0, 2>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv, tcp);
 }
 
 // dw[KH,KW,C,Cout] (fp32) = im2col(x)^T . dy, reduced over the B*Ho*Wo output pixels (split-K through ws).
@@ -836,7 +927,11 @@ TFDE_API int tfde_conv_igemm_wgrad(const void* x, const void* dy, float* dw, int
   if (rc != 0) return rc;
   PEpilogue ep{dw, nullptr, N, nullptr, 0, M, N};
   const PConv cv{Wo, Ho * Wo, sw, sh, pl, pt, KW, KH * KW, 1, C};
-  if (BN == 64) return p_launch<64, 3, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
-  if (BN == 128) return p_launch<128, 3, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
-  return p_launch<256, 3, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv);
+  CUtensorMap tc;
+  rc = p_prepare_store(ep, &tc);
+  if (rc != 0) return rc;
+  const CUtensorMap* tcp = ep.tma_store ? &tc : nullptr;
+  if (BN == 64) return p_launch<64, 3, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv, tcp);
+  if (BN == 128) return p_launch<128, 3, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv, tcp);
+  return p_launch<256, 3, 3>(ta, tb, ep, M, N, K, ws, ws_bytes, stream, cv, tcp);
 }

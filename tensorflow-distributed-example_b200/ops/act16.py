@@ -444,6 +444,12 @@ def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bia
                 tensorcore.gemm_bf16_nt(a_nt, dy2, out=dw.view(kc, cout))
         else:
             tensorcore.gemm_bf16_nt(a_nt, dy2, out=dw.view(kc, cout))
+    elif _WGRAD_NT and cout % 8 == 0:
+        # kc not a multiple of 8 (the 7x7x3 stem): reduce the PADDED operand [M, kp] the same way -- rows kc..kp of
+        # the product come from the padding columns and are dropped -- instead of transposing both operands
+        dwp = _scratch(dev, "Wp", kp * cout * 2).view(torch.float32).view(kp, cout)
+        tensorcore.gemm_bf16_nt(a, dy2, out=dwp)
+        dw.view(kc, cout).copy_(dwp[:kc])
     else:
         at = _scratch(dev, "A", kc * M).view(kc, M)
         native.check(L.tfde_transpose_bf16(a.data_ptr(), at.data_ptr(), M, kc, kp, M, native.stream_ptr()),
