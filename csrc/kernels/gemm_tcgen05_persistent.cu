@@ -102,6 +102,40 @@ __device__ __forceinline__ void p_tmem_ld(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ void p_tmem_ld_nowait(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr) : "memory");
+}
+// accumulator registers (fp32 bit patterns) += bias[col + j], ReLU; both optional, warp-uniform
+__device__ __forceinline__ void p_bias_act(uint32_t (&r)[32], const float* __restrict__ bias, int col, bool has_bias,
+                                           bool relu) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    float x = __uint_as_float(r[j]);
+    if (has_bias) x += __ldg(bias + col + j);
+    if (relu) x = fmaxf(x, 0.f);
+    r[j] = __float_as_uint(x);
+  }
+}
+// 8 consecutive fp32 accumulator values -> 8 bf16 (round to nearest even) in one 16-byte chunk
+__device__ __forceinline__ uint4 p_pack8(const uint32_t (&r)[32], int j) {
+  uint4 o;
+  __nv_bfloat162 p0 = __floats2bfloat162_rn(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
+  __nv_bfloat162 p1 = __floats2bfloat162_rn(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+  __nv_bfloat162 p2 = __floats2bfloat162_rn(__uint_as_float(r[j + 4]), __uint_as_float(r[j + 5]));
+  __nv_bfloat162 p3 = __floats2bfloat162_rn(__uint_as_float(r[j + 6]), __uint_as_float(r[j + 7]));
+  o.x = *reinterpret_cast<uint32_t*>(&p0); o.y = *reinterpret_cast<uint32_t*>(&p1);
+  o.z = *reinterpret_cast<uint32_t*>(&p2); o.w = *reinterpret_cast<uint32_t*>(&p3);
+  return o;
+}
+
 struct PEpilogue {
   float* c_f32; __nv_bfloat16* c_bf16; long ldc;
   const float* bias; int relu;
@@ -313,44 +347,34 @@ gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tmA, con
             if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
             __syncwarp();
           }
-#pragma unroll 1
-          for (int h = 0; h * 32 < pass; ++h) {
+          // both 32-column TMEM loads of a bf16 slab are in flight before the one wait; bias / activation only
+          // when present (warp-uniform), then straight from the accumulator registers into packed 16-byte chunks
+          const bool has_bias = ep.bias != nullptr, relu = ep.relu != 0;
+          const uint32_t tcol = tmem_d + ((uint32_t)(q * 32) << 16) + acc * BN + (uint32_t)c0;
+          if (out16) {
+            uint32_t ra[32], rb[32];
+            p_tmem_ld_nowait(tcol, ra);
+            p_tmem_ld_nowait(tcol + 32, rb);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (has_bias || relu) {
+              p_bias_act(ra, ep.bias, nbase, has_bias, relu);
+              p_bias_act(rb, ep.bias, nbase + 32, has_bias, relu);
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              const uint4 o = c < 4 ? p_pack8(ra, c * 8) : p_pack8(rb, (c - 4) * 8);
+              if (tma_out)                                  // 128-byte rows, 16-byte chunk c of row r at c ^ (r & 7)
+                *reinterpret_cast<uint4*>(sb + lane * 128 + ((c ^ (lane & 7)) << 4)) = o;
+              else
+                *reinterpret_cast<uint4*>(stg + lane * P_STG_PITCH + c * 16) = o;
+            }
+          } else {
             uint32_t r[32];
-            p_tmem_ld(tmem_d + ((uint32_t)(q * 32) << 16) + acc * BN + (uint32_t)(c0 + h * 32), r);
-            float v[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              float x = __uint_as_float(r[j]);
-              if (ep.bias != nullptr) x += __ldg(ep.bias + nbase + h * 32 + j);
-              v[j] = ep.relu ? fmaxf(x, 0.f) : x;
-            }
+            p_tmem_ld(tcol, r);
+            if (has_bias || relu) p_bias_act(r, ep.bias, nbase, has_bias, relu);
             uint4* srow = reinterpret_cast<uint4*>(stg + lane * P_STG_PITCH);
-            if (tma_out) {                                 // 128-byte rows, 16-byte chunk c of row r at c ^ (r & 7)
 #pragma unroll
-              for (int j = 0; j < 32; j += 8) {
-                uint4 o;
-                __nv_bfloat162 p0 = __floats2bfloat162_rn(v[j], v[j + 1]), p1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
-                __nv_bfloat162 p2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]), p3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
-                o.x = *reinterpret_cast<uint32_t*>(&p0); o.y = *reinterpret_cast<uint32_t*>(&p1);
-                o.z = *reinterpret_cast<uint32_t*>(&p2); o.w = *reinterpret_cast<uint32_t*>(&p3);
-                *reinterpret_cast<uint4*>(sb + lane * 128 + (((h * 4 + (j >> 3)) ^ (lane & 7)) << 4)) = o;
-              }
-            } else if (out16) {
-#pragma unroll
-              for (int j = 0; j < 32; j += 8) {
-                uint4 o;
-                __nv_bfloat162 p0 = __floats2bfloat162_rn(v[j], v[j + 1]), p1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
-                __nv_bfloat162 p2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]), p3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
-                o.x = *reinterpret_cast<uint32_t*>(&p0); o.y = *reinterpret_cast<uint32_t*>(&p1);
-                o.z = *reinterpret_cast<uint32_t*>(&p2); o.w = *reinterpret_cast<uint32_t*>(&p3);
-                srow[h * 4 + (j >> 3)] = o;
-              }
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; j += 4)
-                srow[j >> 2] = make_uint4(__float_as_uint(v[j]), __float_as_uint(v[j + 1]), __float_as_uint(v[j + 2]),
-                                          __float_as_uint(v[j + 3]));
-            }
+            for (int j = 0; j < 32; j += 4) srow[j >> 2] = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
           }
           if (tma_out) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
           __syncwarp();
