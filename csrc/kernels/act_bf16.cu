@@ -487,6 +487,32 @@ __global__ void maxpool_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ dy, co
     int oh_lo = (hh - g.PH + g.sh) / g.sh; if (hh - g.PH + 1 <= 0) oh_lo = 0;
     int ow_lo = (ww - g.PW + g.sw) / g.sw; if (ww - g.PW + 1 <= 0) ow_lo = 0;
     const int oh_hi = min(hh / g.sh, g.Ho - 1), ow_hi = min(ww / g.sw, g.Wo - 1);
+    if (g.PH <= 2 * g.sh && g.PW <= 2 * g.sw) {
+      // at most 2 x 2 windows cover an input position (the 3x3 / stride-2 pool of the ResNet stem, 2x2 / 2 pools):
+      // all eight loads are issued before the first compare instead of one dependent pair per loop trip
+      uint2 ib[4]; uint4 dv[4]; uint32_t want[4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        const int oh = oh_lo + (a >> 1), ow = ow_lo + (a & 1);
+        const int kh = hh - oh * g.sh, kw = ww - ow * g.sw;
+        const bool ok = oh <= oh_hi && ow <= ow_hi && kh >= 0 && kh < g.PH && kw >= 0 && kw < g.PW;
+        const long o = ((b * g.Ho + oh) * g.Wo + ow) * (long)g.C + c;
+        want[a] = ok ? (uint32_t)(kh * g.PW + kw) : 0xffffffffu;      // never equals a stored arg-max byte
+        ib[a] = ok ? __ldg(reinterpret_cast<const uint2*>(idx + o)) : make_uint2(0u, 0u);
+        dv[a] = ok ? ldg16(dy + o) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        const F8 d = unpack8(dv[a]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t got = ((j < 4 ? ib[a].x : ib[a].y) >> (8 * (j & 3))) & 0xffu;
+          if (got == want[a]) s.v[j] += d.v[j];
+        }
+      }
+      *reinterpret_cast<uint4*>(dx + ((b * g.H + h) * g.W + w) * (long)g.C + c) = pack8(s);
+      continue;
+    }
     for (int oh = oh_lo; oh <= oh_hi; ++oh) {
       const int kh = hh - oh * g.sh;
       if (kh < 0 || kh >= g.PH) continue;

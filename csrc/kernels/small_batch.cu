@@ -447,7 +447,7 @@ dense_bwd_skinny_kernel(const float* __restrict__ x, const float* __restrict__ w
 // 1 if tfde_dense_skinny_fwd handles this shape (otherwise use tfde_dense_fwd).
 TFDE_API int tfde_dense_skinny_supported(int M, int K, int N) {
   const int tiles = ((M + SK_TM - 1) / SK_TM) * ((N + SK_TN - 1) / SK_TN);
-  return (K % 4 == 0 && N % 4 == 0 && K >= 512 && tiles >= 1 && tiles <= 4) ? 1 : 0;
+  return (K % 4 == 0 && N % 4 == 0 && K >= 512 && tiles >= 1 && tiles <= 8) ? 1 : 0;
 }
 TFDE_API size_t tfde_dense_skinny_ws_floats(int M, int K, int N) {
   const int tiles = ((M + SK_TM - 1) / SK_TM) * ((N + SK_TN - 1) / SK_TN);

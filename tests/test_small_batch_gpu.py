@@ -23,7 +23,7 @@ def _close(a, b, rtol=2e-4, atol=2e-5, what=""):
 
 
 @pytest.mark.parametrize("M,K,N,relu,bias", [(64, 5408, 64, True, True), (1, 5408, 64, False, True),
-                                             (37, 1176, 200, True, False), (128, 2048, 128, False, True),
+                                             (37, 1176, 200, True, False), (128, 1176, 200, False, False), (128, 2048, 128, False, True),
                                              (64, 512, 4, True, True), (50, 16000, 60, False, False)])
 def test_dense_skinny_cluster_splitk(M, K, N, relu, bias):
     L = native.load()
