@@ -298,6 +298,28 @@ int tfde_gemm_bf16_nn_stats_persistent(const void* A, const void* B, void* c_bf1
                                        int N, int K, int kb, long ldb, float* stat_sum, float* stat_sq,
                                        tfde_stream_t stream);
 
+/* ---- implicit-GEMM convolutions (gemm_tcgen05_persistent.cu, CONV modes) ------------------------------------ */
+/* The im2col operand is never written to memory: the producer warp of the persistent tcgen05 GEMM fetches
+ * 128-pixel x 64-channel tiles of the NHWC bf16 activation with im2col-mode TMA loads (cuTensorMapEncodeIm2col,
+ * SASS UTMALDG.4D.IM2COL; padding = the tensor map's zero fill). Channel counts: C % 64 == 0 and Cout % 64 == 0,
+ * windows up to 16 x 16, pads = (top, bottom, left, right). bf16 outputs leave through TMA stores (UTMASTG).
+ * ref: Conv2D of mnist_keras_distributed.py:83-98 / distributed_with_keras.py:34 (cuDNN in TF). */
+int tfde_conv_igemm_supported(int B, int H, int W, int C, int KH, int KW, int Ho, int Wo, int Cout);
+/* y[B,Ho,Wo,Cout] = conv(x[B,H,W,C], w16[KH,KW,C,Cout] as stored) + bias; stat_sum/stat_sq: optional fused
+ * batch-norm partial statistics as in tfde_gemm_bf16_nn_stats_persistent. */
+int tfde_conv_igemm_fwd(const void* x, const void* w16, void* y, const float* bias, int B, int H, int W, int C, int KH,
+                        int KW, int Ho, int Wo, int sh, int sw, int pt, int pb, int pl, int pr, int Cout,
+                        float* stat_sum, float* stat_sq, float* ws, size_t ws_bytes, tfde_stream_t stream);
+/* dx[B,H,W,C] of a STRIDE-1 convolution: the same kernel run over dy with the mirrored padding; the forward
+ * pass's bf16 weights are read K-major with the taps mirrored (no rotated copy). */
+int tfde_conv_igemm_dgrad(const void* dy, const void* w16, void* dx, int B, int H, int W, int C, int KH, int KW,
+                          int Ho, int Wo, int pt, int pl, int Cout, float* ws, size_t ws_bytes, tfde_stream_t stream);
+/* dw[KH,KW,C,Cout] (fp32) = im2col(x)^T . dy: 64-pixel x 64-channel im2col boxes as the MN-major A operand,
+ * reduced over the B*Ho*Wo output pixels with deterministic split-K through ws. */
+int tfde_conv_igemm_wgrad(const void* x, const void* dy, float* dw, int B, int H, int W, int C, int KH, int KW,
+                          int Ho, int Wo, int sh, int sw, int pt, int pb, int pl, int pr, int Cout, float* ws,
+                          size_t ws_bytes, tfde_stream_t stream);
+
 /* ---- bf16-activation layer kernels (act_bf16.cu) ----------------------------------------------------------- */
 /* Keras mixed_bfloat16 semantics: bf16 tensors between layers, fp32 variables / statistics. All tensors are
  * channels-last with C % 8 == 0 (tfde_act16_supported_channels). `ws`/`counters`: per-stream scratch for the

@@ -1,6 +1,6 @@
 """Writes profiles/sass/<kernel>.sass for the kernels of libtfde_kernels.so and a summary of the SASS
-mnemonics that prove the Blackwell-native paths (UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG = TMA,
-UTCBAR = tcgen05.commit, SYNCS = mbarrier, peer/system-scope memory ops in the all-reduce)."""
+mnemonics that prove the Blackwell-native paths (UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG = TMA load,
+UTMALDG.4D.IM2COL = im2col-mode TMA load, UTMASTG = TMA store, UTCBAR = tcgen05.commit, SYNCS = mbarrier, peer/system-scope memory ops in the all-reduce)."""
 import collections
 import os
 import re
@@ -14,7 +14,7 @@ KEEP = ("fused_step_kernel", "dense_bwd_skinny_kernel", "ps_push_multi_kernel", 
         "conv3x3c1_relu_pool", "allreduce_nvls_kernel", "gemm_bf16_tcgen05_persistent_kernel", "colstats_bf16_kernel",
         "bn_bwd_apply_bf16_kernel", "gemm_fp32_kernel", "smallconv", "bn_reduce_smallc")
 N_LISTED = 14     # kernels of KEEP[:N_LISTED] get a full listing; the rest only a row in the summary
-MNEMONICS = ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMAPF", "SYNCS", "LDGSTS", "UCGABAR", "LDGMC", "HMMA", "FFMA", "LDG",
+MNEMONICS = ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMALDG.4D.IM2COL", "UTMASTG", "UTMAPF", "SYNCS", "LDGSTS", "UCGABAR", "LDGMC", "HMMA", "FFMA", "LDG",
              "STG", "STS", "LDS", "ATOMG", "REDG", "MEMBAR", "CCTL")
 
 
@@ -37,6 +37,9 @@ def main():
             m2 = re.search(r"(smallconv_\w+?_kernel|bn_reduce_smallc_kernel)ILi?b?(\d+)", name)
             if m2:
                 short = f"{m2.group(1)}_{m2.group(2)}"
+        m3 = re.search(r"(gemm_bf16_tcgen05(?:_persistent)?_kernel|colstats_bf16_kernel|gemm_fp32_kernel)<([^>]*)>", clean)
+        if m3:                               # template instantiations: one listing / row each
+            short = m3.group(1) + "_" + re.sub(r"[^A-Za-z0-9]+", "_", m3.group(2).replace("(int)", "")).strip("_")
         counts = collections.Counter()
         for line in body.splitlines():
             m = re.search(r"/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
@@ -48,7 +51,12 @@ def main():
                 if ".SYS" in op or ".STRONG.SYS" in op:
                     counts["sys-scope"] += 1
         path = os.path.join(OUT, short + ".sass")
-        if any(k in name for k in KEEP[:N_LISTED]):
+        listed = any(k in name for k in KEEP[:N_LISTED])
+        if "persistent_kernel" in short:     # 18 instantiations: list the plain GEMM and the three convolution modes
+            listed = short.endswith(("_256_0_0", "_256_2_1", "_256_0_2", "_256_3_3"))
+        elif short.startswith("gemm_bf16_tcgen05_kernel"):
+            listed = short.endswith("_256_2")
+        if listed:
             with open(path, "w") as f:
                 f.write("Function : " + part)
         rows.append((short, counts))
