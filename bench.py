@@ -59,7 +59,7 @@ def parse_args():
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--repeats", type=int, default=5, help="timed regions of K steps each; the median is reported")
     ap.add_argument("--steps-per-execution", type=int, default=0,
-                    help="steps handed to the device per launch (Keras steps_per_execution); 0 = min(16, steps/4), so that the copies of one execution overlap the kernel of the previous one")
+                    help="steps handed to the device per launch (Keras steps_per_execution); 0 = min(64, steps) with streamed inputs (Model A), else min(16, steps/4) so that the copies of one execution overlap the kernel of the previous one")
     ap.add_argument("--no-check", action="store_true", help="skip the replica / CPU-oracle correctness check")
     ap.add_argument("--l2", default="inputs", choices=["inputs", "flush"],
                     help="timing protocol for `value`: distinct inputs from a pool larger than L2 (default) or "
@@ -295,8 +295,16 @@ def run_ours(args):
     # steps_per_execution (Keras): the device-timed region feeds device-resident batches, where one launch can take all
     # K steps; the end-to-end region wants >= 4 executions in flight so that the H2D copies of one execution overlap the
     # kernel of the previous one
-    spe = args.steps_per_execution if args.steps_per_execution > 0 else max(1, min(16, K // 4))
     spe_dev = args.steps_per_execution if args.steps_per_execution > 0 else max(1, min(64, K))
+    from tfde_b200.ops import fused_step as _fs
+    if args.steps_per_execution > 0:
+        spe = args.steps_per_execution
+    elif args.model == "a" and _fs.enabled() and _fs.streamed_inputs():
+        # streamed inputs: the whole-step kernel is launched without waiting for the copies and takes up every step when
+        # that step's batch has landed, so ONE execution covers the region with the copies hidden under compute
+        spe = spe_dev
+    else:
+        spe = max(1, min(16, K // 4))
     if args.dtype == "bf16":
         tf.keras.mixed_precision.set_global_policy("mixed_bfloat16")
     check = correctness_check(tf, strategy, args, rank, world) if not args.no_check else None
@@ -435,12 +443,14 @@ def run_ours(args):
                    "allreduce": ar},
         "clocks": clocks,
         "e2e": {"value": gb * K / e2e_med, "unit": "images/sec", "ms_per_step": 1e3 * e2e_med / K,
-                "h2d_bytes_per_step": per, "d2h_bytes_per_step": 16, "last_loss": loss,
+                "h2d_bytes_per_step": per + (4 if (fused and _fs.streamed_inputs()) else 0), "d2h_bytes_per_step": 16, "last_loss": loss,
                 "s_per_repeat": e2e_s,
                 "note": ("model.train_on_batches(x, y, steps) == Keras steps_per_execution: per step one cudaMemcpyAsync "
-                         "of that step's pinned uint8 images and one of its int64 labels (copy stream, overlapping the "
-                         "previous execution), one launch per execution, every step's [loss, correct, rows, 0] written "
-                         "into mapped pinned memory and read on the host one execution late (K reads for K steps)")},
+                         "of that step's pinned uint8 images, one of its int64 labels and a 4-byte ready tag (copy "
+                         "stream); one launch per execution, started without waiting for the copies -- the kernel takes "
+                         "up step s when its tag has landed (TFDE_FUSED_STREAM=0: all copies first, then the launch); "
+                         "every step's [loss, correct, rows, 0] written into mapped pinned memory and read on the host "
+                         "(K reads for K steps)")},
         "gpu_launches": int(launches),
         "kernel_launches_per_step": launches / K,
         "correctness": check,

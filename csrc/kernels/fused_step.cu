@@ -161,6 +161,9 @@ struct FsParams {
   float* srecv[FS_MAX_RANKS];     // srecv[r]: rank r's small-block receive slots [2][world][FS_SMALL_MAX]
   uint32_t* flags[FS_MAX_RANKS];  // flags[r]: RS [world][176] | AG [176] | S [world]
   unsigned long long* prof;       // optional [FS_PIX][FS_PROF_STAMPS] globaltimer stamps of the LAST step of a launch
+  // streamed inputs (end-to-end path): ready[s] becomes >= ready_tag once step s's images and labels have landed in
+  // x / y -- written by a 4-byte copy queued behind that step's copies on the copy stream, while this kernel runs
+  const uint32_t* ready; uint32_t ready_tag;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -385,6 +388,7 @@ fused_step_kernel(const FsParams p) {
   const bool hg_cta = pix < 16;             // computes 4 rows of the head kernel gradient
   const int grp = pix / FS_GROUPS;          // two-level ticket group
   __shared__ Hyper s_hprev;                 // hyper-parameters of the step whose slice exchange is still pending
+  __shared__ int s_in_ready;                // streamed inputs: the next step's batch was on the device at this step's start
   bool pending = false;                     // W > 1: the previous step's slice is reduced/updated lazily, right
   float gacc[2][4];                         //        before this step's GEMM needs it (off the critical path)
   const int tc = t >> 4, tn = t & 15;
@@ -420,6 +424,16 @@ fused_step_kernel(const FsParams p) {
       h.lr_t = (p.opt == 3) ? h.lr * sqrtf(1.f - b2p) / (1.f - b1p) : h.lr;
     }
     FS_STAMP(0);
+    if (p.ready != nullptr) {
+      // streamed inputs: the first step of a launch waits for its batch; every step looks ahead (non-blocking) whether
+      // the NEXT batch is already here, so the prefetch at its end does not have to ask (steady state: the copy
+      // engine is a whole step ahead)
+      if (t == 0) {
+        if (s == 0) wait_flag<true>(p, p.ready, p.ready_tag, 12, pix, 0);
+        s_in_ready = (s + 1 < p.nsteps) && (int)(ld_acquire_sys(p.ready + s + 1) - p.ready_tag) >= 0;
+      }
+      if (s == 0) __syncthreads();
+    }
     // ================================ P1: conv + pool + split-K dense partial =========================
     int ylab = -1;
     {
@@ -1016,6 +1030,10 @@ fused_step_kernel(const FsParams p) {
     // ================================ wait for the step to be complete ==================================
     FS_STAMP(10);
     if (s + 1 < p.nsteps) {
+      if (p.ready != nullptr && !s_in_ready) {   // (uniform per CTA: written at the top of this step) not seen yet: wait
+        if (t == 0) wait_flag<true>(p, p.ready + s + 1, p.ready_tag, 12, pix, 4);
+        __syncthreads();
+      }
       load_patch(s + 1, pv);               // next step's inputs: in flight while this step's tail finishes
       if (t == 0) wait_flag<false>(p, p.state + ST_DONE, e, 11, pix, 3);
       __syncthreads();
@@ -1050,6 +1068,7 @@ struct TfdeFusedStepDesc {
   unsigned long long timeout_ns;
   void* rs[FS_MAX_RANKS]; void* gsum[FS_MAX_RANKS]; void* srecv[FS_MAX_RANKS]; void* flags[FS_MAX_RANKS];
   void* prof;
+  void* ready; unsigned ready_tag;          // streamed inputs (tfde_fused_exec_streamed); NULL: inputs are resident
 };
 
 TFDE_API size_t tfde_fused_step_desc_bytes() { return sizeof(TfdeFusedStepDesc); }
@@ -1127,6 +1146,7 @@ TFDE_API int tfde_fused_step(const TfdeFusedStepDesc* d, cudaStream_t stream) {
     p.srecv[i] = (float*)d->srecv[i]; p.flags[i] = (uint32_t*)d->flags[i];
   }
   p.prof = (unsigned long long*)d->prof;
+  p.ready = (const uint32_t*)d->ready; p.ready_tag = d->ready_tag;
   if (d->world > 1)
     for (int i = 0; i < d->world; ++i)
       if (!p.rs[i] || !p.gsum[i] || !p.srecv[i] || !p.flags[i]) return TFDE_ERR_INVALID;
@@ -1183,6 +1203,42 @@ TFDE_API int tfde_fused_exec(const TfdeFusedStepDesc* d, const void* host_x, con
   if (err != cudaSuccess) return (int)err;
   int rc = tfde_fused_step(d, stream);
   if (rc != 0) return rc;
+  return (int)cudaEventRecord((cudaEvent_t)ev_done, stream);
+}
+
+// Streamed form of tfde_fused_exec: the kernel is launched FIRST-COME -- it does not wait for the copies. Per step the
+// copy stream carries that step's images, its labels and then a 4-byte tag into d->ready[s]; the kernel (d->ready,
+// d->ready_tag) consumes step s once ready[s] >= tag (bounded wait, status code 12). One launch then covers any
+// number of steps with every copy but the first step's hidden under compute, instead of one launch per staging chunk.
+// host_tags: pinned uint32[nsteps], all equal to d->ready_tag (tags grow with every use of the same ready array).
+// The copies are plain cudaMemcpyAsync calls (copy engine); nothing on the copy stream depends on the kernel.
+TFDE_API int tfde_fused_exec_streamed(const TfdeFusedStepDesc* d, const void* host_x, const void* host_y,
+                                      const void* host_tags, size_t x_bytes_per_step, size_t y_bytes_per_step,
+                                      cudaStream_t copy_stream, void* ev_copied, void* ev_done, cudaStream_t stream) {
+  if (d->ready == nullptr || host_tags == nullptr) return TFDE_ERR_INVALID;
+  cudaError_t err;
+  char* dx = (char*)d->x; char* dy = (char*)d->y;
+  auto copy_step = [&](int s) -> cudaError_t {
+    cudaError_t e = cudaMemcpyAsync(dx + (size_t)s * x_bytes_per_step, (const char*)host_x + (size_t)s * x_bytes_per_step,
+                                    x_bytes_per_step, cudaMemcpyHostToDevice, copy_stream);
+    if (e != cudaSuccess) return e;
+    e = cudaMemcpyAsync(dy + (size_t)s * y_bytes_per_step, (const char*)host_y + (size_t)s * y_bytes_per_step,
+                        y_bytes_per_step, cudaMemcpyHostToDevice, copy_stream);
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyAsync((char*)d->ready + (size_t)s * 4, (const char*)host_tags + (size_t)s * 4, 4,
+                           cudaMemcpyHostToDevice, copy_stream);
+  };
+  // the first step's batch is queued before the launch, the rest right behind it
+  err = copy_step(0);
+  if (err != cudaSuccess) return (int)err;
+  int rc = tfde_fused_step(d, stream);
+  if (rc != 0) return rc;
+  for (int s = 1; s < d->nsteps; ++s) {
+    err = copy_step(s);
+    if (err != cudaSuccess) return (int)err;
+  }
+  err = cudaEventRecord((cudaEvent_t)ev_copied, copy_stream);
+  if (err != cudaSuccess) return (int)err;
   return (int)cudaEventRecord((cudaEvent_t)ev_done, stream);
 }
 

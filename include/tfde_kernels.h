@@ -242,6 +242,7 @@ typedef struct TfdeFusedStepDesc {
   unsigned long long timeout_ns;
   void* rs[8]; void* gsum[8]; void* srecv[8]; void* flags[8];    /* world > 1: peer-mapped receive buffers */
   void* prof;                              /* optional globaltimer stamps [169][16] */
+  void* ready; unsigned ready_tag;         /* streamed inputs: uint32 ready[nsteps] (step s usable once >= ready_tag); NULL = resident */
 } TfdeFusedStepDesc;
 size_t tfde_fused_step_desc_bytes(void);
 size_t tfde_fused_step_part_floats(void);
@@ -263,6 +264,12 @@ int tfde_fused_step(const TfdeFusedStepDesc* d, tfde_stream_t stream);
 int tfde_fused_exec(const TfdeFusedStepDesc* d, const void* host_x, const void* host_y, size_t x_bytes_per_step,
                     size_t y_bytes_per_step, tfde_stream_t copy_stream, void* ev_copied, void* ev_done,
                     tfde_stream_t stream);
+/* Streamed form: the kernel is launched without waiting for the copies; behind every step's images and labels the copy
+ * stream writes host_tags[s] (pinned, == d->ready_tag) into d->ready[s], and the kernel takes up step s when it sees it.
+ * One launch covers all steps with all copies but the first hidden under compute. */
+int tfde_fused_exec_streamed(const TfdeFusedStepDesc* d, const void* host_x, const void* host_y, const void* host_tags,
+                             size_t x_bytes_per_step, size_t y_bytes_per_step, tfde_stream_t copy_stream,
+                             void* ev_copied, void* ev_done, tfde_stream_t stream);
 int tfde_event_create(void** out);
 int tfde_event_destroy(void* e);
 int tfde_event_synchronize(void* e);

@@ -42,6 +42,7 @@ class _FusedStepDesc(ctypes.Structure):
         ("rs", ctypes.c_void_p * MAX_RANKS), ("gsum", ctypes.c_void_p * MAX_RANKS),
         ("srecv", ctypes.c_void_p * MAX_RANKS), ("flags", ctypes.c_void_p * MAX_RANKS),
         ("prof", ctypes.c_void_p),
+        ("ready", ctypes.c_void_p), ("ready_tag", ctypes.c_uint),
     ]
 
 
@@ -56,6 +57,9 @@ for _n, _a, _r in [
     ("tfde_fused_step", [ctypes.POINTER(_FusedStepDesc), ctypes.c_void_p], ctypes.c_int),
     ("tfde_fused_exec", [ctypes.POINTER(_FusedStepDesc), ctypes.c_void_p, ctypes.c_void_p, _sz, _sz,
                          ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p], ctypes.c_int),
+    ("tfde_fused_exec_streamed", [ctypes.POINTER(_FusedStepDesc), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                  _sz, _sz, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p],
+     ctypes.c_int),
     ("tfde_event_create", [ctypes.POINTER(ctypes.c_void_p)], ctypes.c_int),
     ("tfde_event_destroy", [ctypes.c_void_p], ctypes.c_int),
     ("tfde_event_synchronize", [ctypes.c_void_p], ctypes.c_int),
@@ -66,6 +70,12 @@ for _n, _a, _r in [
 
 def enabled() -> bool:
     return os.environ.get("TFDE_FUSED_STEP", "1") == "1"
+
+
+def streamed_inputs() -> bool:
+    """End-to-end executions launch the kernel without waiting for the host->device copies; the kernel takes up each
+    step when that step's ready tag has landed (``TFDE_FUSED_STREAM=0``: all copies first, then the launch)."""
+    return os.environ.get("TFDE_FUSED_STREAM", "1") == "1"
 
 
 def match(model):
@@ -106,6 +116,10 @@ class _Slot:
         # pinned staging for callers whose batches are not pinned
         self.host_x = None
         self.host_y = None
+        # streamed inputs: per-step ready words on the device, their pinned source, a tag that grows with every use
+        self.ready = torch.zeros(K, dtype=torch.int32, device=dev)
+        self.host_tags = torch.zeros(K, dtype=torch.int32).pin_memory()
+        self.tag = 0
         ev = ctypes.c_void_p()
         native.check(L.tfde_event_create(ctypes.byref(ev)), "event_create", kernels=0)
         self.ev_copied = ev.value
@@ -236,9 +250,21 @@ class FusedStepPlan:
             slot.host_y.copy_(y.reshape(-1))
             y = slot.host_y
         self._fill(slot.x, slot.y, B, nsteps, global_batch, slot.dev_tails)
-        native.check(L.tfde_fused_exec(ctypes.byref(self.desc), x.data_ptr(), y.data_ptr(),
-                                       B * 784 * x.element_size(), B * 8, self._copy_stream.cuda_stream,
-                                       slot.ev_copied, slot.ev_done, stream.cuda_stream), "fused_exec")
+        if streamed_inputs() and hasattr(L, "tfde_fused_exec_streamed"):
+            slot.tag = (slot.tag + 1) & 0xFFFFFFFF     # (slot.wait() above: nobody reads the previous tags any more)
+            slot.host_tags.fill_(slot.tag - (1 << 32) if slot.tag >= (1 << 31) else slot.tag)   # uint32 bit pattern
+            self.desc.ready, self.desc.ready_tag = slot.ready.data_ptr(), slot.tag
+            try:
+                native.check(L.tfde_fused_exec_streamed(ctypes.byref(self.desc), x.data_ptr(), y.data_ptr(),
+                                                        slot.host_tags.data_ptr(), B * 784 * x.element_size(), B * 8,
+                                                        self._copy_stream.cuda_stream, slot.ev_copied, slot.ev_done,
+                                                        stream.cuda_stream), "fused_exec")
+            finally:
+                self.desc.ready, self.desc.ready_tag = None, 0
+        else:
+            native.check(L.tfde_fused_exec(ctypes.byref(self.desc), x.data_ptr(), y.data_ptr(),
+                                           B * 784 * x.element_size(), B * 8, self._copy_stream.cuda_stream,
+                                           slot.ev_copied, slot.ev_done, stream.cuda_stream), "fused_exec")
         slot.busy = True
         slot.nsteps = nsteps
         slot.src = (x, y)                              # keep the pinned sources alive until the copies ran
@@ -303,7 +329,7 @@ class FusedStepPlan:
     def check(self):
         st = self.status.cpu().tolist()
         if st[0] != 0:
-            what = {10: "grid barrier", 11: "step-complete flag", 21: "small-tensor exchange with peer",
+            what = {10: "grid barrier", 11: "step-complete flag", 12: "streamed input batch (host->device copy)", 21: "small-tensor exchange with peer",
                     22: "reduce-scatter contribution from peer", 23: "reduced slice from owner"}.get(st[0], "wait")
             raise RuntimeError(
                 f"whole-step kernel timed out on rank {self.rank}: {what} (code {st[0]}), epoch/target {st[1]}, "

@@ -212,3 +212,29 @@ def test_epoch_counters_wrap_around_2_pow_32():
     assert int(plan.state[96].item()) & 0xFFFFFFFF == (E0 + 7) % (1 << 32)
     for a, b in zip(m.get_weights(), ref_m.get_weights()):
         assert np.array_equal(a, b)
+
+
+def test_streamed_inputs_equal_staged_inputs(monkeypatch):
+    """End-to-end executions with the kernel launched ahead of its host->device copies (it takes up every step when that
+    step's ready tag has landed) == all copies first, then the launch: bit for bit, over many back-to-back executions
+    that re-use the two staging slots (growing tags), from pinned and from pageable host memory."""
+    x, y = _data(64 * 40, seed=11)
+    xp, yp = x.pin_memory(), y.pin_memory()
+    res = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("TFDE_FUSED_STREAM", mode)
+        with Strategy(device="cuda").scope():
+            m = tf.models.build_and_compile_cnn_model(optimizer=_opt("momentum"), seed=7)
+        losses = []
+        for rep in range(3):                                   # 3 x (8 + 8 + 4) steps from pinned memory, pipelined
+            for lo, k in ((0, 8), (8, 8), (16, 4)):
+                m.train_on_batches(xp[lo * 64:(lo + k) * 64], yp[lo * 64:(lo + k) * 64], steps=k)
+                losses += m.last_losses()
+        m.train_on_batches(x[20 * 64:], y[20 * 64:], steps=20)  # pageable source, one long execution
+        losses += m.last_losses()
+        m.fused_plan().check()
+        res[mode] = (losses, m.get_weights())
+    assert len(res["1"][0]) == 80 and res["1"][0] == res["0"][0]
+    assert all(np.isfinite(v) for v in res["1"][0])
+    for a, b in zip(res["1"][1], res["0"][1]):
+        assert np.array_equal(a, b)
