@@ -128,6 +128,9 @@ class _Slot:
         self.ev_done = ev.value
         self.busy = False
         self.nsteps = 0
+        # the zero fill of `ready` ran on the caller's current stream; the copy stream writes tags into it and the
+        # kernel (another stream) polls it: it must have landed before either starts
+        torch.cuda.current_stream(dev).synchronize()
 
     def wait(self):
         if self.busy:
@@ -190,6 +193,8 @@ class FusedStepPlan:
             torch.cuda.synchronize(dev)
             dist.barrier(group=st.group)          # everyone has mapped everything before anyone launches
             log.info("whole-step kernel: in-kernel all-reduce over %d replicas (peer memory)", W)
+        # the zero fills above ran on the caller's current stream, the kernel runs on the model's: one-time join
+        torch.cuda.synchronize(dev)
         self._slots = {}
         self._turn = 0
         self._copy_stream = None
