@@ -484,9 +484,14 @@ class Sequential:
         if self._stream is None:
             self._stream = torch.cuda.Stream(device=self.device)
         if x.is_cuda:
-            with torch.cuda.stream(self._stream):
-                self._stream.wait_stream(torch.cuda.current_stream(self.device))
-                plan.launch(x.contiguous(), yy.contiguous().long(), B, K, gb)
+            # (conversions, if any, run on the caller's stream BEFORE the edge to the model's stream is recorded; the
+            # launch names its stream explicitly: no stream-context switch on the per-launch host path)
+            xc = x if x.is_contiguous() else x.contiguous()
+            yc = yy if (yy.dtype == torch.int64 and yy.is_contiguous()) else yy.contiguous().long()
+            cur = torch.cuda.current_stream(self.device)
+            if cur != self._stream:
+                self._stream.wait_stream(cur)
+            plan.launch(xc, yc, B, K, gb, stream=self._stream)
             self._host_tail = None
         else:
             plan.execute(x, yy, B, K, gb, self._stream)
@@ -565,9 +570,12 @@ class Sequential:
             # stream, loss written into mapped pinned memory); device batches are consumed in place.
             yy = y.reshape(-1)
             if x.is_cuda:
-                with torch.cuda.stream(self._stream):
-                    self._stream.wait_stream(torch.cuda.current_stream(self.device))
-                    plan.launch(x.contiguous(), yy.contiguous().long(), b, 1, gb)
+                xc = x if x.is_contiguous() else x.contiguous()
+                yc = yy if (yy.dtype == torch.int64 and yy.is_contiguous()) else yy.contiguous().long()
+                cur = torch.cuda.current_stream(self.device)
+                if cur != self._stream:
+                    self._stream.wait_stream(cur)
+                plan.launch(xc, yc, b, 1, gb, stream=self._stream)
                 self._host_tail = None
             else:
                 plan.execute(x, yy, b, 1, gb, self._stream)

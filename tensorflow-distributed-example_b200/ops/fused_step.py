@@ -223,11 +223,12 @@ class FusedStepPlan:
         return (1 <= B <= MAX_B and x.dtype in (torch.uint8, torch.float32)
                 and not self.model.loss.from_probs and self.model.strategy.synchronous)
 
-    def launch(self, x: torch.Tensor, y: torch.Tensor, B: int, nsteps: int, global_batch: int, tails=None):
+    def launch(self, x: torch.Tensor, y: torch.Tensor, B: int, nsteps: int, global_batch: int, tails=None, stream=None):
         """``nsteps`` optimizer steps on device-resident inputs x [nsteps*B, 28, 28, 1] / y [nsteps*B] (int64),
-        on the current stream."""
+        on ``stream`` (default: the current stream)."""
         self._fill(x, y, B, nsteps, global_batch, tails)
-        native.check(native.load().tfde_fused_step(ctypes.byref(self.desc), native.stream_ptr()), "fused_step")
+        sp = stream.cuda_stream if stream is not None else native.stream_ptr()
+        native.check(native.load().tfde_fused_step(ctypes.byref(self.desc), sp), "fused_step")
 
     # ------------------------------------------------------------------------------------------
     def execute(self, x, y, B: int, nsteps: int, global_batch: int, stream: torch.cuda.Stream) -> _Slot:
