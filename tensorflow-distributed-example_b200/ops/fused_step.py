@@ -196,6 +196,7 @@ class FusedStepPlan:
         # the zero fills above ran on the caller's current stream, the kernel runs on the model's: one-time join
         torch.cuda.synchronize(dev)
         self._slots = {}
+        self._pin_cache = {}
         self._turn = 0
         self._copy_stream = None
         self.last_slot: Optional[_Slot] = None
@@ -223,6 +224,17 @@ class FusedStepPlan:
         return (1 <= B <= MAX_B and x.dtype in (torch.uint8, torch.float32)
                 and not self.model.loss.from_probs and self.model.strategy.synchronous)
 
+    def _pinned(self, t: torch.Tensor) -> bool:
+        """``t.is_pinned()`` costs a driver query (~10 us) per call: remembered per host allocation. A stale entry (the
+        address re-used by pageable memory) only costs asynchrony: cudaMemcpyAsync stages pageable sources itself."""
+        key = (t.data_ptr(), t.numel() * t.element_size())
+        hit = self._pin_cache.get(key)
+        if hit is None:
+            if len(self._pin_cache) > 256:
+                self._pin_cache.clear()
+            hit = self._pin_cache[key] = bool(t.is_pinned())
+        return hit
+
     def launch(self, x: torch.Tensor, y: torch.Tensor, B: int, nsteps: int, global_batch: int, tails=None, stream=None):
         """``nsteps`` optimizer steps on device-resident inputs x [nsteps*B, 28, 28, 1] / y [nsteps*B] (int64),
         on ``stream`` (default: the current stream)."""
@@ -245,12 +257,12 @@ class FusedStepPlan:
         slot = slots[self._turn & 1]
         self._turn += 1
         slot.wait()                                   # the execution that last used this slot has finished
-        if not (x.is_pinned() and x.is_contiguous()):
+        if not (self._pinned(x) and x.is_contiguous()):
             if slot.host_x is None:
                 slot.host_x = torch.empty((nsteps * B, 28, 28, 1), dtype=xdtype).pin_memory()
             slot.host_x.view(-1).copy_(x.reshape(-1))
             x = slot.host_x
-        if y.dtype != torch.int64 or not (y.is_pinned() and y.is_contiguous()):
+        if y.dtype != torch.int64 or not (self._pinned(y) and y.is_contiguous()):
             if slot.host_y is None:
                 slot.host_y = torch.empty((nsteps * B,), dtype=torch.int64).pin_memory()
             slot.host_y.copy_(y.reshape(-1))
