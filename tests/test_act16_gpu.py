@@ -87,6 +87,17 @@ def test_elementwise_and_pools():
     dy = torch.randn(*yc.shape, generator=g).to(BF)
     _close(act16.maxpool_bwd(dy.to(dev), ig, tuple(x.shape), (3, 3), (2, 2), pads),
            act16.maxpool_bwd(dy, ic, tuple(x.shape), (3, 3), (2, 2), pads), 1e-2, 1e-2)
+    # overlapping windows with more than 2 x 2 covers per input position (3x3 / stride 1): the general backward loop;
+    # 2x2 / stride 2: exactly one cover (the batched-load path, like 3x3 / 2 above)
+    for pool, st, pd in (((3, 3), (1, 1), (1, 1, 1, 1)), ((2, 2), (2, 2), (0, 0, 0, 0))):
+        xs = torch.randn(2, 12, 12, 32, generator=g).to(BF)
+        yc2, ic2 = act16.maxpool_fwd(xs, pool, st, pd)
+        yg2, ig2 = act16.maxpool_fwd(xs.to(dev), pool, st, pd)
+        _close(yg2, yc2, 0, 0)
+        assert torch.equal(ig2.cpu(), ic2)
+        dy2 = torch.randn(*yc2.shape, generator=g).to(BF)
+        _close(act16.maxpool_bwd(dy2.to(dev), ig2, tuple(xs.shape), pool, st, pd),
+               act16.maxpool_bwd(dy2, ic2, tuple(xs.shape), pool, st, pd), 1e-2, 1e-2)
     # global average pool
     _close(act16.global_avgpool_fwd(a.to(dev)), act16.global_avgpool_fwd(a), 1e-4, 1e-4)
     d = torch.randn(8, 64, generator=g)
