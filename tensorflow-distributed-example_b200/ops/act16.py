@@ -426,38 +426,35 @@ def conv2d_bwd(x, w, dy, stride=(1, 1), pads=(0, 0, 0, 0), need_dx=True, has_bia
                 conv_igemm.wgrad(x, dy, w.shape, stride, pads, dw)
         else:
             conv_igemm.wgrad(x, dy, w.shape, stride, pads, dw)
-        a = kp = None
     else:
         a, kp = _a_operand(x, w.shape, stride, pads, ho, wo, "C", cache=a_cache, reuse=a_cache is not None)
-    if igemm:
-        pass
-    elif _WGRAD_NT and kc % 8 == 0:
-        # operands as the forward pass left them: A[M, kc] and dy[M, cout], reduced over rows -> the tcgen05
-        # GEMM reads them MN-major, no transposed copies
-        a_nt = a[:, :kc] if kp != kc else a
-        owns_a = a_cache is not None or a.data_ptr() == x.data_ptr()     # not in the shared scratch pool
-        if side_stream is not None and need_dx and owns_a:
-            # only the optimizer consumes dW: fork it so it overlaps the data-gradient chain of this layer and
-            # the batch-norm backward of the previous one (joined before the optimizer / all-reduce)
-            side_stream.wait_stream(torch.cuda.current_stream(dev))
-            with torch.cuda.stream(side_stream):
+        if _WGRAD_NT and kc % 8 == 0:
+            # operands as the forward pass left them: A[M, kc] and dy[M, cout], reduced over rows -> the tcgen05
+            # GEMM reads them MN-major, no transposed copies
+            a_nt = a[:, :kc] if kp != kc else a
+            owns_a = a_cache is not None or a.data_ptr() == x.data_ptr()     # not in the shared scratch pool
+            if side_stream is not None and need_dx and owns_a:
+                # only the optimizer consumes dW: fork it so it overlaps the data-gradient chain of this layer and
+                # the batch-norm backward of the previous one (joined before the optimizer / all-reduce)
+                side_stream.wait_stream(torch.cuda.current_stream(dev))
+                with torch.cuda.stream(side_stream):
+                    tensorcore.gemm_bf16_nt(a_nt, dy2, out=dw.view(kc, cout))
+            else:
                 tensorcore.gemm_bf16_nt(a_nt, dy2, out=dw.view(kc, cout))
+        elif _WGRAD_NT and cout % 8 == 0:
+            # kc not a multiple of 8 (the 7x7x3 stem): reduce the PADDED operand [M, kp] the same way -- rows kc..kp of
+            # the product come from the padding columns and are dropped -- instead of transposing both operands
+            dwp = _scratch(dev, "Wp", kp * cout * 2).view(torch.float32).view(kp, cout)
+            tensorcore.gemm_bf16_nt(a, dy2, out=dwp)
+            dw.view(kc, cout).copy_(dwp[:kc])
         else:
-            tensorcore.gemm_bf16_nt(a_nt, dy2, out=dw.view(kc, cout))
-    elif _WGRAD_NT and cout % 8 == 0:
-        # kc not a multiple of 8 (the 7x7x3 stem): reduce the PADDED operand [M, kp] the same way -- rows kc..kp of
-        # the product come from the padding columns and are dropped -- instead of transposing both operands
-        dwp = _scratch(dev, "Wp", kp * cout * 2).view(torch.float32).view(kp, cout)
-        tensorcore.gemm_bf16_nt(a, dy2, out=dwp)
-        dw.view(kc, cout).copy_(dwp[:kc])
-    else:
-        at = _scratch(dev, "A", kc * M).view(kc, M)
-        native.check(L.tfde_transpose_bf16(a.data_ptr(), at.data_ptr(), M, kc, kp, M, native.stream_ptr()),
-                     "transpose_bf16")
-        dyt = _scratch(dev, "B", cout * M).view(cout, M)
-        native.check(L.tfde_transpose_bf16(dy2.data_ptr(), dyt.data_ptr(), M, cout, cout, M, native.stream_ptr()),
-                     "transpose_bf16")
-        tensorcore.gemm_bf16_tn(at, dyt, None, False, torch.float32, out=dw.view(kc, cout))
+            at = _scratch(dev, "A", kc * M).view(kc, M)
+            native.check(L.tfde_transpose_bf16(a.data_ptr(), at.data_ptr(), M, kc, kp, M, native.stream_ptr()),
+                         "transpose_bf16")
+            dyt = _scratch(dev, "B", cout * M).view(cout, M)
+            native.check(L.tfde_transpose_bf16(dy2.data_ptr(), dyt.data_ptr(), M, cout, cout, M, native.stream_ptr()),
+                         "transpose_bf16")
+            tensorcore.gemm_bf16_tn(at, dyt, None, False, torch.float32, out=dw.view(kc, cout))
     db = None
     if has_bias:
         if bias_grad_zero:
